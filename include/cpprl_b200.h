@@ -1,0 +1,274 @@
+/* cpprl_b200.h — C ABI of the B200-native on-policy update hot path.
+ *
+ * This is the drop-in boundary.  Plain pointers and sizes only: no torch types,
+ * no C++ types, no exceptions.  Every pointer named `d_*` or documented "device" is a CUDA device
+ * pointer on the current device; `stream` is a `cudaStream_t` passed as `void *` (NULL = legacy
+ * default stream).  Every function returns 0 on success or a CPPRL_B200_E* code and leaves a
+ * message retrievable with cpprl_b200_last_error() (thread-local).  There is NO CPU fallback:
+ * with no usable sm_100 device every compute entry point returns CPPRL_B200_ECUDA.
+ *
+ * The C++ host shim (include/cpprl/ *.h, namespace cpprl) keeps the reference's class API and
+ * forwards here; the "replaces" notes cite the reference implementation (paths relative to the
+ * reference repository root) that each entry point stands in for.
+ *
+ * Layout conventions (identical to the reference's RolloutStorage, src/storage.cpp:23-48):
+ * all rollout tensors are time-major contiguous [T or T+1, N, ...] fp32, Discrete actions int64.
+ * A "row" is one transition; its flat id is t*N + env (src/generators/feed_forward_generator.cpp:51-76).
+ */
+#ifndef CPPRL_B200_H
+#define CPPRL_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CPPRL_B200_ABI_VERSION 1
+
+enum cpprl_b200_status
+{
+    CPPRL_B200_OK = 0,
+    CPPRL_B200_EINVAL = 1,       /* bad argument (null pointer, non-positive size, ...) */
+    CPPRL_B200_ECUDA = 2,        /* CUDA runtime error / no sm_100 device */
+    CPPRL_B200_EUNSUPPORTED = 3, /* configuration not implemented on the GPU path (fails loudly) */
+    CPPRL_B200_ENCCL = 4,        /* communicator error */
+    CPPRL_B200_ESTATE = 5        /* call sequence error (e.g. epoch() before begin()) */
+};
+
+enum cpprl_b200_base_kind
+{
+    CPPRL_B200_BASE_MLP = 0,     /* MlpBase, non recurrent  (src/model/mlp_base.cpp:9-64) */
+    CPPRL_B200_BASE_GRU_MLP = 1, /* MlpBase with GRU front  (src/model/nn_base.cpp:47-114) */
+    CPPRL_B200_BASE_CNN = 2      /* CnnBase                 (src/model/cnn_base.cpp:9-47) */
+};
+
+enum cpprl_b200_head_kind
+{
+    CPPRL_B200_HEAD_CATEGORICAL = 0, /* CategoricalOutput + Categorical (src/model/output_layers.cpp:31-43) */
+    CPPRL_B200_HEAD_NORMAL = 1       /* NormalOutput + Normal           (src/model/output_layers.cpp:45-59) */
+};
+
+/* ---- library / error ------------------------------------------------------------------- */
+
+int cpprl_b200_abi_version(void);
+/* Thread-local text of the last failure on this thread ("" if none). */
+const char *cpprl_b200_last_error(void);
+/* Number of kernels this library has launched in this process (all threads). */
+uint64_t cpprl_b200_launch_count(void);
+/* 0 if the current device is usable (compute capability 10.x); fills sm_count / name if non-NULL. */
+int cpprl_b200_device_info(int *sm_count, int *cc_major, int *cc_minor, char *name, int name_len);
+
+/* ---- (a) returns / GAE ------------------------------------------------------------------
+ * replaces RolloutStorage::compute_returns, src/storage.cpp:113-144.
+ *   use_gae != 0: value_preds[T] <- next_value; backward scan
+ *        delta = r[t] + gamma*V[t+1]*m[t+1] - V[t];  gae = delta + (gamma*tau)*m[t+1]*gae;
+ *        returns[t] = gae + V[t]            (returns[T] is left untouched, as the reference does)
+ *   use_gae == 0: returns[T] <- next_value; returns[t] = returns[t+1]*gamma*m[t+1] + r[t]
+ * rewards [T,N], value_preds [T+1,N] (row T written in GAE mode), masks [T+1,N], next_value [N],
+ * returns [T+1,N].  One thread per environment (4 with 16-byte accesses when N % 4 == 0),
+ * backward in time with the loads of several steps in flight; no communication between envs. */
+int cpprl_b200_compute_returns(const float *d_rewards, float *d_value_preds, const float *d_masks,
+                               const float *d_next_value, float *d_returns, int64_t T, int64_t N,
+                               int use_gae, float gamma, float tau, void *stream);
+
+/* ---- advantage = returns[:T] - value_preds[:T], normalised -------------------------------
+ * replaces the prologue of PPO::update, src/algorithms/ppo.cpp:51-57:
+ *   adv = (adv - mean(adv)) / (std(adv) + 1e-5), std with Bessel's correction over all T*N values.
+ * d_moments (device, 4 doubles, zeroed by the call) receives {sum, sum of squares, mean, std}.
+ * d_advantages [T,N] receives the normalised advantages (normalize != 0) or the raw ones. */
+int cpprl_b200_advantages(const float *d_returns, const float *d_value_preds, int64_t T, int64_t N,
+                          int normalize, float *d_advantages, double *d_moments, void *stream);
+
+/* ---- (b) minibatch gather ----------------------------------------------------------------
+ * replaces the eight `.index(indices[k])` gathers of FeedForwardGenerator::next,
+ * src/generators/feed_forward_generator.cpp:42-80, for ONE field:
+ *   dst[i, :] = src[idx[i], :]   for i < n_idx, rows of row_bytes bytes (any dtype; bit-exact copy).
+ * idx is int64 (device), values in [0, n_src_rows).  row_bytes must be a multiple of 4. */
+int cpprl_b200_gather_rows(const void *d_src, int64_t n_src_rows, int64_t row_bytes, const int64_t *d_idx,
+                           int64_t n_idx, void *d_dst, void *stream);
+
+/* ---- (e) observation normaliser ------------------------------------------------------------
+ * replaces RunningMeanStdImpl::update / update_from_moments, src/running_mean_std.cpp:20-43:
+ * batch mean and POPULATION variance of x [M,D] per column, then the Chan merge into
+ * (count[1], mean[D], var[D]) (all fp32 device buffers, updated in place).
+ * d_workspace: device scratch of cpprl_b200_rms_workspace_bytes(M, D) bytes. */
+int64_t cpprl_b200_rms_workspace_bytes(int64_t M, int64_t D);
+int cpprl_b200_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean,
+                          float *d_var, void *d_workspace, void *stream);
+/* replaces ObservationNormalizerImpl::process_observation, src/observation_normalizer.cpp:69-74:
+ *   out = clamp((x - mean) / sqrt(var + 1e-8), -clip, +clip),  x/out [M,D]; clip read from device. */
+int cpprl_b200_normalize_observations(const float *d_x, int64_t M, int64_t D, const float *d_mean,
+                                      const float *d_var, const float *d_clip, float *d_out, void *stream);
+
+/* ---- (d) optimiser steps on a flat fp32 buffer ----------------------------------------------
+ * replaces torch::optim::Adam::step as constructed at src/algorithms/ppo.cpp:39-42 (betas 0.9/0.999,
+ * no weight decay, no amsgrad):  m = b1*m + (1-b1)*g;  v = b2*v + (1-b2)*g*g;
+ *   p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps),   t = step (1-based, host supplied). */
+int cpprl_b200_adam_step(float *d_params, const float *d_grads, float *d_exp_avg, float *d_exp_avg_sq,
+                         int64_t n, int64_t step, float lr, float beta1, float beta2, float eps, void *stream);
+/* replaces torch::optim::RMSprop::step as constructed at src/algorithms/a2c.cpp:30-34 (momentum 0, not
+ * centered):  s = alpha*s + (1-alpha)*g*g;  p -= lr * g / (sqrt(s) + eps). */
+int cpprl_b200_rmsprop_step(float *d_params, const float *d_grads, float *d_square_avg, int64_t n, float lr,
+                            float alpha, float eps, void *stream);
+
+/* ---- policy description -------------------------------------------------------------------
+ * Parameters live in ONE flat fp32 device buffer in the reference's module registration order
+ * (checked against the oracle's named_parameters() in tests/):
+ *   MLP      : actor.0.{weight[H,D],bias[H]} actor.2.{weight[H,H],bias[H]}
+ *              critic.0.{weight[H,D],bias[H]} critic.2.{weight[H,H],bias[H]}
+ *              critic_linear.{weight[1,H],bias[1]}  then the head
+ *   GRU_MLP  : gru.{weight_ih_l0[3H,D],weight_hh_l0[3H,H],bias_ih_l0[3H],bias_hh_l0[3H]} first,
+ *              towers then take H inputs
+ *   head     : Categorical  linear.{weight[A,H],bias[A]}
+ *              Normal       scale_log[A], linear_loc.{weight[A,H],bias[A]}
+ * The host shim makes the torch modules' parameter tensors views into this buffer, so the kernels
+ * update them in place. */
+typedef struct cpprl_b200_policy
+{
+    int32_t base_kind;    /* cpprl_b200_base_kind */
+    int32_t head_kind;    /* cpprl_b200_head_kind */
+    int64_t obs_dim;      /* D (MLP bases) or C*H*W (CNN) */
+    int64_t obs_chw[3];   /* CNN only: C, H, W */
+    int64_t hidden;       /* H: 64 (MLP bases) / 512 (CNN) */
+    int64_t num_actions;  /* A */
+    float *d_params;      /* flat parameters, n_params floats */
+    int64_t n_params;
+    /* observation normaliser buffers (src/observation_normalizer.cpp:9-11, src/running_mean_std.cpp:8-11);
+     * all NULL when the policy was built with normalize_observations = false */
+    float *d_norm_clip;   /* [1] */
+    float *d_norm_count;  /* [1] */
+    float *d_norm_mean;   /* [D] */
+    float *d_norm_var;    /* [D] */
+} cpprl_b200_policy;
+
+/* Number of parameters the layout above implies (0 if the description is unsupported). */
+int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy);
+
+/* ---- rollout description -------------------------------------------------------------------
+ * Device views of the reference's RolloutStorage buffers (src/storage.cpp:15-49). */
+typedef struct cpprl_b200_rollout
+{
+    int64_t T, N;
+    int64_t hidden_dim;              /* Hs of the storage (row width of d_hidden_states) */
+    int64_t action_cols;             /* 1 for Discrete, A for Box */
+    const float *d_observations;     /* [T+1,N,D] */
+    const float *d_hidden_states;    /* [T+1,N,Hs]   (read by recurrent policies only) */
+    const void *d_actions;           /* int64 [T,N,1] (Categorical) or fp32 [T,N,A] (Normal) */
+    const float *d_value_preds;      /* [T+1,N] */
+    const float *d_returns;          /* [T+1,N] */
+    const float *d_masks;            /* [T+1,N] */
+    const float *d_action_log_probs; /* [T,N] */
+} cpprl_b200_rollout;
+
+/* ---- (c) forward evaluation ------------------------------------------------------------------
+ * replaces PolicyImpl::evaluate_actions, src/model/policy.cpp:83-115 (forward only), on B explicit rows:
+ * obs [B,D], masks [B] and hxs [n_hxs,H] (recurrent only; n_hxs == B selects step mode, otherwise
+ * sequence mode with n_hxs agents, src/model/nn_base.cpp:51-112), actions int64 [B] or fp32 [B,A].
+ * Outputs: value [B], logp [B], entropy [1] (mean over rows), hxs_out [n_hxs,H] (recurrent; may be NULL). */
+int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs,
+                                int64_t n_hxs, const float *d_masks, const void *d_actions, int64_t B,
+                                float *d_value, float *d_logp, float *d_entropy, float *d_hxs_out,
+                                void *stream);
+
+/* ---- (c)+(d) PPO update -----------------------------------------------------------------------
+ * replaces PPO::update, src/algorithms/ppo.cpp:44-178, including the generator's gathers
+ * (feed_forward_generator.cpp:42-80 / recurrent_generator.cpp:47-98), Policy::evaluate_actions,
+ * the loss, autograd backward, torch::optim::Adam::step and the final normaliser update.
+ * The handle owns the Adam state (exp_avg, exp_avg_sq, step), which persists across updates exactly
+ * as the reference's optimizer member does (ppo.h:22). */
+typedef struct cpprl_b200_ppo_options
+{
+    float clip_param;      /* ppo.cpp:47 (multiplied by decay_level by the caller) */
+    int32_t num_epoch;
+    int32_t num_mini_batch;
+    float actor_loss_coef, value_loss_coef, entropy_coef;
+    float learning_rate;   /* already multiplied by decay_level, ppo.cpp:48 */
+    float epsilon;         /* Adam eps */
+    float kl_target;       /* stop before applying a minibatch whose KL > 1.5*kl_target, ppo.cpp:96-104 */
+} cpprl_b200_ppo_options;
+
+/* Statistics in the order PPO::update returns them, ppo.cpp:156-177. */
+typedef struct cpprl_b200_ppo_stats
+{
+    float value_loss, action_loss, clip_fraction, entropy, kl_divergence;
+    float kl_early_stop_update; /* -1 if the update ran to the end */
+    int32_t num_updates;        /* optimizer steps applied */
+} cpprl_b200_ppo_stats;
+
+typedef struct cpprl_b200_ppo cpprl_b200_ppo; /* opaque */
+
+int cpprl_b200_ppo_create(cpprl_b200_ppo **out, int64_t n_params);
+void cpprl_b200_ppo_destroy(cpprl_b200_ppo *h);
+/* Device pointers to the optimizer state (n_params floats each) and the step counter, for checkpointing. */
+int cpprl_b200_ppo_state(cpprl_b200_ppo *h, float **d_exp_avg, float **d_exp_avg_sq, int64_t *step);
+int cpprl_b200_ppo_set_step(cpprl_b200_ppo *h, int64_t step);
+
+/* Whole update in one call.  h_perms: HOST int64 permutations, one per epoch, drawn by the caller exactly
+ * as the reference's generators draw them (torch::randperm(T*N) per epoch for feed-forward policies,
+ * feed_forward_generator.cpp:31-34; torch::randperm(N) per epoch for recurrent ones,
+ * recurrent_generator.cpp:38) laid out [num_epoch, perm_len].  Synchronous at return (stats are host
+ * values), one stream synchronisation in total.
+ * Feed-forward minibatch k of an epoch is rows perm[k*mbs .. (k+1)*mbs), mbs = (T*N)/num_mini_batch;
+ * (T*N) % mbs != 0 is EINVAL (the reference's .view throws).  Recurrent: num_mini_batch must equal N
+ * (reference quirk): minibatch k is environment perm[k], all T steps. */
+int cpprl_b200_ppo_update(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                          const cpprl_b200_ppo_options *opt, const int64_t *h_perms, int64_t perm_len,
+                          cpprl_b200_ppo_stats *stats, void *stream);
+
+/* The same update in stages, so the host can draw epoch e+1's permutation while epoch e runs and can
+ * honour the KL early stop without drawing permutations the reference would not draw:
+ *   begin (advantage moments) -> epoch x num_epoch (each: async H2D of the permutation + one persistent
+ *   kernel over the epoch's minibatches) -> [stopped() between epochs when kl_target can trigger] -> end
+ *   (normaliser update, statistics read-back, the only mandatory synchronisation). */
+int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                         const cpprl_b200_ppo_options *opt, void *stream);
+int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, int64_t perm_len);
+/* Same as ppo_epoch with the permutation already on the device (int64). */
+int cpprl_b200_ppo_epoch_device(cpprl_b200_ppo *h, const int64_t *d_perm, int64_t perm_len);
+int cpprl_b200_ppo_stopped(cpprl_b200_ppo *h, int *stopped); /* synchronises */
+int cpprl_b200_ppo_end(cpprl_b200_ppo *h, cpprl_b200_ppo_stats *stats);
+/* Like ppo_end but leaves the statistics on the device and does not synchronise (for CUDA-event timing);
+ * fetch later with ppo_fetch_stats. */
+int cpprl_b200_ppo_end_async(cpprl_b200_ppo *h);
+int cpprl_b200_ppo_fetch_stats(cpprl_b200_ppo *h, cpprl_b200_ppo_stats *stats);
+
+/* ---- A2C update --------------------------------------------------------------------------------
+ * replaces A2C::update, src/algorithms/a2c.cpp:36-90 (normaliser update FIRST, one forward/backward over
+ * all T*N rows, value loss mean(adv^2) without 0.5, actor_loss_coef ignored, RMSprop step). */
+typedef struct cpprl_b200_a2c_options
+{
+    float value_loss_coef, entropy_coef;
+    float learning_rate; /* already multiplied by decay_level, a2c.cpp:39 */
+    float epsilon, alpha;
+} cpprl_b200_a2c_options;
+
+typedef struct cpprl_b200_a2c_stats
+{
+    float value_loss, action_loss, entropy; /* a2c.cpp:87-89 */
+} cpprl_b200_a2c_stats;
+
+typedef struct cpprl_b200_a2c cpprl_b200_a2c; /* opaque */
+
+int cpprl_b200_a2c_create(cpprl_b200_a2c **out, int64_t n_params);
+void cpprl_b200_a2c_destroy(cpprl_b200_a2c *h);
+int cpprl_b200_a2c_state(cpprl_b200_a2c *h, float **d_square_avg);
+int cpprl_b200_a2c_update(cpprl_b200_a2c *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                          const cpprl_b200_a2c_options *opt, cpprl_b200_a2c_stats *stats, void *stream);
+int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_policy *policy,
+                                const cpprl_b200_rollout *rollout, const cpprl_b200_a2c_options *opt,
+                                void *stream);
+int cpprl_b200_a2c_fetch_stats(cpprl_b200_a2c *h, cpprl_b200_a2c_stats *stats);
+
+/* ---- timing hooks ---------------------------------------------------------------------------------
+ * The fused kernels record CUDA events on the caller's stream around each launch; these return the
+ * accumulated device time and launch count of the named kernel family since the last reset
+ * ("update", "returns", "advantages", "rms", "gather").  Synchronises the events it reads. */
+int cpprl_b200_kernel_time_ms(const char *family, double *total_ms, int64_t *launches);
+void cpprl_b200_kernel_time_reset(void);
+void cpprl_b200_kernel_time_enable(int on);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CPPRL_B200_H */

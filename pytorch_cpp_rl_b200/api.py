@@ -1,0 +1,419 @@
+"""Python host-side mirror of the reference's operator interface for the update hot path.
+
+Same names and argument meaning as the reference's C++ classes (`RolloutStorage::compute_returns`,
+`PPO::update`, `A2C::update`, `Policy::evaluate_actions`, `FeedForwardGenerator`, `ObservationNormalizer`,
+`RunningMeanStd`) so the parity tests read like the reference's own.  Every method forwards to the C ABI
+(include/cpprl_b200.h); torch is used only to own device memory and streams.  The C++ drop-in
+(include/cpprl/*.h, libcpprl.so) sits on the same C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import cabi
+from .cabi import check
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("cpprl_b200: tensors must live on a CUDA device (there is no CPU fallback)")
+        if t is not None and not t.is_contiguous():
+            raise RuntimeError("cpprl_b200: tensors must be contiguous")
+
+
+# ---------------------------------------------------------------------------------------------------
+# spaces / policy
+# ---------------------------------------------------------------------------------------------------
+@dataclass
+class ActionSpace:  # include/cpprl/spaces.h:9-13 in the reference
+    type: str
+    shape: Sequence[int]
+
+
+def mlp_param_shapes(num_inputs: int, num_actions: int, head: str, hidden: int = 64, recurrent: bool = False):
+    """(name, shape) list in the reference's module registration order."""
+    shapes = []
+    tower_in = num_inputs
+    if recurrent:
+        shapes += [("base.gru.weight_ih_l0", (3 * hidden, num_inputs)), ("base.gru.weight_hh_l0", (3 * hidden, hidden)),
+                   ("base.gru.bias_ih_l0", (3 * hidden,)), ("base.gru.bias_hh_l0", (3 * hidden,))]
+        tower_in = hidden
+    for tower in ("actor", "critic"):
+        shapes += [(f"base.{tower}.0.weight", (hidden, tower_in)), (f"base.{tower}.0.bias", (hidden,)),
+                   (f"base.{tower}.2.weight", (hidden, hidden)), (f"base.{tower}.2.bias", (hidden,))]
+    shapes += [("base.critic_linear.weight", (1, hidden)), ("base.critic_linear.bias", (1,))]
+    if head == "Discrete":
+        shapes += [("output.linear.weight", (num_actions, hidden)), ("output.linear.bias", (num_actions,))]
+    elif head == "Box":
+        shapes += [("output.scale_log", (num_actions,)), ("output.linear_loc.weight", (num_actions, hidden)),
+                   ("output.linear_loc.bias", (num_actions,))]
+    else:
+        raise RuntimeError(f"Action space {head} not supported")
+    return shapes
+
+
+class RunningMeanStd:
+    """Device buffers count[1], mean[D], variance[D] (running_mean_std.cpp:8-11) updated by the rms kernel."""
+
+    def __init__(self, size: int, device="cuda"):
+        self.count = torch.full((1,), 1e-4, dtype=torch.float32, device=device)
+        self.mean = torch.zeros(size, dtype=torch.float32, device=device)
+        self.variance = torch.ones(size, dtype=torch.float32, device=device)
+        self._ws = None
+
+    def update(self, observation: torch.Tensor) -> None:
+        D = self.mean.numel()
+        x = observation.reshape(-1, D)
+        _need_cuda(x)
+        lib = cabi.load()
+        need = lib.cpprl_b200_rms_workspace_bytes(x.shape[0], D)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(need, dtype=torch.uint8, device=x.device)
+        check(lib.cpprl_b200_rms_update(_ptr(x), x.shape[0], D, _ptr(self.count), _ptr(self.mean),
+                                        _ptr(self.variance), _ptr(self._ws), _stream()))
+
+
+class ObservationNormalizer:
+    def __init__(self, size: int, clip: float = 10.0, device="cuda"):
+        self.clip = torch.full((1,), clip, dtype=torch.float32, device=device)
+        self.rms = RunningMeanStd(size, device)
+
+    def process_observation(self, observation: torch.Tensor) -> torch.Tensor:
+        D = self.rms.mean.numel()
+        x = observation.reshape(-1, D)
+        _need_cuda(x)
+        out = torch.empty_like(x)
+        check(cabi.load().cpprl_b200_normalize_observations(_ptr(x), x.shape[0], D, _ptr(self.rms.mean),
+                                                            _ptr(self.rms.variance), _ptr(self.clip), _ptr(out),
+                                                            _stream()))
+        return out.view(observation.shape)
+
+    def update(self, observations: torch.Tensor) -> None:
+        self.rms.update(observations)
+
+
+class Policy:
+    """Flat-parameter policy (MlpBase + Categorical / Normal head).  `params` is ONE fp32 device buffer in
+    the reference's registration order; `named_parameters()` returns views into it."""
+
+    def __init__(self, action_space: ActionSpace, num_inputs: int, normalize_observations: bool = False,
+                 hidden: int = 64, recurrent: bool = False, device="cuda"):
+        if action_space.type not in ("Discrete", "Box"):
+            raise RuntimeError("Action space " + action_space.type + " not supported")
+        self.action_space = action_space
+        self.num_inputs = num_inputs
+        self.hidden = hidden
+        self.recurrent = recurrent
+        self.num_actions = int(action_space.shape[0])
+        self.shapes = mlp_param_shapes(num_inputs, self.num_actions, action_space.type, hidden, recurrent)
+        n = sum(int(torch.Size(s).numel()) for _, s in self.shapes)
+        self.params = torch.zeros(n, dtype=torch.float32, device=device)
+        self.observation_normalizer = ObservationNormalizer(num_inputs, device=device) if normalize_observations else None
+
+    def named_parameters(self):
+        out, o = [], 0
+        for name, shape in self.shapes:
+            n = int(torch.Size(shape).numel())
+            out.append((name, self.params[o:o + n].view(shape)))
+            o += n
+        return out
+
+    def is_recurrent(self) -> bool:
+        return self.recurrent
+
+    def using_observation_normalizer(self) -> bool:
+        return self.observation_normalizer is not None
+
+    def update_observation_normalizer(self, observations: torch.Tensor) -> None:
+        assert self.observation_normalizer is not None
+        self.observation_normalizer.update(observations)
+
+    def desc(self) -> cabi.Policy:
+        p = cabi.Policy()
+        p.base_kind = cabi.BASE_GRU_MLP if self.recurrent else cabi.BASE_MLP
+        p.head_kind = cabi.HEAD_CATEGORICAL if self.action_space.type == "Discrete" else cabi.HEAD_NORMAL
+        p.obs_dim = self.num_inputs
+        p.hidden = self.hidden
+        p.num_actions = self.num_actions
+        p.d_params = self.params.data_ptr()
+        p.n_params = self.params.numel()
+        if self.observation_normalizer is not None:
+            n = self.observation_normalizer
+            p.d_norm_clip = n.clip.data_ptr()
+            p.d_norm_count = n.rms.count.data_ptr()
+            p.d_norm_mean = n.rms.mean.data_ptr()
+            p.d_norm_var = n.rms.variance.data_ptr()
+        return p
+
+    def evaluate_actions(self, inputs, rnn_hxs, masks, actions) -> List[torch.Tensor]:
+        """{value [B,1], action_log_probs [B,1], entropy [], rnn_hxs} — policy.cpp:83-115 (forward only)."""
+        _need_cuda(inputs, actions)
+        B = inputs.shape[0]
+        value = torch.empty(B, 1, dtype=torch.float32, device=inputs.device)
+        logp = torch.empty(B, 1, dtype=torch.float32, device=inputs.device)
+        entropy = torch.empty(1, dtype=torch.float32, device=inputs.device)
+        d = self.desc()
+        n_hxs = 0 if rnn_hxs is None else rnn_hxs.shape[0]
+        check(cabi.load().cpprl_b200_evaluate_actions(C.byref(d), _ptr(inputs), _ptr(rnn_hxs), n_hxs, _ptr(masks),
+                                                      _ptr(actions), B, _ptr(value), _ptr(logp), _ptr(entropy),
+                                                      None, _stream()))
+        return [value, logp, entropy.view(()), rnn_hxs]
+
+
+# ---------------------------------------------------------------------------------------------------
+# rollout storage
+# ---------------------------------------------------------------------------------------------------
+class RolloutStorage:
+    """Time-major fp32 buffers exactly as storage.cpp:15-49 lays them out, resident in HBM."""
+
+    def __init__(self, num_steps: int, num_processes: int, obs_shape: Sequence[int], action_space: ActionSpace,
+                 hidden_state_size: int, device="cuda"):
+        f = dict(dtype=torch.float32, device=device)
+        T, N = num_steps, num_processes
+        self.num_steps, self.num_processes = T, N
+        self.action_space = action_space
+        self.observations = torch.zeros(T + 1, N, *obs_shape, **f)
+        self.hidden_states = torch.zeros(T + 1, N, hidden_state_size, **f)
+        self.rewards = torch.zeros(T, N, 1, **f)
+        self.value_predictions = torch.zeros(T + 1, N, 1, **f)
+        self.returns = torch.zeros(T + 1, N, 1, **f)
+        self.action_log_probs = torch.zeros(T, N, 1, **f)
+        if action_space.type == "Discrete":
+            self.actions = torch.zeros(T, N, 1, dtype=torch.int64, device=device)
+        else:
+            self.actions = torch.zeros(T, N, int(action_space.shape[0]), **f)
+        self.masks = torch.ones(T + 1, N, 1, **f)
+        self.step = 0
+
+    def compute_returns(self, next_value: torch.Tensor, use_gae: bool, gamma: float, tau: float) -> None:
+        _need_cuda(self.rewards, self.value_predictions, self.masks, next_value, self.returns)
+        check(cabi.load().cpprl_b200_compute_returns(_ptr(self.rewards), _ptr(self.value_predictions), _ptr(self.masks),
+                                                     _ptr(next_value), _ptr(self.returns), self.num_steps,
+                                                     self.num_processes, int(use_gae), gamma, tau, _stream()))
+
+    def after_update(self) -> None:  # storage.cpp:106-111
+        self.observations[0].copy_(self.observations[-1])
+        self.hidden_states[0].copy_(self.hidden_states[-1])
+        self.masks[0].copy_(self.masks[-1])
+
+    def desc(self) -> cabi.Rollout:
+        r = cabi.Rollout()
+        r.T, r.N = self.num_steps, self.num_processes
+        r.hidden_dim = self.hidden_states.shape[-1]
+        r.action_cols = self.actions.shape[-1]
+        r.d_observations = self.observations.data_ptr()
+        r.d_hidden_states = self.hidden_states.data_ptr()
+        r.d_actions = self.actions.data_ptr()
+        r.d_value_preds = self.value_predictions.data_ptr()
+        r.d_returns = self.returns.data_ptr()
+        r.d_masks = self.masks.data_ptr()
+        r.d_action_log_probs = self.action_log_probs.data_ptr()
+        return r
+
+    def feed_forward_generator(self, advantages: torch.Tensor, num_mini_batch: int, indices: torch.Tensor):
+        """Minibatches as FeedForwardGenerator::next yields them (feed_forward_generator.cpp:42-80) for a
+        caller-supplied permutation (`indices`, int64, host or device).  Returns a list of dicts."""
+        T, N = self.num_steps, self.num_processes
+        batch = T * N
+        if batch < num_mini_batch:
+            raise RuntimeError(
+                f"PPO needs the number of processes ({N}) * the number of steps ({T}) = {batch} to be greater than "
+                f"or equal to the number of minibatches ({num_mini_batch})")
+        mbs = batch // num_mini_batch
+        idx = indices.to(self.observations.device).view(-1, mbs)
+        fields = {
+            "observations": self.observations[:T].reshape(batch, -1),
+            "hidden_states": self.hidden_states[:T].reshape(batch, -1),
+            "actions": self.actions.reshape(batch, -1),
+            "value_predictions": self.value_predictions[:T].reshape(batch, 1),
+            "returns": self.returns[:T].reshape(batch, 1),
+            "masks": self.masks[:T].reshape(batch, 1),
+            "action_log_probs": self.action_log_probs.reshape(batch, 1),
+            "advantages": advantages.reshape(batch, 1),
+        }
+        out = []
+        for k in range(idx.shape[0]):
+            mb = {name: gather_rows(src.contiguous(), idx[k].contiguous()) for name, src in fields.items()}
+            mb["observations"] = mb["observations"].view(mbs, *self.observations.shape[2:])
+            out.append(mb)
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# stand-alone stages
+# ---------------------------------------------------------------------------------------------------
+def gather_rows(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """dst[i] = src[idx[i]] for 2-D src (bit-exact copy; replaces Tensor::index on flattened rows)."""
+    _need_cuda(src, idx)
+    assert idx.dtype == torch.int64 and src.dim() == 2
+    dst = torch.empty((idx.numel(), src.shape[1]), dtype=src.dtype, device=src.device)
+    row_bytes = src.shape[1] * src.element_size()
+    check(cabi.load().cpprl_b200_gather_rows(_ptr(src), src.shape[0], row_bytes, _ptr(idx), idx.numel(), _ptr(dst),
+                                             _stream()))
+    return dst
+
+
+def advantages(returns: torch.Tensor, value_preds: torch.Tensor, normalize: bool = True):
+    """returns[:-1] - value_preds[:-1], normalised as ppo.cpp:51-57.  Returns (adv [T,N,1], moments[4] f64)."""
+    _need_cuda(returns, value_preds)
+    T, N = returns.shape[0] - 1, returns.shape[1]
+    adv = torch.empty(T, N, 1, dtype=torch.float32, device=returns.device)
+    moments = torch.empty(4, dtype=torch.float64, device=returns.device)
+    check(cabi.load().cpprl_b200_advantages(_ptr(returns), _ptr(value_preds), T, N, int(normalize), _ptr(adv),
+                                            _ptr(moments), _stream()))
+    return adv, moments
+
+
+def adam_step(params, grads, exp_avg, exp_avg_sq, step: int, lr: float, eps: float = 1e-8, beta1=0.9, beta2=0.999):
+    _need_cuda(params, grads, exp_avg, exp_avg_sq)
+    check(cabi.load().cpprl_b200_adam_step(_ptr(params), _ptr(grads), _ptr(exp_avg), _ptr(exp_avg_sq), params.numel(),
+                                           step, lr, beta1, beta2, eps, _stream()))
+
+
+def rmsprop_step(params, grads, square_avg, lr: float, alpha: float = 0.99, eps: float = 1e-8):
+    _need_cuda(params, grads, square_avg)
+    check(cabi.load().cpprl_b200_rmsprop_step(_ptr(params), _ptr(grads), _ptr(square_avg), params.numel(), lr, alpha,
+                                              eps, _stream()))
+
+
+# ---------------------------------------------------------------------------------------------------
+# algorithms
+# ---------------------------------------------------------------------------------------------------
+@dataclass
+class UpdateDatum:  # algorithm.h:10-14
+    name: str
+    value: float
+
+
+class PPO:
+    """cpprl::PPO (ppo.h:24-36) over the fused CUDA update.  `update` needs the per-epoch permutations the
+    reference's generator would draw; by default they are drawn here with torch.randperm on the CPU generator,
+    one per epoch, exactly as feed_forward_generator.cpp:31-34 does."""
+
+    def __init__(self, policy: Policy, clip_param: float, num_epoch: int, num_mini_batch: int, actor_loss_coef: float,
+                 value_loss_coef: float, entropy_coef: float, learning_rate: float, epsilon: float = 1e-8,
+                 max_grad_norm: float = 0.5, kl_target: float = 0.01):
+        self.policy = policy
+        self.original_clip_param = clip_param
+        self.num_epoch, self.num_mini_batch = num_epoch, num_mini_batch
+        self.actor_loss_coef, self.value_loss_coef, self.entropy_coef = actor_loss_coef, value_loss_coef, entropy_coef
+        self.original_learning_rate = learning_rate
+        self.epsilon, self.max_grad_norm, self.kl_target = epsilon, max_grad_norm, kl_target
+        self._h = C.c_void_p()
+        check(cabi.load().cpprl_b200_ppo_create(C.byref(self._h), policy.params.numel()))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            cabi.load().cpprl_b200_ppo_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def _options(self, decay_level: float) -> cabi.PPOOptions:
+        import numpy as np
+        o = cabi.PPOOptions()
+        # float32 products, as the reference forms them (ppo.cpp:47-48)
+        o.clip_param = float(np.float32(self.original_clip_param) * np.float32(decay_level))
+        o.learning_rate = float(np.float32(self.original_learning_rate) * np.float32(decay_level))
+        o.num_epoch, o.num_mini_batch = self.num_epoch, self.num_mini_batch
+        o.actor_loss_coef, o.value_loss_coef, o.entropy_coef = self.actor_loss_coef, self.value_loss_coef, self.entropy_coef
+        o.epsilon, o.kl_target = self.epsilon, self.kl_target
+        return o
+
+    def optimizer_state(self):
+        m, v, step = C.c_void_p(), C.c_void_p(), C.c_int64()
+        check(cabi.load().cpprl_b200_ppo_state(self._h, C.byref(m), C.byref(v), C.byref(step)))
+        return m.value, v.value, step.value
+
+    def update(self, rollouts: RolloutStorage, decay_level: float = 1.0, perms: Optional[torch.Tensor] = None,
+               return_stats: bool = False):
+        lib = cabi.load()
+        T, N = rollouts.num_steps, rollouts.num_processes
+        if perms is None:
+            n = N if self.policy.is_recurrent() else T * N
+            perms = torch.stack([torch.randperm(n, dtype=torch.int64) for _ in range(self.num_epoch)])
+        perms = perms.contiguous()
+        assert perms.dtype == torch.int64 and not perms.is_cuda
+        pd, rd, od = self.policy.desc(), rollouts.desc(), self._options(decay_level)
+        stats = cabi.PPOStats()
+        check(lib.cpprl_b200_ppo_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(perms.data_ptr()),
+                                        perms.shape[1], C.byref(stats), _stream()))
+        if return_stats:
+            return stats
+        data = [UpdateDatum("Value loss", stats.value_loss), UpdateDatum("Action loss", stats.action_loss),
+                UpdateDatum("Clip fraction", stats.clip_fraction), UpdateDatum("Entropy", stats.entropy),
+                UpdateDatum("KL divergence", stats.kl_divergence)]
+        if stats.kl_early_stop_update > -1:
+            data.append(UpdateDatum("KL divergence early stop update", stats.kl_early_stop_update))
+        return data
+
+    # staged interface (device-resident permutations, no synchronisation until fetch) used by bench.py
+    def begin(self, rollouts: RolloutStorage, decay_level: float = 1.0):
+        self._keep = (self.policy.desc(), rollouts.desc(), self._options(decay_level))
+        pd, rd, od = self._keep
+        check(cabi.load().cpprl_b200_ppo_begin(self._h, C.byref(pd), C.byref(rd), C.byref(od), _stream()))
+
+    def epoch_device(self, d_perm: torch.Tensor):
+        check(cabi.load().cpprl_b200_ppo_epoch_device(self._h, _ptr(d_perm), d_perm.numel()))
+
+    def end_async(self):
+        check(cabi.load().cpprl_b200_ppo_end_async(self._h))
+
+    def fetch_stats(self) -> cabi.PPOStats:
+        stats = cabi.PPOStats()
+        check(cabi.load().cpprl_b200_ppo_fetch_stats(self._h, C.byref(stats)))
+        return stats
+
+
+class A2C:
+    """cpprl::A2C (a2c.h:23-32) over the fused CUDA update."""
+
+    def __init__(self, policy: Policy, actor_loss_coef: float, value_loss_coef: float, entropy_coef: float,
+                 learning_rate: float, epsilon: float = 1e-8, alpha: float = 0.99, max_grad_norm: float = 0.5):
+        self.policy = policy
+        self.actor_loss_coef, self.value_loss_coef, self.entropy_coef = actor_loss_coef, value_loss_coef, entropy_coef
+        self.original_learning_rate = learning_rate
+        self.epsilon, self.alpha, self.max_grad_norm = epsilon, alpha, max_grad_norm
+        self._h = C.c_void_p()
+        check(cabi.load().cpprl_b200_a2c_create(C.byref(self._h), policy.params.numel()))
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value:
+            cabi.load().cpprl_b200_a2c_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def _options(self, decay_level: float) -> cabi.A2COptions:
+        import numpy as np
+        o = cabi.A2COptions()
+        o.value_loss_coef, o.entropy_coef = self.value_loss_coef, self.entropy_coef
+        o.learning_rate = float(np.float32(self.original_learning_rate) * np.float32(decay_level))
+        o.epsilon, o.alpha = self.epsilon, self.alpha
+        return o
+
+    def update(self, rollouts: RolloutStorage, decay_level: float = 1.0):
+        pd, rd, od = self.policy.desc(), rollouts.desc(), self._options(decay_level)
+        stats = cabi.A2CStats()
+        check(cabi.load().cpprl_b200_a2c_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.byref(stats), _stream()))
+        return [UpdateDatum("Value loss", stats.value_loss), UpdateDatum("Action loss", stats.action_loss),
+                UpdateDatum("Entropy", stats.entropy)]
+
+    def update_async(self, rollouts: RolloutStorage, decay_level: float = 1.0):
+        self._keep = (self.policy.desc(), rollouts.desc(), self._options(decay_level))
+        pd, rd, od = self._keep
+        check(cabi.load().cpprl_b200_a2c_update_async(self._h, C.byref(pd), C.byref(rd), C.byref(od), _stream()))
+
+    def fetch_stats(self) -> cabi.A2CStats:
+        stats = cabi.A2CStats()
+        check(cabi.load().cpprl_b200_a2c_fetch_stats(self._h, C.byref(stats)))
+        return stats

@@ -1,0 +1,774 @@
+// cabi_update.cu — C-ABI entry points for evaluate_actions, PPO update and A2C update
+// (host-side orchestration: validation, scratch, permutation staging, launches, statistics read-back).
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "mlp_update.cuh"
+
+namespace cpprl_b200
+{
+// from mlp_update.cu / returns_scan.cu
+size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap);
+int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s);
+int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums,
+                             cudaStream_t s);
+
+namespace
+{
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// Parameter offsets of the non-recurrent MLP policy in the reference's registration order.
+bool mlp_param_offsets(const cpprl_b200_policy &p, ParamOffsets &po)
+{
+    if (p.base_kind != CPPRL_B200_BASE_MLP || p.hidden != kHid)
+        return false;
+    const int D = static_cast<int>(p.obs_dim), A = static_cast<int>(p.num_actions);
+    int o = 0;
+    po.w1[0] = o, o += kHid * D;
+    po.b1[0] = o, o += kHid;
+    po.w2[0] = o, o += kHid * kHid;
+    po.b2[0] = o, o += kHid;
+    po.w1[1] = o, o += kHid * D;
+    po.b1[1] = o, o += kHid;
+    po.w2[1] = o, o += kHid * kHid;
+    po.b2[1] = o, o += kHid;
+    po.wv = o, o += kHid;
+    po.bv = o, o += 1;
+    if (p.head_kind == CPPRL_B200_HEAD_NORMAL)
+        po.slog = o, o += A;
+    else
+        po.slog = -1;
+    po.wo = o, o += A * kHid;
+    po.bo = o, o += A;
+    po.P = o;
+    po.Pstride = round_up(o, 4) + kNumStats;
+    return true;
+}
+
+ImageLayout make_image_layout(int Dp, int Ap)
+{
+    ImageLayout il;
+    int o = 0;
+    for (int t = 0; t < 2; ++t)
+    {
+        il.w1t[t] = o, o += Dp * kHid;
+        il.b1[t] = o, o += kHid;
+        il.w2t[t] = o, o += kHid * kHid;
+        il.w2n[t] = o, o += kHid * kHid;
+        il.b2[t] = o, o += kHid;
+    }
+    il.wo = o, o += Ap * kHid;
+    il.bo = o, o += Ap;
+    il.wv = o, o += kHid;
+    il.bv = o, o += 4;
+    il.slog = o, o += Ap;
+    il.floats = round_up(o, 4);
+    return il;
+}
+
+int validate_policy(const cpprl_b200_policy *p, const char *who)
+{
+    if (!p || !p->d_params)
+        return fail(CPPRL_B200_EINVAL, std::string(who) + ": null policy / parameter buffer");
+    if (p->base_kind == CPPRL_B200_BASE_GRU_MLP)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": recurrent (GRU) MlpBase is not implemented on the GPU path yet");
+    if (p->base_kind == CPPRL_B200_BASE_CNN)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": CnnBase is not implemented on the GPU path yet");
+    if (p->base_kind != CPPRL_B200_BASE_MLP)
+        return fail(CPPRL_B200_EINVAL, std::string(who) + ": unknown base kind");
+    if (p->head_kind != CPPRL_B200_HEAD_CATEGORICAL && p->head_kind != CPPRL_B200_HEAD_NORMAL)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": only Categorical and Normal heads are implemented (Bernoulli is out of scope)");
+    if (p->hidden != kHid)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": MlpBase hidden size must be 64 on the GPU path");
+    if (p->obs_dim < 1 || p->obs_dim > 256)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": obs_dim must be in [1, 256]");
+    if (p->num_actions < 1 || p->num_actions > kMaxActions)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": num_actions must be in [1, 16]");
+    ParamOffsets po;
+    mlp_param_offsets(*p, po);
+    if (p->n_params != po.P)
+        return fail(CPPRL_B200_EINVAL, std::string(who) + ": n_params does not match the policy layout (expected " +
+                                           std::to_string(po.P) + ", got " + std::to_string(p->n_params) + ")");
+    const bool any = p->d_norm_clip || p->d_norm_count || p->d_norm_mean || p->d_norm_var;
+    const bool all = p->d_norm_clip && p->d_norm_count && p->d_norm_mean && p->d_norm_var;
+    if (any && !all)
+        return fail(CPPRL_B200_EINVAL, std::string(who) + ": normaliser buffers must be all set or all NULL");
+    return 0;
+}
+
+// Scratch shared by every update flavour.
+struct Scratch
+{
+    float *image = nullptr;
+    size_t image_floats = 0;
+    float *gpart = nullptr;
+    size_t gpart_floats = 0;
+    unsigned int *barrier = nullptr;
+    UpdateState *state = nullptr;
+    double *adv_sums = nullptr;
+    void *rms_ws = nullptr;
+    size_t rms_ws_bytes = 0;
+
+    int ensure(size_t img, size_t gp, size_t rms)
+    {
+        if (!barrier)
+        {
+            CPPRL_CUDA_TRY(cudaMalloc(&barrier, 64));
+            CPPRL_CUDA_TRY(cudaMemset(barrier, 0, 64));
+            CPPRL_CUDA_TRY(cudaMalloc(&state, sizeof(UpdateState)));
+            CPPRL_CUDA_TRY(cudaMemset(state, 0, sizeof(UpdateState)));
+            CPPRL_CUDA_TRY(cudaMalloc(&adv_sums, 4 * sizeof(double)));
+        }
+        if (img > image_floats)
+        {
+            if (image)
+                cudaFree(image);
+            CPPRL_CUDA_TRY(cudaMalloc(&image, img * sizeof(float)));
+            image_floats = img;
+        }
+        if (gp > gpart_floats)
+        {
+            if (gpart)
+                cudaFree(gpart);
+            CPPRL_CUDA_TRY(cudaMalloc(&gpart, gp * sizeof(float)));
+            gpart_floats = gp;
+        }
+        if (rms > rms_ws_bytes)
+        {
+            if (rms_ws)
+                cudaFree(rms_ws);
+            CPPRL_CUDA_TRY(cudaMalloc(&rms_ws, rms));
+            rms_ws_bytes = rms;
+        }
+        return 0;
+    }
+    void release()
+    {
+        cudaFree(image), cudaFree(gpart), cudaFree(barrier), cudaFree(state), cudaFree(adv_sums), cudaFree(rms_ws);
+        image = gpart = nullptr;
+        barrier = nullptr;
+        state = nullptr;
+        adv_sums = nullptr;
+        rms_ws = nullptr;
+    }
+};
+
+struct Plan
+{
+    int R = 0, grid = 0;
+};
+
+// Tile rows and grid for a minibatch of B rows: the smallest tile that still gives every SM at most one
+// tile, falling back to the smaller tile when the shared-memory plan of the larger one does not fit.
+int choose_plan(int64_t B, const ImageLayout &il, const ParamOffsets &po, int Dp, int Ap, Plan &plan)
+{
+    const int sms = sm_count();
+    int R = (B <= 32ll * sms) ? 32 : 64;
+    if (R == 64 && mlp_update_smem_bytes(64, il.floats, po.Pstride, Dp, Ap) > 227 * 1024)
+        R = 32;
+    if (mlp_update_smem_bytes(R, il.floats, po.Pstride, Dp, Ap) > 227 * 1024)
+        return fail(CPPRL_B200_EUNSUPPORTED, "update: observation / action size needs more than 227 KB of shared memory");
+    const int64_t tiles = (B + R - 1) / R;
+    plan.R = R;
+    plan.grid = static_cast<int>(tiles < sms ? tiles : sms);
+    return 0;
+}
+
+void fill_policy_args(MlpUpdateArgs &a, const cpprl_b200_policy &p, const ParamOffsets &po, const ImageLayout &il,
+                      int Dp, int Ap)
+{
+    a.params = p.d_params;
+    a.po = po;
+    a.il = il;
+    a.D = static_cast<int>(p.obs_dim);
+    a.Dp = Dp;
+    a.A = static_cast<int>(p.num_actions);
+    a.Ap = Ap;
+    a.head = p.head_kind == CPPRL_B200_HEAD_NORMAL ? 1 : 0;
+    a.norm_mean = p.d_norm_mean;
+    a.norm_var = p.d_norm_var;
+    a.norm_clip = p.d_norm_clip;
+}
+
+__global__ void reset_state_kernel(UpdateState *st)
+{
+    const long long keep = st->opt_step;
+    UpdateState z = {};
+    z.opt_step = keep;
+    z.kl_stop_update = -1.f;
+    *st = z;
+}
+
+__global__ void set_opt_step_kernel(UpdateState *st, long long step) { st->opt_step = step; }
+
+__global__ void finish_entropy_kernel(float *entropy, float inv_b) { entropy[0] *= inv_b; }
+} // namespace
+} // namespace cpprl_b200
+
+using namespace cpprl_b200;
+
+// =====================================================================================================
+// PPO
+// =====================================================================================================
+struct cpprl_b200_ppo
+{
+    int64_t n_params = 0;
+    float *d_m = nullptr, *d_v = nullptr;
+    Scratch scratch;
+    // permutation staging (double buffered)
+    int64_t *d_perm[2] = {nullptr, nullptr};
+    int64_t *h_perm[2] = {nullptr, nullptr};
+    size_t perm_cap = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copied[2] = {nullptr, nullptr};   // H2D of buffer b finished
+    cudaEvent_t consumed[2] = {nullptr, nullptr}; // kernel reading buffer b finished
+    bool consumed_valid[2] = {false, false};
+    UpdateState *h_state = nullptr; // pinned
+    // per-update context
+    bool active = false;
+    cudaStream_t stream = nullptr;
+    cpprl_b200_policy policy;
+    cpprl_b200_rollout rollout;
+    cpprl_b200_ppo_options opt;
+    MlpUpdateArgs args;
+    Plan plan;
+    int64_t mbs = 0, n_mb = 0;
+    int epoch = 0;
+    int64_t host_step = 0;
+};
+
+extern "C" int cpprl_b200_ppo_create(cpprl_b200_ppo **out, int64_t n_params)
+{
+    if (!out || n_params <= 0)
+        return fail(CPPRL_B200_EINVAL, "ppo_create: bad arguments");
+    if (int rc = require_device())
+        return rc;
+    auto *h = new cpprl_b200_ppo();
+    h->n_params = n_params;
+    int rc = 0;
+    auto attempt = [&]() -> int {
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_m, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_v, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaMemset(h->d_m, 0, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaMemset(h->d_v, 0, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; ++b)
+        {
+            CPPRL_CUDA_TRY(cudaEventCreateWithFlags(&h->copied[b], cudaEventDisableTiming));
+            CPPRL_CUDA_TRY(cudaEventCreateWithFlags(&h->consumed[b], cudaEventDisableTiming));
+        }
+        CPPRL_CUDA_TRY(cudaMallocHost(&h->h_state, sizeof(UpdateState)));
+        return h->scratch.ensure(0, 0, 0);
+    };
+    rc = attempt();
+    if (rc != 0)
+    {
+        cpprl_b200_ppo_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return 0;
+}
+
+extern "C" void cpprl_b200_ppo_destroy(cpprl_b200_ppo *h)
+{
+    if (!h)
+        return;
+    cudaFree(h->d_m), cudaFree(h->d_v);
+    for (int b = 0; b < 2; ++b)
+    {
+        cudaFree(h->d_perm[b]);
+        if (h->h_perm[b])
+            cudaFreeHost(h->h_perm[b]);
+        if (h->copied[b])
+            cudaEventDestroy(h->copied[b]);
+        if (h->consumed[b])
+            cudaEventDestroy(h->consumed[b]);
+    }
+    if (h->copy_stream)
+        cudaStreamDestroy(h->copy_stream);
+    if (h->h_state)
+        cudaFreeHost(h->h_state);
+    h->scratch.release();
+    delete h;
+}
+
+extern "C" int cpprl_b200_ppo_state(cpprl_b200_ppo *h, float **d_exp_avg, float **d_exp_avg_sq, int64_t *step)
+{
+    if (!h)
+        return fail(CPPRL_B200_EINVAL, "ppo_state: null handle");
+    if (d_exp_avg)
+        *d_exp_avg = h->d_m;
+    if (d_exp_avg_sq)
+        *d_exp_avg_sq = h->d_v;
+    if (step)
+        *step = h->host_step;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_set_step(cpprl_b200_ppo *h, int64_t step)
+{
+    if (!h || step < 0)
+        return fail(CPPRL_B200_EINVAL, "ppo_set_step: bad arguments");
+    set_opt_step_kernel<<<1, 1>>>(h->scratch.state, step);
+    CPPRL_LAUNCH_CHECK("set_opt_step_kernel");
+    CPPRL_CUDA_TRY(cudaDeviceSynchronize());
+    h->host_step = step;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *ro,
+                                    const cpprl_b200_ppo_options *opt, void *stream)
+{
+    if (!h || !ro || !opt)
+        return fail(CPPRL_B200_EINVAL, "ppo_begin: null argument");
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "ppo_update"))
+        return rc;
+    if (policy->n_params != h->n_params)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: handle was created for a different parameter count");
+    if (!ro->d_observations || !ro->d_actions || !ro->d_value_preds || !ro->d_returns || !ro->d_action_log_probs)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: null rollout buffer");
+    if (ro->T <= 0 || ro->N <= 0)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: non-positive rollout size");
+    if (opt->num_epoch < 0 || opt->num_mini_batch <= 0)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: bad epoch / minibatch count");
+    const int64_t rows = ro->T * ro->N;
+    if (rows < opt->num_mini_batch)
+        return fail(CPPRL_B200_EINVAL, "PPO needs the number of processes (" + std::to_string(ro->N) +
+                                           ") * the number of steps (" + std::to_string(ro->T) + ") = " +
+                                           std::to_string(rows) +
+                                           " to be greater than or equal to the number of minibatches (" +
+                                           std::to_string(opt->num_mini_batch) + ")");
+    const int64_t mbs = rows / opt->num_mini_batch; // storage.cpp:163
+    if (rows % mbs != 0)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: T*N is not divisible by the minibatch size (the reference's view throws)");
+    const int64_t expect_cols = policy->head_kind == CPPRL_B200_HEAD_CATEGORICAL ? 1 : policy->num_actions;
+    if (ro->action_cols != expect_cols)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: rollout action_cols does not match the policy head");
+
+    h->policy = *policy;
+    h->rollout = *ro;
+    h->opt = *opt;
+    h->stream = static_cast<cudaStream_t>(stream);
+    h->mbs = mbs;
+    h->n_mb = rows / mbs;
+    h->epoch = 0;
+
+    ParamOffsets po;
+    mlp_param_offsets(*policy, po);
+    const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
+    const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
+    const ImageLayout il = make_image_layout(Dp, Ap);
+    if (int rc = choose_plan(mbs, il, po, Dp, Ap, h->plan))
+        return rc;
+    const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
+    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(h->plan.grid) * po.Pstride, rms_ws))
+        return rc;
+
+    MlpUpdateArgs &a = h->args;
+    std::memset(&a, 0, sizeof(a));
+    fill_policy_args(a, *policy, po, il, Dp, Ap);
+    a.image = h->scratch.image;
+    a.obs = ro->d_observations;
+    a.actions = ro->d_actions;
+    a.value_preds = ro->d_value_preds;
+    a.returns = ro->d_returns;
+    a.old_logp = ro->d_action_log_probs;
+    a.rows = rows;
+    a.B = static_cast<int>(mbs);
+    a.n_steps = static_cast<int>(h->n_mb);
+    a.adv_sums = h->scratch.adv_sums;
+    a.algo = kAlgoPPO;
+    a.clip_param = opt->clip_param;
+    // clamp(ratio, 1.0 - clip, 1.0 + clip): bounds formed in double, applied to a float tensor (ppo.cpp:111-113)
+    a.clip_lo = static_cast<float>(1.0 - static_cast<double>(opt->clip_param));
+    a.clip_hi = static_cast<float>(1.0 + static_cast<double>(opt->clip_param));
+    a.c_actor = opt->actor_loss_coef;
+    a.c_value = opt->value_loss_coef;
+    a.c_entropy = opt->entropy_coef;
+    a.kl_limit = static_cast<double>(opt->kl_target) * 1.5; // ppo.cpp:100
+    a.opt = kOptAdam;
+    a.opt_m = h->d_m;
+    a.opt_v = h->d_v;
+    a.lr = static_cast<double>(opt->learning_rate);
+    a.beta1 = 0.9f;
+    a.beta2 = 0.999f;
+    a.eps = opt->epsilon;
+    a.gpart = h->scratch.gpart;
+    a.barrier = h->scratch.barrier;
+    a.state = h->scratch.state;
+
+    cudaStream_t s = h->stream;
+    KernelTimer timer("update", s);
+    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
+    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+    CPPRL_LAUNCH_CHECK("reset_state_kernel");
+    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 4 * sizeof(double), s));
+    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, rows, h->scratch.adv_sums, s))
+        return rc;
+    h->active = true;
+    return 0;
+}
+
+static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
+{
+    h->args.perm = reinterpret_cast<const long long *>(d_perm);
+    KernelTimer timer("update", h->stream);
+    int rc = mlp_update_launch(h->plan.R, h->args, h->plan.grid, h->stream);
+    if (rc == 0)
+        ++h->epoch;
+    return rc;
+}
+
+extern "C" int cpprl_b200_ppo_epoch_device(cpprl_b200_ppo *h, const int64_t *d_perm, int64_t perm_len)
+{
+    if (!h || !d_perm)
+        return fail(CPPRL_B200_EINVAL, "ppo_epoch: null argument");
+    if (!h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
+    if (perm_len != h->mbs * h->n_mb)
+        return fail(CPPRL_B200_EINVAL, "ppo_epoch: permutation length must be T*N");
+    return ppo_launch_epoch(h, d_perm);
+}
+
+extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, int64_t perm_len)
+{
+    if (!h || !h_perm)
+        return fail(CPPRL_B200_EINVAL, "ppo_epoch: null argument");
+    if (!h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
+    if (perm_len != h->mbs * h->n_mb)
+        return fail(CPPRL_B200_EINVAL, "ppo_epoch: permutation length must be T*N");
+    if (static_cast<size_t>(perm_len) > h->perm_cap)
+    {
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
+        for (int b = 0; b < 2; ++b)
+        {
+            cudaFree(h->d_perm[b]);
+            if (h->h_perm[b])
+                cudaFreeHost(h->h_perm[b]);
+            h->d_perm[b] = nullptr, h->h_perm[b] = nullptr;
+            CPPRL_CUDA_TRY(cudaMalloc(&h->d_perm[b], perm_len * sizeof(int64_t)));
+            CPPRL_CUDA_TRY(cudaMallocHost(&h->h_perm[b], perm_len * sizeof(int64_t)));
+            h->consumed_valid[b] = false;
+        }
+        h->perm_cap = perm_len;
+    }
+    const int b = h->epoch & 1;
+    // the pinned buffer is free once its previous H2D finished; the device buffer once its kernel finished
+    if (h->consumed_valid[b])
+    {
+        CPPRL_CUDA_TRY(cudaEventSynchronize(h->copied[b]));
+        CPPRL_CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->consumed[b], 0));
+    }
+    std::memcpy(h->h_perm[b], h_perm, perm_len * sizeof(int64_t));
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->d_perm[b], h->h_perm[b], perm_len * sizeof(int64_t), cudaMemcpyHostToDevice,
+                                   h->copy_stream));
+    CPPRL_CUDA_TRY(cudaEventRecord(h->copied[b], h->copy_stream));
+    CPPRL_CUDA_TRY(cudaStreamWaitEvent(h->stream, h->copied[b], 0));
+    int rc = ppo_launch_epoch(h, h->d_perm[b]);
+    if (rc != 0)
+        return rc;
+    CPPRL_CUDA_TRY(cudaEventRecord(h->consumed[b], h->stream));
+    h->consumed_valid[b] = true;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_stopped(cpprl_b200_ppo *h, int *stopped)
+{
+    if (!h || !stopped)
+        return fail(CPPRL_B200_EINVAL, "ppo_stopped: null argument");
+    if (!h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_stopped called without ppo_begin");
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, h->stream));
+    CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    *stopped = h->h_state->stopped;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_end_async(cpprl_b200_ppo *h)
+{
+    if (!h)
+        return fail(CPPRL_B200_EINVAL, "ppo_end: null handle");
+    if (!h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_end called without ppo_begin");
+    const cpprl_b200_policy &p = h->policy;
+    if (p.d_norm_mean)
+    {
+        // finish_update: the normaliser sees ALL (T+1)*N observation rows (ppo.cpp:149-154)
+        const int64_t M = (h->rollout.T + 1) * h->rollout.N;
+        if (int rc = cpprl_b200_rms_update(h->rollout.d_observations, M, p.obs_dim, p.d_norm_count, p.d_norm_mean,
+                                           p.d_norm_var, h->scratch.rms_ws, h->stream))
+            return rc;
+    }
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, h->stream));
+    h->active = false;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_fetch_stats(cpprl_b200_ppo *h, cpprl_b200_ppo_stats *stats)
+{
+    if (!h || !stats)
+        return fail(CPPRL_B200_EINVAL, "ppo_fetch_stats: null argument");
+    CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    const UpdateState &st = *h->h_state;
+    const float n = static_cast<float>(st.num_updates);
+    // means over the applied updates; 0/0 = NaN when the first minibatch tripped the KL stop (ppo.cpp:156-159)
+    stats->value_loss = st.total_value_loss / n;
+    stats->action_loss = st.total_action_loss / n;
+    stats->entropy = st.total_entropy / n;
+    stats->clip_fraction = st.total_clip_fraction / n;
+    stats->kl_divergence = st.last_kl;
+    stats->kl_early_stop_update = st.stopped ? st.kl_stop_update : -1.f;
+    stats->num_updates = st.num_updates;
+    h->host_step = st.opt_step;
+    return 0;
+}
+
+extern "C" int cpprl_b200_ppo_end(cpprl_b200_ppo *h, cpprl_b200_ppo_stats *stats)
+{
+    if (int rc = cpprl_b200_ppo_end_async(h))
+        return rc;
+    return cpprl_b200_ppo_fetch_stats(h, stats);
+}
+
+extern "C" int cpprl_b200_ppo_update(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                                     const cpprl_b200_ppo_options *opt, const int64_t *h_perms, int64_t perm_len,
+                                     cpprl_b200_ppo_stats *stats, void *stream)
+{
+    if (!h_perms || !stats)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: null argument");
+    if (int rc = cpprl_b200_ppo_begin(h, policy, rollout, opt, stream))
+        return rc;
+    for (int e = 0; e < opt->num_epoch; ++e)
+        if (int rc = cpprl_b200_ppo_epoch(h, h_perms + static_cast<int64_t>(e) * perm_len, perm_len))
+        {
+            h->active = false;
+            return rc;
+        }
+    return cpprl_b200_ppo_end(h, stats);
+}
+
+// =====================================================================================================
+// A2C
+// =====================================================================================================
+struct cpprl_b200_a2c
+{
+    int64_t n_params = 0;
+    float *d_sq = nullptr;
+    Scratch scratch;
+    UpdateState *h_state = nullptr;
+    cudaStream_t stream = nullptr;
+};
+
+extern "C" int cpprl_b200_a2c_create(cpprl_b200_a2c **out, int64_t n_params)
+{
+    if (!out || n_params <= 0)
+        return fail(CPPRL_B200_EINVAL, "a2c_create: bad arguments");
+    if (int rc = require_device())
+        return rc;
+    auto *h = new cpprl_b200_a2c();
+    h->n_params = n_params;
+    auto attempt = [&]() -> int {
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_sq, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaMemset(h->d_sq, 0, n_params * sizeof(float)));
+        CPPRL_CUDA_TRY(cudaMallocHost(&h->h_state, sizeof(UpdateState)));
+        return h->scratch.ensure(0, 0, 0);
+    };
+    int rc = attempt();
+    if (rc != 0)
+    {
+        cpprl_b200_a2c_destroy(h);
+        return rc;
+    }
+    *out = h;
+    return 0;
+}
+
+extern "C" void cpprl_b200_a2c_destroy(cpprl_b200_a2c *h)
+{
+    if (!h)
+        return;
+    cudaFree(h->d_sq);
+    if (h->h_state)
+        cudaFreeHost(h->h_state);
+    h->scratch.release();
+    delete h;
+}
+
+extern "C" int cpprl_b200_a2c_state(cpprl_b200_a2c *h, float **d_square_avg)
+{
+    if (!h || !d_square_avg)
+        return fail(CPPRL_B200_EINVAL, "a2c_state: null argument");
+    *d_square_avg = h->d_sq;
+    return 0;
+}
+
+extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_policy *policy,
+                                           const cpprl_b200_rollout *ro, const cpprl_b200_a2c_options *opt, void *stream)
+{
+    if (!h || !ro || !opt)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: null argument");
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "a2c_update"))
+        return rc;
+    if (policy->n_params != h->n_params)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: handle was created for a different parameter count");
+    if (!ro->d_observations || !ro->d_actions || !ro->d_returns)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: null rollout buffer");
+    if (ro->T <= 0 || ro->N <= 0)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: non-positive rollout size");
+    const int64_t rows = ro->T * ro->N;
+    if (rows > 0x7fffffffll)
+        return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: more than 2^31 rows");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    h->stream = s;
+
+    ParamOffsets po;
+    mlp_param_offsets(*policy, po);
+    const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
+    const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
+    const ImageLayout il = make_image_layout(Dp, Ap);
+    Plan plan;
+    if (int rc = choose_plan(rows, il, po, Dp, Ap, plan))
+        return rc;
+    const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
+    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(plan.grid) * po.Pstride, rms_ws))
+        return rc;
+
+    KernelTimer timer("update", s);
+    if (policy->d_norm_mean)
+    {
+        // the normaliser is updated BEFORE the forward pass (a2c.cpp:52-55)
+        if (int rc = cpprl_b200_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
+                                           policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, s))
+            return rc;
+    }
+    MlpUpdateArgs a;
+    std::memset(&a, 0, sizeof(a));
+    fill_policy_args(a, *policy, po, il, Dp, Ap);
+    a.image = h->scratch.image;
+    a.obs = ro->d_observations;
+    a.actions = ro->d_actions;
+    a.value_preds = ro->d_value_preds;
+    a.returns = ro->d_returns;
+    a.old_logp = ro->d_action_log_probs ? ro->d_action_log_probs : ro->d_returns;
+    a.rows = rows;
+    a.perm = nullptr;
+    a.B = static_cast<int>(rows);
+    a.n_steps = 1;
+    a.adv_sums = nullptr;
+    a.algo = kAlgoA2C;
+    a.c_actor = 1.f;
+    a.c_value = opt->value_loss_coef;
+    a.c_entropy = opt->entropy_coef;
+    a.opt = kOptRmsprop;
+    a.opt_m = nullptr;
+    a.opt_v = h->d_sq;
+    a.lr = static_cast<double>(opt->learning_rate);
+    a.alpha = opt->alpha;
+    a.eps = opt->epsilon;
+    a.gpart = h->scratch.gpart;
+    a.barrier = h->scratch.barrier;
+    a.state = h->scratch.state;
+    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
+    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+    CPPRL_LAUNCH_CHECK("reset_state_kernel");
+    if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
+        return rc;
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, s));
+    return 0;
+}
+
+extern "C" int cpprl_b200_a2c_fetch_stats(cpprl_b200_a2c *h, cpprl_b200_a2c_stats *stats)
+{
+    if (!h || !stats)
+        return fail(CPPRL_B200_EINVAL, "a2c_fetch_stats: null argument");
+    CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    stats->value_loss = h->h_state->a2c_value_loss;
+    stats->action_loss = h->h_state->a2c_action_loss;
+    stats->entropy = h->h_state->a2c_entropy;
+    return 0;
+}
+
+extern "C" int cpprl_b200_a2c_update(cpprl_b200_a2c *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                                     const cpprl_b200_a2c_options *opt, cpprl_b200_a2c_stats *stats, void *stream)
+{
+    if (!stats)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: null stats");
+    if (int rc = cpprl_b200_a2c_update_async(h, policy, rollout, opt, stream))
+        return rc;
+    return cpprl_b200_a2c_fetch_stats(h, stats);
+}
+
+// =====================================================================================================
+// forward evaluation
+// =====================================================================================================
+static std::mutex g_eval_mu;
+static Scratch g_eval_scratch;
+
+extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
+{
+    if (!policy)
+        return 0;
+    ParamOffsets po;
+    if (!mlp_param_offsets(*policy, po))
+        return 0;
+    return po.P;
+}
+
+extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float * /*d_hxs*/,
+                                           int64_t /*n_hxs*/, const float * /*d_masks*/, const void *d_actions, int64_t B,
+                                           float *d_value, float *d_logp, float *d_entropy, float * /*d_hxs_out*/,
+                                           void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "evaluate_actions"))
+        return rc;
+    if (!d_obs || !d_actions || !d_value || !d_logp || !d_entropy)
+        return fail(CPPRL_B200_EINVAL, "evaluate_actions: null pointer");
+    if (B <= 0 || B > 0x7fffffffll)
+        return fail(CPPRL_B200_EINVAL, "evaluate_actions: bad batch size");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    std::lock_guard<std::mutex> lock(g_eval_mu);
+
+    ParamOffsets po;
+    mlp_param_offsets(*policy, po);
+    const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
+    const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
+    const ImageLayout il = make_image_layout(Dp, Ap);
+    Plan plan;
+    if (int rc = choose_plan(B, il, po, Dp, Ap, plan))
+        return rc;
+    if (int rc = g_eval_scratch.ensure(il.floats, 0, 0))
+        return rc;
+    MlpUpdateArgs a;
+    std::memset(&a, 0, sizeof(a));
+    fill_policy_args(a, *policy, po, il, Dp, Ap);
+    a.image = g_eval_scratch.image;
+    a.obs = d_obs;
+    a.actions = d_actions;
+    a.rows = B;
+    a.B = static_cast<int>(B);
+    a.n_steps = 1;
+    a.algo = kAlgoForward;
+    a.barrier = g_eval_scratch.barrier;
+    a.out_value = d_value;
+    a.out_logp = d_logp;
+    a.out_entropy_sum = d_entropy;
+    CPPRL_CUDA_TRY(cudaMemsetAsync(g_eval_scratch.image, 0, il.floats * sizeof(float), s));
+    CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
+    if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
+        return rc;
+    finish_entropy_kernel<<<1, 1, 0, s>>>(d_entropy, 1.f / static_cast<float>(B)); // entropy().mean() (policy.cpp:109)
+    CPPRL_LAUNCH_CHECK("finish_entropy_kernel");
+    return 0;
+}

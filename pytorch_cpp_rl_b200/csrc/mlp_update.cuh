@@ -1,0 +1,92 @@
+// mlp_update.cuh — argument block shared by the fused MLP update kernel and its host launcher.
+#pragma once
+#include <stdint.h>
+
+namespace cpprl_b200
+{
+constexpr int kHid = 64;           // MlpBase hidden size this kernel is specialised for
+constexpr int kUpdThreads = 256;   // 8 warps: warps 0-3 run the actor tower, 4-7 the critic tower
+constexpr int kNumStats = 8;       // slots appended to the gradient vector (5 used)
+constexpr int kMaxActions = 16;
+
+enum { kAlgoPPO = 0, kAlgoA2C = 1, kAlgoForward = 2 };
+enum { kOptAdam = 0, kOptRmsprop = 1 };
+
+// Offsets (in floats) of each tensor inside the flat parameter buffer (reference registration order).
+struct ParamOffsets
+{
+    int w1[2], b1[2], w2[2], b2[2]; // [0] actor, [1] critic
+    int wv, bv;                     // critic_linear
+    int slog;                       // Normal scale_log (-1 for Categorical)
+    int wo, bo;                     // head linear
+    int P;                          // total parameter count
+    int Pstride;                    // P rounded up to 4, + kNumStats
+};
+
+// Offsets (in floats) inside the shared-memory weight image (also kept as a global scratch copy).
+struct ImageLayout
+{
+    int w1t[2]; // [Dp][64]  contraction-major, output index permuted
+    int b1[2];  // [64] permuted
+    int w2t[2]; // [64][64]  [k][perm(j)]   forward
+    int w2n[2]; // [64][64]  [j][perm(k)]   backward (dH1)
+    int b2[2];  // [64] permuted
+    int wo;     // [Ap][64]
+    int bo;     // [Ap]
+    int wv;     // [64]
+    int bv;     // [4]
+    int slog;   // [Ap]
+    int floats; // total, multiple of 4
+};
+
+// Device-resident running state of one update (reset by begin, read back by end).
+struct UpdateState
+{
+    int stopped;          // KL early stop triggered (ppo.cpp:100-104)
+    int num_updates;      // optimizer steps applied in this update
+    float total_value_loss, total_action_loss, total_entropy, total_clip_fraction;
+    float last_kl;
+    float kl_stop_update; // num_updates at the stop, -1 otherwise
+    long long opt_step;   // Adam step count (persists across updates)
+    float a2c_value_loss, a2c_action_loss, a2c_entropy;
+    int pad;
+};
+
+struct MlpUpdateArgs
+{
+    // policy
+    float *params;        // flat parameters (updated in place)
+    float *image;         // global copy of the shared-memory weight image
+    ParamOffsets po;
+    ImageLayout il;
+    int D, Dp, A, Ap;     // obs dim, padded to 8; actions, padded to 4
+    int head;             // 0 categorical, 1 normal
+    const float *norm_mean, *norm_var, *norm_clip; // nullable (no observation normaliser)
+    // rollout (row id = t*N + env)
+    const float *obs;     // [rows(+N), D]
+    const void *actions;  // int64 [rows] or fp32 [rows, A]
+    const float *value_preds, *returns, *old_logp;
+    long long rows;       // T*N
+    // minibatches
+    const long long *perm; // row ids for this launch, nullable = identity
+    int B;                // rows per minibatch
+    int n_steps;          // minibatches in this launch
+    const double *adv_sums; // {sum, sumsq} of raw advantages over all rows (PPO), nullable
+    // loss
+    int algo;
+    float clip_param, clip_lo, clip_hi;
+    float c_actor, c_value, c_entropy;
+    double kl_limit;      // 1.5 * kl_target
+    // optimiser
+    int opt;
+    float *opt_m, *opt_v; // Adam exp_avg / exp_avg_sq, RMSprop square_avg in opt_v
+    double lr;
+    float beta1, beta2, eps, alpha;
+    // scratch / state
+    float *gpart;         // [grid][Pstride] per-CTA gradient partials
+    unsigned int *barrier;
+    UpdateState *state;
+    // forward-only outputs (kAlgoForward)
+    float *out_value, *out_logp, *out_entropy_sum;
+};
+} // namespace cpprl_b200

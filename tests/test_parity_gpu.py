@@ -1,0 +1,331 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the compiled reference (oracle/_ref).
+
+Tolerances are BASELINE.json's: indices and gathers bit-exact; returns/advantages 1e-5 relative;
+losses and post-update parameters 1e-4 relative (parameters with a max(|ref|, lr) floor).
+"""
+import numpy as np
+import pytest
+import torch
+
+from pytorch_cpp_rl_b200 import api, cabi
+from pytorch_cpp_rl_b200.workloads import CONFIGS, synth_rollout
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+def test_library_runs_on_sm100():
+    lib = cabi.load()
+    import ctypes as C
+    sms, major, minor = C.c_int(), C.c_int(), C.c_int()
+    name = C.create_string_buffer(128)
+    cabi.check(lib.cpprl_b200_device_info(C.byref(sms), C.byref(major), C.byref(minor), name, 128))
+    assert major.value == 10 and sms.value > 0
+
+
+# ---- (a) returns -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_compute_returns_known_answer(use_gae):
+    """The reference's own golden vectors, src/storage.cpp:341-437 (3 steps x 2 envs, gamma = tau = 0.6)."""
+    space = api.ActionSpace("Discrete", [3])
+    st = api.RolloutStorage(3, 2, [4], space, 5)
+    value_preds = [[0, 1], [1, 2], [2, 3]]
+    rewards = [[0, 1], [1, 2], [2, 3]]
+    masks = [[1, 1], [1, 0], [1, 1]]
+    for t in range(3):  # insert() semantics: values/rewards at t, mask at t+1
+        st.value_predictions[t, :, 0] = torch.tensor(value_preds[t], dtype=torch.float32)
+        st.rewards[t, :, 0] = torch.tensor(rewards[t], dtype=torch.float32)
+        st.masks[t + 1, :, 0] = torch.tensor(masks[t], dtype=torch.float32)
+    next_value = torch.tensor([[0.0], [1.0]], device="cuda")
+    st.compute_returns(next_value, use_gae, 0.6, 0.6)
+    got = st.returns[..., 0].cpu().numpy()
+    if use_gae:
+        want = [[1.032, 2.2], [2.2, 2.0], [2.0, 3.6], [0.0, 0.0]]
+    else:
+        want = [[1.32, 2.2], [2.2, 2.0], [2.0, 3.6], [0.0, 1.0]]
+    np.testing.assert_allclose(got, np.array(want, np.float32), rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("T,N", [(128, 8), (5, 4096), (256, 1024), (128, 512), (7, 3), (1, 1), (33, 130)])
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_compute_returns_vs_reference(ref, T, N, use_gae):
+    w = CONFIGS["cfg1"].scaled(T=T, N=N, normalize_obs=False, storage_hidden=1)
+    for seed in (0, 1):
+        r = synth_rollout(w, seed)
+        r["value_predictions"][:T] = np.random.default_rng(seed + 7).standard_normal((T, N, 1)).astype(np.float32)
+        sess = H.make_ref_session(ref, w)
+        H.ref_load_rollout(sess, r)
+        sess.compute_returns(r["next_value"], use_gae, 0.99, 0.95)
+        want, want_v = sess.get_returns(), sess.get_value_predictions()
+        _, st = H.make_gpu_side(w, r, sess.get_params())
+        st.compute_returns(torch.from_numpy(r["next_value"]).cuda(), use_gae, 0.99, 0.95)
+        got, got_v = st.returns.cpu().numpy(), st.value_predictions.cpu().numpy()
+        # same operator order, no FMA contraction: bit-identical to the CPU libtorch path
+        assert np.array_equal(got, want)
+        assert np.array_equal(got_v, want_v)
+
+
+def test_compute_returns_linearity_full_size():
+    """Size-independent property at a bandwidth-sweep size: returns are linear in (rewards, values, next_value)."""
+    T, N = 256, 1 << 16
+    g = torch.Generator(device="cuda").manual_seed(0)
+    space = api.ActionSpace("Discrete", [4])
+    def run(scale):
+        st = api.RolloutStorage(T, N, [1], space, 1)
+        gg = torch.Generator(device="cuda").manual_seed(1)
+        st.rewards.copy_(torch.randn(T, N, 1, device="cuda", generator=gg) * scale)
+        st.value_predictions.copy_(torch.randn(T + 1, N, 1, device="cuda", generator=gg) * scale)
+        st.masks.copy_((torch.rand(T + 1, N, 1, device="cuda", generator=gg) < 0.98).float())
+        nv = torch.randn(N, 1, device="cuda", generator=gg) * scale
+        st.compute_returns(nv, True, 0.99, 0.95)
+        return st.returns[:T].clone()
+    a, b = run(1.0), run(2.0)  # scaling by a power of two is exact in fp32
+    assert torch.equal(a * 2.0, b)
+
+
+# ---- advantages ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,N", [(128, 8), (256, 1024), (5, 7)])
+def test_advantages_vs_torch(T, N):
+    rng = np.random.default_rng(3)
+    ret = rng.standard_normal((T + 1, N, 1)).astype(np.float32) * 3 + 1
+    val = rng.standard_normal((T + 1, N, 1)).astype(np.float32)
+    adv, moments = api.advantages(torch.from_numpy(ret).cuda(), torch.from_numpy(val).cuda(), True)
+    a = torch.from_numpy(ret[:-1] - val[:-1])
+    want = (a - a.mean()) / (a.std() + 1e-5)  # the reference's expression, ppo.cpp:51-57, on CPU libtorch
+    np.testing.assert_allclose(adv.cpu().numpy(), want.numpy(), rtol=1e-5, atol=2e-6)
+    raw, _ = api.advantages(torch.from_numpy(ret).cuda(), torch.from_numpy(val).cuda(), False)
+    assert np.array_equal(raw.cpu().numpy(), a.numpy())
+
+
+# ---- (b) gather --------------------------------------------------------------------------------------------
+def test_generator_minibatches_bit_exact(ref):
+    w = CONFIGS["cfg1"]
+    r = synth_rollout(w, 0)
+    sess = H.make_ref_session(ref, w)
+    H.fill_policy_outputs(sess, w, r)
+    r["returns"][:] = np.random.default_rng(5).standard_normal(r["returns"].shape).astype(np.float32)
+    H.ref_load_rollout(sess, r)
+    adv = np.random.default_rng(6).standard_normal((w.T, w.N, 1)).astype(np.float32)
+    want, n_mb, mbs = sess.generate_minibatches(adv, w.num_mini_batch, perm_seed=1234)
+    perm = H.draw_perms(1234, w.rows, 1)[0]
+    _, st = H.make_gpu_side(w, r, sess.get_params())
+    got = st.feed_forward_generator(torch.from_numpy(adv).cuda(), w.num_mini_batch, perm)
+    assert len(got) == n_mb and got[0]["advantages"].shape[0] == mbs
+    for k in range(n_mb):
+        for name in want:
+            g = got[k][name].cpu().numpy().reshape(mbs, -1)
+            assert np.array_equal(g, want[name][k * mbs:(k + 1) * mbs].reshape(mbs, -1)), (k, name)
+
+
+@pytest.mark.parametrize("cols,dtype", [(1, torch.float32), (17, torch.float32), (64, torch.float32), (1, torch.int64),
+                                        (28224, torch.float32)])
+def test_gather_rows_matches_index(cols, dtype):
+    rows = 1000 if cols < 1000 else 64
+    src = (torch.arange(rows * cols, device="cuda") % 9973).to(dtype).view(rows, cols)
+    idx = torch.randperm(rows, device="cuda")[: rows // 2]
+    assert torch.equal(api.gather_rows(src, idx), src[idx])
+    assert api.gather_rows(src, idx[:0]).shape == (0, cols)
+
+
+# ---- (e) observation normaliser ------------------------------------------------------------------------------
+def test_observation_normalizer_known_answer():
+    """src/observation_normalizer.cpp:108-129: three single-row updates, then normalise the third row."""
+    n = api.ObservationNormalizer(5)
+    rows = [[-10., 0., 5., 3.2, 0.], [-5., 2., 4., 3.7, -3.], [1, 2, 3, 4, 5]]
+    for row in rows:
+        n.update(torch.tensor(row, device="cuda"))
+    got = n.process_observation(torch.tensor(rows[2], device="cuda")).cpu().numpy()
+    want = [1.26008659, 0.70712887, -1.2240818, 1.10914509, 1.31322402]
+    np.testing.assert_allclose(got, want, rtol=1e-5)
+
+
+def test_observation_normalizer_clips_known_answer():
+    """src/observation_normalizer.cpp:95-106."""
+    n = api.ObservationNormalizer(7, clip=1.0)
+    out = n.process_observation(torch.tensor([-1000., -100, -10, 0, 10, 100, 1000], device="cuda"))
+    assert float(out.max()) <= 1.0 and float(out.min()) >= -1.0
+
+
+@pytest.mark.parametrize("M,D", [(1032, 8), (24576, 8), (263168, 17), (10, 3), (1, 5)])
+def test_rms_update_vs_reference(ref, M, D):
+    rng = np.random.default_rng(M + D)
+    x = (rng.standard_normal((M, D)) * 2.5 + 0.7).astype(np.float32)
+    y = rng.standard_normal((64, D)).astype(np.float32) * 4
+    count0, mean0, var0 = np.array([1e-4], np.float32), np.zeros(D, np.float32), np.ones(D, np.float32)
+    n = api.ObservationNormalizer(D)
+    c, m, v = count0, mean0, var0
+    for it in range(3):  # three consecutive merges exercise the Chan update with a non-trivial prior
+        xi = x * (it + 1)
+        c, m, v, want_y = ref.obs_normalizer(D, 10.0, c, m, v, x=xi, y=y)
+        n.update(torch.from_numpy(xi).cuda())
+        got_y = n.process_observation(torch.from_numpy(y).cuda()).cpu().numpy()
+        np.testing.assert_allclose(n.rms.count.cpu().numpy(), c, rtol=1e-6)
+        np.testing.assert_allclose(n.rms.mean.cpu().numpy(), m, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(n.rms.variance.cpu().numpy(), v, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(got_y, want_y, rtol=1e-5, atol=1e-5)
+
+
+def test_normalize_clamps(ref):
+    D = 4
+    y = np.array([[1000, -1000, 0.5, 3]], np.float32)
+    _, _, _, want = ref.obs_normalizer(D, 2.0, [1e-4], np.zeros(D), np.ones(D), y=y)
+    n = api.ObservationNormalizer(D, clip=2.0)
+    got = n.process_observation(torch.from_numpy(y).cuda()).cpu().numpy()
+    assert np.array_equal(got, want)
+
+
+# ---- (d) optimisers -----------------------------------------------------------------------------------------------
+def test_adam_and_rmsprop_vs_torch_optim():
+    torch.manual_seed(0)
+    n = 10007
+    p0 = torch.randn(n)
+    grads = [torch.randn(n) * (10.0 ** -k) for k in range(4)]
+    # libtorch CPU optimisers (what the reference constructs at ppo.cpp:39-42 / a2c.cpp:30-34)
+    p_ref = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([p_ref], lr=3e-4, eps=1e-5)
+    p = p0.clone().cuda()
+    m, v = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    for step, g in enumerate(grads, 1):
+        p_ref.grad = g.clone()
+        opt.step()
+        api.adam_step(p, g.cuda(), m, v, step, 3e-4, eps=1e-5)
+        np.testing.assert_allclose(p.cpu().numpy(), p_ref.detach().numpy(), rtol=1e-6, atol=1e-7)
+    p_ref = p0.clone().requires_grad_(True)
+    opt = torch.optim.RMSprop([p_ref], lr=7e-4, eps=1e-5, alpha=0.99)
+    p = p0.clone().cuda()
+    s = torch.zeros(n, device="cuda")
+    for g in grads:
+        p_ref.grad = g.clone()
+        opt.step()
+        api.rmsprop_step(p, g.cuda(), s, 7e-4, alpha=0.99, eps=1e-5)
+        np.testing.assert_allclose(p.cpu().numpy(), p_ref.detach().numpy(), rtol=1e-6, atol=1e-7)
+
+
+# ---- (c) forward ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg,B", [("cfg1", 256), ("cfg1", 37), ("cfg3", 8192), ("cfg3", 100), ("cfg2", 20480)])
+def test_evaluate_actions_vs_reference(ref, cfg, B):
+    w = CONFIGS[cfg]
+    sess = H.make_ref_session(ref, w, init_seed=3)
+    rng = np.random.default_rng(11)
+    obs = rng.standard_normal((B, w.obs_dim)).astype(np.float32) * 2
+    if w.head == "categorical":
+        actions = rng.integers(0, w.num_actions, (B, 1))
+    else:
+        actions = rng.standard_normal((B, w.num_actions)).astype(np.float32)
+    params = sess.get_params() + (rng.standard_normal(sess.n_params) * 0.05).astype(np.float32)
+    sess.set_params(params)
+    if w.normalize_obs:
+        sess.set_normalizer([100.0], rng.standard_normal(w.obs_dim) * 0.3, rng.random(w.obs_dim) + 0.5)
+    v, lp, ent = sess.evaluate_actions(obs, np.zeros((B, 1), np.float32), np.ones((B, 1), np.float32), actions)
+    r = synth_rollout(w.scaled(T=1, N=1), 0)
+    policy, _ = H.make_gpu_side(w.scaled(T=1, N=1), r, params, sess.get_normalizer() if w.normalize_obs else None)
+    dact = torch.from_numpy(np.ascontiguousarray(actions)).cuda()
+    if w.head != "categorical":
+        dact = dact.float()
+    out = policy.evaluate_actions(torch.from_numpy(obs).cuda(), None, None, dact)
+    np.testing.assert_allclose(out[0].cpu().numpy(), v, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(out[1].cpu().numpy(), lp, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(float(out[2]), ent, rtol=1e-5)
+
+
+# ---- (c)+(d) whole updates --------------------------------------------------------------------------------------------
+def _run_ppo_case(ref, w, seed, n_updates=2, perturb=0.0):
+    r = synth_rollout(w, seed)
+    sess = H.make_ref_session(ref, w, init_seed=seed)
+    if perturb:
+        rng = np.random.default_rng(seed + 99)
+        sess.set_params(sess.get_params() + (rng.standard_normal(sess.n_params) * perturb).astype(np.float32))
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    params0 = sess.get_params()
+    policy, st = H.make_gpu_side(w, r, params0, sess.get_normalizer() if w.normalize_obs else None)
+    algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef,
+                   w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    for upd in range(n_updates):
+        sess.compute_returns(r["next_value"], w.use_gae, w.gamma, w.tau)
+        want_stats, _ = sess.update(1.0, perm_seed=1000 + seed + upd)
+        st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        perms = H.draw_perms(1000 + seed + upd, w.rows, w.num_epoch)
+        got = algo.update(st, 1.0, perms=perms)
+        got_stats = np.array([d.value for d in got], np.float32)
+        assert len(got_stats) == len(want_stats), (got_stats, want_stats)
+        # Value loss, Action loss, Clip fraction, Entropy, KL divergence [, early-stop index]
+        np.testing.assert_allclose(got_stats[0], want_stats[0], rtol=1e-4)
+        np.testing.assert_allclose(got_stats[1], want_stats[1], rtol=1e-4, atol=2e-6)
+        np.testing.assert_allclose(got_stats[2], want_stats[2], rtol=1e-4, atol=1.0 / w.rows)
+        np.testing.assert_allclose(got_stats[3], want_stats[3], rtol=1e-4)
+        np.testing.assert_allclose(got_stats[4], want_stats[4], rtol=1e-3, atol=2e-6)
+        if len(want_stats) > 5:
+            assert got_stats[5] == want_stats[5]
+        want_p = sess.get_params()
+        got_p = policy.params.cpu().numpy()
+        err = np.abs(got_p - want_p) / np.maximum(np.abs(want_p), w.learning_rate)
+        assert err.max() <= 1e-4 * max(1, w.optimizer_steps) ** 0.5 + 1e-4, (upd, err.max(), np.argmax(err))
+        if w.normalize_obs:
+            _, c, m, v = sess.get_normalizer()
+            n = policy.observation_normalizer
+            np.testing.assert_allclose(n.rms.count.cpu().numpy(), c, rtol=1e-6)
+            np.testing.assert_allclose(n.rms.mean.cpu().numpy(), m, rtol=1e-5, atol=1e-6)
+            np.testing.assert_allclose(n.rms.variance.cpu().numpy(), v, rtol=1e-5, atol=1e-6)
+    return policy, sess
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_ppo_update_cfg1(ref, seed):
+    _run_ppo_case(ref, CONFIGS["cfg1"], seed)
+
+
+def test_ppo_update_cfg1_kl_early_stop(ref):
+    # a perturbed policy against stale log-probs with the default kl_target trips the stop (ppo.cpp:100-104)
+    w = CONFIGS["cfg1"].scaled(kl_target=0.01, learning_rate=3e-2)
+    _run_ppo_case(ref, w, 5, n_updates=3)
+
+
+def test_ppo_update_cfg3_reduced(ref):
+    # cfg3's model and hyper-parameters on a rollout the CPU oracle finishes in seconds
+    w = CONFIGS["cfg3"].scaled(T=32, N=64, num_epoch=3, num_mini_batch=4)
+    _run_ppo_case(ref, w, 0)
+    w = CONFIGS["cfg3"].scaled(T=16, N=640, num_epoch=2, num_mini_batch=2)  # 5120-row minibatches -> 64-row tiles
+    _run_ppo_case(ref, w, 1, n_updates=1)
+
+
+def test_ppo_update_cfg3_full(ref):
+    w = CONFIGS["cfg3"]
+    _run_ppo_case(ref, w, 0, n_updates=1)
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_a2c_update_cfg2(ref, seed):
+    w = CONFIGS["cfg2"]
+    r = synth_rollout(w, seed)
+    sess = H.make_ref_session(ref, w, init_seed=seed)
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    policy, st = H.make_gpu_side(w, r, sess.get_params(), sess.get_normalizer())
+    algo = api.A2C(policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    for upd in range(3):
+        sess.compute_returns(r["next_value"], w.use_gae, w.gamma, w.tau)
+        want_stats, _ = sess.update(1.0)
+        st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        got = np.array([d.value for d in algo.update(st, 1.0)], np.float32)
+        np.testing.assert_allclose(got, want_stats, rtol=1e-4, atol=2e-6)
+        want_p, got_p = sess.get_params(), policy.params.cpu().numpy()
+        err = np.abs(got_p - want_p) / np.maximum(np.abs(want_p), w.learning_rate)
+        assert err.max() <= 2e-4, (upd, err.max())
+        _, c, m, v = sess.get_normalizer()
+        n = policy.observation_normalizer
+        np.testing.assert_allclose(n.rms.mean.cpu().numpy(), m, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(n.rms.variance.cpu().numpy(), v, rtol=1e-5, atol=1e-6)
+
+
+def test_unsupported_configs_fail_loudly():
+    space = api.ActionSpace("Discrete", [4])
+    policy = api.Policy(space, 8, recurrent=True)
+    st = api.RolloutStorage(4, 4, [8], space, 64)
+    with pytest.raises(cabi.CpprlB200Error) as e:
+        api.PPO(policy, 0.2, 1, 4, 1, 0.5, 0.01, 3e-4).update(st)
+    assert e.value.code == cabi.EUNSUPPORTED
+    with pytest.raises(RuntimeError):
+        api.gather_rows(torch.zeros(4, 4), torch.zeros(2, dtype=torch.int64))  # CPU tensors: no fallback
