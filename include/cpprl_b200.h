@@ -268,6 +268,10 @@ int cpprl_b200_kernel_time_ms(const char *family, double *total_ms, int64_t *lau
 void cpprl_b200_kernel_time_reset(void);
 void cpprl_b200_kernel_time_enable(int on);
 
+/* Profiling hook: when d_buffer (device, grid*32 int64) is non-NULL, thread 0 of every CTA of the fused PPO
+ * update kernel stores clock64() at its phase boundaries during minibatch `step` of each launch. */
+void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step);
+
 #ifdef __cplusplus
 }
 #endif

@@ -102,6 +102,7 @@ SIGNATURES = {
     "cpprl_b200_kernel_time_ms": (C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cpprl_b200_kernel_time_reset": (None, []),
     "cpprl_b200_kernel_time_enable": (None, [C.c_int]),
+    "cpprl_b200_debug_phase_clocks": (None, [C.c_void_p, C.c_int]),
 }
 
 _lib = None

@@ -404,7 +404,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     a.state = h->scratch.state;
 
     cudaStream_t s = h->stream;
-    KernelTimer timer("update", s);
+    KernelTimer timer("prologue", s);
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
     reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
     CPPRL_LAUNCH_CHECK("reset_state_kernel");
@@ -415,9 +415,19 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     return 0;
 }
 
+static long long *g_dbg_clocks = nullptr;
+static int g_dbg_step = 0;
+extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
+{
+    g_dbg_clocks = d_buffer;
+    g_dbg_step = step;
+}
+
 static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
     h->args.perm = reinterpret_cast<const long long *>(d_perm);
+    h->args.dbg_clocks = g_dbg_clocks;
+    h->args.dbg_step = g_dbg_step;
     KernelTimer timer("update", h->stream);
     int rc = mlp_update_launch(h->plan.R, h->args, h->plan.grid, h->stream);
     if (rc == 0)

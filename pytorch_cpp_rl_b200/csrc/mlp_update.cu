@@ -42,10 +42,13 @@ struct Tile
     static_assert(R == 32 || R == 64, "tile rows");
 };
 
+constexpr int kRedSplit = 8;   // warps splitting the partials of one parameter in phase 2
+constexpr int kRedChunk = 128; // parameters reduced per pass by one CTA
+
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct SmemPlan
 {
-    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, misc, total;
+    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, red, misc, total;
 };
 
 __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap)
@@ -69,6 +72,8 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.adv = o, o += LD;
     p.act = o, o += Ap * LD;
     p.rowid = o, o += 2 * LD; // long long per row
+    p.stat = o, o += (5 + Ap) * LD; // per-row loss terms and scale_log gradients, reduced at the start of P5
+    p.red = o, o += kRedSplit * kRedChunk; // phase-2 reduction scratch
     p.misc = o, o += 32;
     p.total = o;
     return p;
@@ -260,6 +265,41 @@ __device__ __forceinline__ float block_bcast_sum_stats(const float *gpart, int G
     return warp_sum(s);
 }
 
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) of the weight image global -> shared ------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ void mbar_init(void *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(void *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    const uint32_t addr = smem_u32(bar);
+    while (!done)
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, void *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 // ---- the kernel -------------------------------------------------------------------------------------
 template <int R>
 __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpdateArgs a)
@@ -267,20 +307,29 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     constexpr int LD = Tile<R>::LD;
     extern __shared__ __align__(16) float smem[];
     const SmemPlan sp = make_plan(R, a.il.floats, a.po.Pstride, a.Dp, a.Ap);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tower = tid >> 7, u = tid & 127; // warps 0-3 run the actor tower, 4-7 the critic tower
+    const int jb = u & 15, rb = u >> 4;
+    // every pointer is `smem + integer` so the compiler keeps the shared state space (LDS/STS, never generic LD/ST)
     float *img = smem + sp.img;
     float *gsm = smem + sp.gsm;
     float *X = smem + sp.x;
-    float *H1[2] = {smem + sp.h1[0], smem + sp.h1[1]};
-    float *H2[2] = {smem + sp.h2[0], smem + sp.h2[1]};
+    float *h1t = smem + sp.h1[0] + tower * (kHid * LD); // this thread's tower
+    float *h2t = smem + sp.h2[0] + tower * (kHid * LD);
     float *LOGIT = smem + sp.logit, *DLOGIT = smem + sp.dlogit;
     float *VAL = smem + sp.val, *DVAL = smem + sp.dval, *RET = smem + sp.ret, *OLDLP = smem + sp.oldlp,
-          *ADV = smem + sp.adv, *ACT = smem + sp.act;
+          *ADV = smem + sp.adv, *ACT = smem + sp.act, *RED = smem + sp.red, *STAT = smem + sp.stat;
     long long *ROWID = reinterpret_cast<long long *>(smem + sp.rowid);
     float *MISC = smem + sp.misc;
+    void *mbar = MISC + 24;
+    const float *w1t_img = img + (tower ? a.il.w1t[1] : a.il.w1t[0]);
+    const float *b1_img = img + (tower ? a.il.b1[1] : a.il.b1[0]);
+    const float *w2t_img = img + (tower ? a.il.w2t[1] : a.il.w2t[0]);
+    const float *w2n_img = img + (tower ? a.il.w2n[1] : a.il.w2n[0]);
+    const float *b2_img = img + (tower ? a.il.b2[1] : a.il.b2[0]);
+    const int po_w1 = tower ? a.po.w1[1] : a.po.w1[0], po_b1 = tower ? a.po.b1[1] : a.po.b1[0];
+    const int po_w2 = tower ? a.po.w2[1] : a.po.w2[0], po_b2 = tower ? a.po.b2[1] : a.po.b2[0];
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tower = tid >> 7, u = tid & 127; // warps 0-3 actor, 4-7 critic
-    const int jb = u & 15, rb = u >> 4;
     const int G = gridDim.x;
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
     const int D = a.D, Dp = a.Dp, A = a.A;
@@ -311,223 +360,289 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         }
         MISC[0] = mean;
         MISC[1] = denom;
+        mbar_init(mbar, 1);
     }
+    const int n_tiles = (a.B + R - 1) / R;
+
+    // P0, split in two so the permutation lookup of the NEXT minibatch can be issued a whole phase early:
+    // stage_rows   : row ids of tile `tile` of minibatch `step` through the permutation -> ROWID
+    // stage_data   : (after a barrier) everything addressed by those ids: the normalised observation tile
+    //                feature-major, actions and per-row scalars.  Global loads are issued in batches before
+    //                their shared-memory stores so several are in flight per thread.
+    auto stage_rows = [&](int step, int tile) {
+        if (tid < R)
+        {
+            const int row0 = tile * R;
+            long long row = -1;
+            if (row0 + tid < a.B)
+            {
+                const long long pos = static_cast<long long>(step) * a.B + row0 + tid;
+                row = a.perm ? __ldg(a.perm + pos) : pos;
+            }
+            ROWID[tid] = row;
+        }
+    };
+    auto stage_data = [&]() {
+        float ret = 0.f, vold = 0.f, olp = 0.f;
+        long long act = 0;
+        const long long my_row = tid < R ? ROWID[tid] : -1;
+        if (my_row >= 0)
+        {
+            if (training)
+            {
+                ret = __ldg(a.returns + my_row);
+                olp = __ldg(a.old_logp + my_row);
+                if (a.adv_sums)
+                    vold = __ldg(a.value_preds + my_row);
+            }
+            if (a.head == 0)
+                act = __ldg(static_cast<const long long *>(a.actions) + my_row);
+        }
+        const float clip = a.norm_mean ? __ldg(a.norm_clip) : 0.f;
+        for (int e0 = tid; e0 < Dp * R; e0 += 4 * kUpdThreads)
+        {
+            float v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const int e = e0 + j * kUpdThreads;
+                const int k = e / R, r = e - k * R; // R is a power of two
+                v[j] = 0.f;
+                if (e < Dp * R && k < D)
+                {
+                    const long long row = ROWID[r];
+                    if (row >= 0)
+                        v[j] = __ldg(a.obs + row * D + k);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const int e = e0 + j * kUpdThreads;
+                const int k = e / R, r = e - k * R;
+                if (e < Dp * R)
+                {
+                    float x = v[j];
+                    if (a.norm_mean && k < D && ROWID[r] >= 0)
+                    {
+                        // clamp((x - mean) / sqrt(var + 1e-8), -clip, clip)    (observation_normalizer.cpp:71-73)
+                        x = (x - __ldg(a.norm_mean + k)) / sqrtf(__ldg(a.norm_var + k) + 1e-8f);
+                        x = fminf(fmaxf(x, -clip), clip);
+                    }
+                    X[k * LD + r] = x;
+                }
+            }
+        }
+        if (a.head == 1)
+            for (int e = tid; e < A * R; e += kUpdThreads)
+            {
+                const int k = e / R, r = e - k * R;
+                const long long row = ROWID[r];
+                ACT[k * LD + r] = row >= 0 ? __ldg(static_cast<const float *>(a.actions) + row * A + k) : 0.f;
+            }
+        if (tid < R)
+        {
+            RET[tid] = ret;
+            OLDLP[tid] = olp;
+            ADV[tid] = (ret - vold - MISC[0]) / MISC[1]; // (adv - mean) / (std + 1e-5)              (ppo.cpp:57)
+            if (a.head == 0)
+                reinterpret_cast<int *>(ACT)[tid] = static_cast<int>(act);
+        }
+    };
+
+#define CPPRL_MARK(slot)                                                              \
+    do                                                                                \
+    {                                                                                 \
+        if (a.dbg_clocks && tid == 0 && step == a.dbg_step)                           \
+            a.dbg_clocks[blockIdx.x * 32 + (slot)] = clock64();                       \
+    } while (0)
     grid_barrier(a.barrier, G);
     if (stopped)
         return;
-
     const float inv_b = 1.f / static_cast<float>(a.B);
-    const int n_tiles = (a.B + R - 1) / R;
+    uint32_t img_phase = 0;
+    bool staged = false;
 
     for (int step = 0; step < a.n_steps; ++step)
     {
-        // (re)load the weight image, clear the gradient accumulator
+        CPPRL_MARK(0);
+        // ---- (re)load the weight image with one TMA bulk copy per 32 KB, clear the gradient accumulator ------
+        if (tid == 0)
         {
-            const float4 *src = reinterpret_cast<const float4 *>(a.image);
-            float4 *dst = reinterpret_cast<float4 *>(img);
-            for (int i = tid; i < a.il.floats / 4; i += kUpdThreads)
-                dst[i] = __ldcg(src + i);
-            for (int i = tid; i < Pstride; i += kUpdThreads)
-                gsm[i] = 0.f;
+            const uint32_t bytes = static_cast<uint32_t>(a.il.floats) * 4u;
+            // the image was written by generic-proxy stores of other CTAs (ordered by the grid barrier); make
+            // them visible to the async proxy that performs the bulk copy
+            asm volatile("fence.proxy.async;" ::: "memory");
+            mbar_expect_tx(mbar, bytes);
+            for (uint32_t off = 0; off < bytes; off += 32768u)
+                bulk_g2s(reinterpret_cast<char *>(img) + off, reinterpret_cast<const char *>(a.image) + off,
+                         min(32768u, bytes - off), mbar);
         }
+        for (int i = tid; i < Pstride; i += kUpdThreads)
+            gsm[i] = 0.f;
+        if (!staged && blockIdx.x < n_tiles)
+        {
+            stage_rows(step, blockIdx.x);
+            __syncthreads();
+            stage_data();
+        }
+        staged = false;
+        mbar_wait(mbar, img_phase);
+        img_phase ^= 1u;
         __syncthreads();
-        const float adv_mean = MISC[0], adv_denom = MISC[1];
+        const float ce_b = a.c_entropy * inv_b;
+        CPPRL_MARK(1);
 
         for (int tile = blockIdx.x; tile < n_tiles; tile += G)
         {
             const int row0 = tile * R;
             const int nrows = min(R, a.B - row0);
-            // ---- P0: gather the tile through the permutation ---------------------------------------
-            if (tid < R)
+            if (tile != blockIdx.x)
             {
-                long long row = -1;
-                if (tid < nrows)
-                {
-                    const long long pos = static_cast<long long>(step) * a.B + row0 + tid;
-                    row = a.perm ? a.perm[pos] : pos;
-                }
-                ROWID[tid] = row;
-                float ret = 0.f, vold = 0.f, olp = 0.f;
-                if (row >= 0 && training)
-                {
-                    ret = a.returns[row];
-                    olp = a.old_logp[row];
-                    if (a.adv_sums)
-                        vold = a.value_preds[row];
-                }
-                RET[tid] = ret;
-                OLDLP[tid] = olp;
-                ADV[tid] = (ret - vold - adv_mean) / adv_denom; // (adv - mean) / (std + 1e-5)
-                if (a.head == 0)
-                {
-                    long long act = row >= 0 ? static_cast<const long long *>(a.actions)[row] : 0;
-                    reinterpret_cast<int *>(ACT)[tid] = static_cast<int>(act);
-                }
+                stage_rows(step, tile);
+                __syncthreads();
+                stage_data();
+                __syncthreads();
             }
-            __syncthreads();
-            for (int e = tid; e < Dp * R; e += kUpdThreads)
-            {
-                const int k = e / R, r = e - k * R; // R is a power of two
-                const long long row = ROWID[r];
-                float v = 0.f;
-                if (row >= 0 && k < D)
-                {
-                    v = a.obs[row * D + k];
-                    if (a.norm_mean)
-                    {
-                        // clamp((x - mean) / sqrt(var + 1e-8), -clip, clip)   (observation_normalizer.cpp:71-73)
-                        const float c = a.norm_clip[0];
-                        v = (v - a.norm_mean[k]) / sqrtf(a.norm_var[k] + 1e-8f);
-                        v = fminf(fmaxf(v, -c), c);
-                    }
-                }
-                X[k * LD + r] = v;
-            }
-            if (a.head == 1)
-                for (int e = tid; e < A * R; e += kUpdThreads)
-                {
-                    const int k = e / R, r = e - k * R;
-                    const long long row = ROWID[r];
-                    ACT[k * LD + r] = row >= 0 ? static_cast<const float *>(a.actions)[row * A + k] : 0.f;
-                }
-            __syncthreads();
-
             // ---- P1: layer 1, both towers ------------------------------------------------------------
             {
                 float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(img + a.il.w1t[tower], X, Dp, jb, rb, acc);
-                store_tanh<R>(H1[tower], img + a.il.b1[tower], jb, rb, acc);
+                gemm_cf<R>(w1t_img, X, Dp, jb, rb, acc);
+                store_tanh<R>(h1t, b1_img, jb, rb, acc);
             }
             __syncthreads();
+            CPPRL_MARK(2);
             // ---- P2: layer 2 ---------------------------------------------------------------------------
             {
                 float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(img + a.il.w2t[tower], H1[tower], kHid, jb, rb, acc);
-                store_tanh<R>(H2[tower], img + a.il.b2[tower], jb, rb, acc);
+                gemm_cf<R>(w2t_img, h1t, kHid, jb, rb, acc);
+                store_tanh<R>(h2t, b2_img, jb, rb, acc);
             }
             __syncthreads();
+            CPPRL_MARK(3);
             // ---- P3: heads: logits / loc [A][R] from the actor tower, value [R] from the critic tower ----
             for (int e = tid; e < (A + 1) * R; e += kUpdThreads)
             {
                 const int o = e / R, r = e - o * R;
                 const bool is_value = o == A;
-                const float *w = is_value ? img + a.il.wv : img + a.il.wo + o * kHid;
-                const float *h = is_value ? H2[1] : H2[0];
-                float s0 = 0.f, s1 = 0.f;
-#pragma unroll 8
-                for (int k = 0; k < kHid; k += 2)
+                const float *w = img + (is_value ? a.il.wv : a.il.wo + o * kHid);
+                const float *h = smem + (is_value ? sp.h2[1] : sp.h2[0]) + r;
+                float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll 4
+                for (int k = 0; k < kHid; k += 4)
                 {
-                    s0 = fmaf(w[k], h[k * LD + r], s0);
-                    s1 = fmaf(w[k + 1], h[(k + 1) * LD + r], s1);
+                    const float4 wq = *reinterpret_cast<const float4 *>(w + k);
+                    s0 = fmaf(wq.x, h[k * LD], s0);
+                    s1 = fmaf(wq.y, h[(k + 1) * LD], s1);
+                    s2 = fmaf(wq.z, h[(k + 2) * LD], s2);
+                    s3 = fmaf(wq.w, h[(k + 3) * LD], s3);
                 }
-                const float s = s0 + s1 + (is_value ? img[a.il.bv] : img[a.il.bo + o]);
+                const float s = (s0 + s1) + (s2 + s3) + img[is_value ? a.il.bv : a.il.bo + o];
                 if (is_value)
                     VAL[r] = s;
                 else
                     LOGIT[o * LD + r] = s;
             }
             __syncthreads();
-            // ---- P4: log-prob, entropy, loss and its gradient w.r.t. head outputs (one thread per row) ----
-            if (warp < R / 32)
+            CPPRL_MARK(4);
+            // ---- P4: log-prob, entropy, loss and its gradient w.r.t. the head outputs (one thread per row).
+            // Per-action scratch lives in the LOGIT / DLOGIT / STAT rows of shared memory (column r is private to
+            // this thread), so the loops over the runtime action count stay compact.
+            if (tid < R)
             {
                 const int r = tid;
                 const bool valid = r < nrows;
-                float st_v = 0.f, st_a = 0.f, st_e = 0.f, st_kl = 0.f, st_clip = 0.f;
-                float z[kMaxActions], dz[kMaxActions];
+                const bool live = training && valid;
                 float newlp = 0.f, ent = 0.f;
                 const float value = VAL[r];
+                int act = 0;
                 if (a.head == 0)
                 {
-                    // Categorical(logits): l = z - logsumexp(z); p = softmax(l)      (categorical.cpp:35-36)
+                    // Categorical(logits): l = z - logsumexp(z); p = softmax(l)             (categorical.cpp:35-36)
+                    act = reinterpret_cast<const int *>(ACT)[r];
                     float m = -INFINITY;
                     for (int i = 0; i < A; ++i)
-                    {
-                        z[i] = LOGIT[i * LD + r];
-                        m = fmaxf(m, z[i]);
-                    }
+                        m = fmaxf(m, LOGIT[i * LD + r]);
                     float se = 0.f;
                     for (int i = 0; i < A; ++i)
-                        se += expf(z[i] - m);
+                        se += expf(LOGIT[i * LD + r] - m);
                     const float lse = m + logf(se);
-                    const int act = reinterpret_cast<const int *>(ACT)[r];
                     for (int i = 0; i < A; ++i)
                     {
-                        z[i] -= lse;          // normalised log-probabilities
-                        dz[i] = expf(z[i]);   // probabilities
-                        ent -= z[i] * dz[i];  // entropy = -sum p log p                  (categorical.cpp:48-52)
+                        const float l = LOGIT[i * LD + r] - lse; // normalised log-probability
+                        const float pr = expf(l);                // probability
+                        ent -= l * pr;                           // entropy = -sum p log p        (categorical.cpp:48-52)
+                        newlp = i == act ? l : newlp;            // log_prob = gather(l, action)  (categorical.cpp:54-61)
+                        LOGIT[i * LD + r] = l;
+                        DLOGIT[i * LD + r] = pr;
                     }
-                    newlp = z[min(max(act, 0), A - 1)]; // log_prob = gather(l, action)     (categorical.cpp:54-61)
                 }
                 else
                 {
-                    // Normal(loc, exp(scale_log))                                        (normal.cpp:24-37)
+                    // Normal(loc, exp(scale_log))                                                (normal.cpp:24-37)
                     for (int i = 0; i < A; ++i)
                     {
-                        const float sl = img[a.il.slog + i];
-                        const float sigma = expf(sl);
+                        const float sigma = expf(img[a.il.slog + i]);
                         const float var = sigma * sigma;
                         const float log_sigma = logf(sigma);
                         const float diff = ACT[i * LD + r] - LOGIT[i * LD + r];
                         newlp += -(diff * diff) / (2.f * var) - log_sigma - 0.91893853320467274178f;
                         ent += 0.5f + 0.5f * 1.8378770664093454836f + log_sigma;
-                        z[i] = diff / var;                  // d logp / d loc
-                        dz[i] = diff * diff / var - 1.f;    // d logp / d scale_log
+                        LOGIT[i * LD + r] = diff / var;                   // d logp / d loc
+                        STAT[(5 + i) * LD + r] = diff * diff / var - 1.f; // d logp / d scale_log
                     }
                 }
-                float g_lp = 0.f, dval = 0.f;
-                if (training && valid)
+                float g_lp = 0.f, dval = 0.f, st_v = 0.f, st_a = 0.f, st_kl = 0.f, st_clip = 0.f;
+                if (live)
                 {
                     const float ret = RET[r];
                     if (a.algo == kAlgoPPO)
                     {
                         const float olp = OLDLP[r], adv = ADV[r];
-                        st_kl = olp - newlp;                                   // ppo.cpp:96
-                        const float ratio = expf(newlp - olp);                 // ppo.cpp:107
+                        st_kl = olp - newlp;                                     // ppo.cpp:96
+                        const float ratio = expf(newlp - olp);                   // ppo.cpp:107
                         const float s1 = ratio * adv;
-                        const float rc = fminf(fmaxf(ratio, a.clip_lo), a.clip_hi);
-                        const float s2 = rc * adv;
+                        const float s2 = fminf(fmaxf(ratio, a.clip_lo), a.clip_hi) * adv;
                         st_clip = fabsf(ratio - 1.f) > a.clip_param ? 1.f : 0.f; // ppo.cpp:116-122
-                        st_a = fminf(s1, s2);                                  // action_loss = -mean(min)
+                        st_a = fminf(s1, s2);                                    // action_loss = -mean(min)
                         const bool in_range = ratio >= a.clip_lo && ratio <= a.clip_hi;
-                        const bool active = in_range || s1 < s2;
-                        g_lp = active ? -a.c_actor * inv_b * adv * ratio : 0.f;
+                        g_lp = (in_range || s1 < s2) ? -a.c_actor * inv_b * adv * ratio : 0.f;
                         const float dv = ret - value;
-                        st_v = dv * dv;                                        // value_loss = 0.5*mean
+                        st_v = dv * dv;                                          // value_loss = 0.5*mean
                         dval = -a.c_value * inv_b * dv;
                     }
                     else
                     {
-                        const float adv = ret - value;                         // a2c.cpp:69
-                        st_v = adv * adv;                                      // a2c.cpp:72
-                        st_a = adv * newlp;                                    // a2c.cpp:75
+                        const float adv = ret - value;                           // a2c.cpp:69
+                        st_v = adv * adv;                                        // a2c.cpp:72
+                        st_a = adv * newlp;                                      // a2c.cpp:75
                         g_lp = -inv_b * adv;
                         dval = -2.f * a.c_value * inv_b * adv;
                     }
-                    st_e = ent;
                 }
-                const float ce_b = a.c_entropy * inv_b;
                 if (a.head == 0)
                 {
-                    const int act = reinterpret_cast<const int *>(ACT)[r];
                     for (int i = 0; i < A; ++i)
                     {
-                        const float p = dz[i];
-                        float d = g_lp * ((i == act ? 1.f : 0.f) - p) + ce_b * p * (z[i] + ent);
-                        DLOGIT[i * LD + r] = (training && valid) ? d : 0.f;
+                        const float l = LOGIT[i * LD + r], pr = DLOGIT[i * LD + r];
+                        const float d = g_lp * ((i == act ? 1.f : 0.f) - pr) + ce_b * pr * (l + ent);
+                        DLOGIT[i * LD + r] = live ? d : 0.f;
                     }
                 }
                 else
                 {
                     for (int i = 0; i < A; ++i)
                     {
-                        DLOGIT[i * LD + r] = (training && valid) ? g_lp * z[i] : 0.f;
-                        float ds = (training && valid) ? g_lp * dz[i] - ce_b : 0.f;
-                        ds = warp_sum(ds);
-                        if (lane == 0 && training)
-                            atomicAdd(&gsm[a.po.slog + i], ds);
+                        DLOGIT[i * LD + r] = live ? g_lp * LOGIT[i * LD + r] : 0.f;
+                        STAT[(5 + i) * LD + r] = live ? g_lp * STAT[(5 + i) * LD + r] - ce_b : 0.f;
                     }
                 }
                 DVAL[r] = dval;
+                STAT[0 * LD + r] = st_v;
+                STAT[1 * LD + r] = st_a;
+                STAT[2 * LD + r] = live ? ent : 0.f;
+                STAT[3 * LD + r] = st_kl;
+                STAT[4 * LD + r] = st_clip;
                 if (!training)
                 {
                     if (valid)
@@ -535,88 +650,100 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         a.out_value[row0 + r] = value;
                         a.out_logp[row0 + r] = newlp;
                     }
-                    float e = valid ? ent : 0.f;
-                    e = warp_sum(e);
+                    const float e = warp_sum(valid ? ent : 0.f);
                     if (lane == 0)
                         atomicAdd(a.out_entropy_sum, e);
                 }
-                else
-                {
-                    st_v = warp_sum(st_v), st_a = warp_sum(st_a), st_e = warp_sum(st_e);
-                    st_kl = warp_sum(st_kl), st_clip = warp_sum(st_clip);
-                    float db = warp_sum(dval);
-                    if (lane == 0)
-                    {
-                        atomicAdd(&gsm[Pstat + 0], st_v);
-                        atomicAdd(&gsm[Pstat + 1], st_a);
-                        atomicAdd(&gsm[Pstat + 2], st_e);
-                        atomicAdd(&gsm[Pstat + 3], st_kl);
-                        atomicAdd(&gsm[Pstat + 4], st_clip);
-                        atomicAdd(&gsm[a.po.bv], db);
-                    }
-                    for (int i = 0; i < A; ++i)
-                    {
-                        float d = warp_sum(DLOGIT[i * LD + r]);
-                        if (lane == 0)
-                            atomicAdd(&gsm[a.po.bo + i], d);
-                    }
-                }
-            }
-            if (!training)
-            {
-                __syncthreads();
-                continue;
             }
             __syncthreads();
-            // ---- P5: head weight gradients and dz2 = (head^T dout) * (1 - h2^2), in place over H2 ----------
+            if (!training)
+                continue;
+            CPPRL_MARK(5);
+            // ---- P5a: per-row terms -> gradient vector: loss sums, head biases, scale_log (one item per warp) ----
             {
+                const int n_items = 5 + A + 1 + (a.head == 1 ? A : 0);
+                for (int item = warp; item < n_items; item += kUpdThreads / 32)
+                {
+                    const float *src;
+                    int dst;
+                    if (item < 5)
+                        src = STAT + item * LD, dst = Pstat + item;
+                    else if (item < 5 + A)
+                        src = DLOGIT + (item - 5) * LD, dst = a.po.bo + (item - 5);
+                    else if (item == 5 + A)
+                        src = DVAL, dst = a.po.bv;
+                    else
+                        src = STAT + (5 + item - (6 + A)) * LD, dst = a.po.slog + (item - (6 + A));
+                    float sum = 0.f;
+#pragma unroll
+                    for (int r = 0; r < R; r += 32)
+                        sum += src[r + lane];
+                    sum = warp_sum(sum);
+                    if (lane == 0)
+                        gsm[dst] += sum; // each destination has exactly one owner in this phase
+                }
+            }
+            // ---- P5b: head weight gradients and dz2 = (head^T dout) * (1 - h2^2), in place over H2.
+            // Thread = (feature k, half of the rows); dh for its rows stays in registers while the loop over the
+            // runtime number of head outputs streams dout rows (broadcast LDS) against the cached h2 row.
+            {
+                constexpr int NQ = R / 8; // float4 groups in this thread's half of the rows
                 const int k = u & 63, half = u >> 6;
                 const int nout = tower == 0 ? A : 1;
-                const float *dout = tower == 0 ? DLOGIT : DVAL;
-                const float *wh = tower == 0 ? img + a.il.wo : img + a.il.wv;
-                float *h2 = H2[tower] + k * LD;
-                float wk[kMaxActions], gacc[kMaxActions];
+                const float *dout = (tower == 0 ? DLOGIT : DVAL) + half * (R / 2);
+                const float *wh = img + (tower == 0 ? a.il.wo : a.il.wv) + k;
+                float *h2 = h2t + k * LD + half * (R / 2);
+                const int wbase = (tower == 0 ? a.po.wo : a.po.wv) + k;
+                float4 h[NQ], dh[NQ];
+#pragma unroll
+                for (int qd = 0; qd < NQ; ++qd)
+                {
+                    h[qd] = *reinterpret_cast<const float4 *>(h2 + 4 * qd);
+                    dh[qd] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
                 for (int o = 0; o < nout; ++o)
                 {
-                    wk[o] = wh[o * kHid + k];
-                    gacc[o] = 0.f;
+                    const float wk = wh[o * kHid];
+                    float g0 = 0.f, g1 = 0.f;
+#pragma unroll
+                    for (int qd = 0; qd < NQ; ++qd)
+                    {
+                        const float4 d = *reinterpret_cast<const float4 *>(dout + o * LD + 4 * qd);
+                        g0 = fmaf(d.x, h[qd].x, g0);
+                        g1 = fmaf(d.y, h[qd].y, g1);
+                        g0 = fmaf(d.z, h[qd].z, g0);
+                        g1 = fmaf(d.w, h[qd].w, g1);
+                        dh[qd].x = fmaf(d.x, wk, dh[qd].x);
+                        dh[qd].y = fmaf(d.y, wk, dh[qd].y);
+                        dh[qd].z = fmaf(d.z, wk, dh[qd].z);
+                        dh[qd].w = fmaf(d.w, wk, dh[qd].w);
+                    }
+                    atomicAdd(&gsm[wbase + o * kHid], g0 + g1);
                 }
                 float bsum = 0.f;
-                const int r_begin = half * (R / 2);
-                for (int r = r_begin; r < r_begin + R / 2; r += 4)
+#pragma unroll
+                for (int qd = 0; qd < NQ; ++qd)
                 {
-                    const float4 h = *reinterpret_cast<const float4 *>(h2 + r);
-                    float4 dh = make_float4(0.f, 0.f, 0.f, 0.f);
-                    for (int o = 0; o < nout; ++o)
-                    {
-                        const float4 d = *reinterpret_cast<const float4 *>(dout + o * LD + r);
-                        gacc[o] += d.x * h.x + d.y * h.y + d.z * h.z + d.w * h.w;
-                        dh.x = fmaf(d.x, wk[o], dh.x);
-                        dh.y = fmaf(d.y, wk[o], dh.y);
-                        dh.z = fmaf(d.z, wk[o], dh.z);
-                        dh.w = fmaf(d.w, wk[o], dh.w);
-                    }
                     float4 dz;
-                    dz.x = dh.x * (1.f - h.x * h.x);
-                    dz.y = dh.y * (1.f - h.y * h.y);
-                    dz.z = dh.z * (1.f - h.z * h.z);
-                    dz.w = dh.w * (1.f - h.w * h.w);
-                    bsum += dz.x + dz.y + dz.z + dz.w;
-                    *reinterpret_cast<float4 *>(h2 + r) = dz;
+                    dz.x = dh[qd].x * (1.f - h[qd].x * h[qd].x);
+                    dz.y = dh[qd].y * (1.f - h[qd].y * h[qd].y);
+                    dz.z = dh[qd].z * (1.f - h[qd].z * h[qd].z);
+                    dz.w = dh[qd].w * (1.f - h[qd].w * h[qd].w);
+                    bsum += (dz.x + dz.y) + (dz.z + dz.w);
+                    *reinterpret_cast<float4 *>(h2 + 4 * qd) = dz;
                 }
-                const int wbase = tower == 0 ? a.po.wo : a.po.wv;
-                for (int o = 0; o < nout; ++o)
-                    atomicAdd(&gsm[wbase + o * kHid + k], gacc[o]);
-                atomicAdd(&gsm[a.po.b2[tower] + k], bsum);
+                atomicAdd(&gsm[po_b2 + k], bsum);
             }
             __syncthreads();
+            CPPRL_MARK(6);
             // ---- P6: dW2 += dz2 h1^T ------------------------------------------------------------------------
-            grad_w2<R>(H2[tower], H1[tower], u, gsm + a.po.w2[tower]);
+            grad_w2<R>(h2t, h1t, u, gsm + po_w2);
             __syncthreads();
+            CPPRL_MARK(7);
             // ---- P7: dz1 = (W2^T dz2) * (1 - h1^2), in place over H1; db1 -----------------------------------
             {
                 float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(img + a.il.w2n[tower], H2[tower], kHid, jb, rb, acc);
+                gemm_cf<R>(w2n_img, h2t, kHid, jb, rb, acc);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                 {
@@ -624,35 +751,40 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 #pragma unroll
                     for (int g = 0; g < Tile<R>::NG; ++g)
                     {
-                        float *hp = H1[tower] + (jb + 16 * q) * LD + 32 * g + 4 * rb;
+                        float *hp = h1t + (jb + 16 * q) * LD + 32 * g + 4 * rb;
                         const float4 h = *reinterpret_cast<const float4 *>(hp);
                         float4 dz;
                         dz.x = acc[q][g * 4 + 0] * (1.f - h.x * h.x);
                         dz.y = acc[q][g * 4 + 1] * (1.f - h.y * h.y);
                         dz.z = acc[q][g * 4 + 2] * (1.f - h.z * h.z);
                         dz.w = acc[q][g * 4 + 3] * (1.f - h.w * h.w);
-                        bsum += dz.x + dz.y + dz.z + dz.w;
+                        bsum += (dz.x + dz.y) + (dz.z + dz.w);
                         *reinterpret_cast<float4 *>(hp) = dz;
                     }
-                    atomicAdd(&gsm[a.po.b1[tower] + jb + 16 * q], bsum);
+                    atomicAdd(&gsm[po_b1 + jb + 16 * q], bsum);
                 }
             }
             __syncthreads();
+            CPPRL_MARK(8);
             // ---- P8: dW1 += dz1 x^T ---------------------------------------------------------------------------
-            grad_w1<R>(H1[tower], X, u, D, Dp, gsm + a.po.w1[tower]);
+            grad_w1<R>(h1t, X, u, D, Dp, gsm + po_w1);
             __syncthreads();
         } // tiles
 
         if (!training)
             break;
 
+        CPPRL_MARK(9);
         // ---- publish this CTA's partial ----------------------------------------------------------------------
         {
-            float *dst = a.gpart + static_cast<size_t>(blockIdx.x) * Pstride;
-            for (int i = tid; i < Pstride; i += kUpdThreads)
-                __stcg(dst + i, gsm[i]);
+            float4 *dst = reinterpret_cast<float4 *>(a.gpart + static_cast<size_t>(blockIdx.x) * Pstride);
+            const float4 *src = reinterpret_cast<const float4 *>(gsm);
+            for (int i = tid; i < Pstride / 4; i += kUpdThreads)
+                __stcg(dst + i, src[i]);
         }
+        CPPRL_MARK(10);
         grid_barrier(a.barrier, G);
+        CPPRL_MARK(11);
 
         // ---- phase 2: statistics, KL stop, optimiser on this CTA's slice --------------------------------------
         if (warp < 5)
@@ -706,45 +838,77 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             st->a2c_entropy = sum_e * inv_b;
             st->num_updates += 1;
         }
+        CPPRL_MARK(12);
         {
+            // This CTA owns parameters [c0, c1).  Per pass of kRedChunk parameters, warp w sums the partials of
+            // CTAs w, w+8, ... (independent coalesced loads), then the eight sub-sums are added in a fixed order.
             const float step_size = MISC[16], bc2_sqrt = MISC[17];
             const float lr = static_cast<float>(a.lr);
-            for (int i = blockIdx.x * kUpdThreads + tid; i < P; i += G * kUpdThreads)
+            const int per_cta = (P + G - 1) / G;
+            const int c0 = blockIdx.x * per_cta, c1 = min(P, c0 + per_cta);
+            for (int base = c0; base < c1; base += kRedChunk)
             {
-                float g = 0.f;
-                int c = 0;
-                for (; c + 4 <= G; c += 4)
+                const int n_here = min(kRedChunk, c1 - base);
+                for (int pl = lane; pl < n_here; pl += 32)
                 {
-                    const float g0 = __ldcg(a.gpart + static_cast<size_t>(c) * Pstride + i);
-                    const float g1 = __ldcg(a.gpart + static_cast<size_t>(c + 1) * Pstride + i);
-                    const float g2 = __ldcg(a.gpart + static_cast<size_t>(c + 2) * Pstride + i);
-                    const float g3 = __ldcg(a.gpart + static_cast<size_t>(c + 3) * Pstride + i);
-                    g += (g0 + g1) + (g2 + g3);
+                    const float *src = a.gpart + base + pl;
+                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+                    int c = warp;
+                    for (; c + 3 * kRedSplit < G; c += 4 * kRedSplit)
+                    {
+                        s0 += __ldcg(src + static_cast<size_t>(c) * Pstride);
+                        s1 += __ldcg(src + static_cast<size_t>(c + kRedSplit) * Pstride);
+                        s2 += __ldcg(src + static_cast<size_t>(c + 2 * kRedSplit) * Pstride);
+                        s3 += __ldcg(src + static_cast<size_t>(c + 3 * kRedSplit) * Pstride);
+                    }
+                    for (; c < G; c += kRedSplit)
+                        s0 += __ldcg(src + static_cast<size_t>(c) * Pstride);
+                    RED[warp * kRedChunk + pl] = (s0 + s1) + (s2 + s3);
                 }
-                for (; c < G; ++c)
-                    g += __ldcg(a.gpart + static_cast<size_t>(c) * Pstride + i);
-                float p = a.params[i];
-                if (a.opt == kOptAdam)
+                __syncthreads();
+                if (tid < n_here)
                 {
-                    const float m = a.opt_m[i] * a.beta1 + g * (1.f - a.beta1);
-                    const float v = a.opt_v[i] * a.beta2 + (g * g) * (1.f - a.beta2);
-                    a.opt_m[i] = m;
-                    a.opt_v[i] = v;
-                    p -= step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
+                    const int i = base + tid;
+                    float g = 0.f;
+#pragma unroll
+                    for (int w = 0; w < kRedSplit; ++w)
+                        g += RED[w * kRedChunk + tid];
+                    float p = a.params[i];
+                    if (a.opt == kOptAdam)
+                    {
+                        const float m = a.opt_m[i] * a.beta1 + g * (1.f - a.beta1);
+                        const float v = a.opt_v[i] * a.beta2 + (g * g) * (1.f - a.beta2);
+                        a.opt_m[i] = m;
+                        a.opt_v[i] = v;
+                        p -= step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
+                    }
+                    else
+                    {
+                        const float s = a.opt_v[i] * a.alpha + (g * g) * (1.f - a.alpha);
+                        a.opt_v[i] = s;
+                        p -= lr * (g / (sqrtf(s) + a.eps));
+                    }
+                    a.params[i] = p;
+                    image_scatter(a, a.image, i, p);
                 }
-                else
-                {
-                    const float s = a.opt_v[i] * a.alpha + (g * g) * (1.f - a.alpha);
-                    a.opt_v[i] = s;
-                    p -= lr * (g / (sqrtf(s) + a.eps));
-                }
-                a.params[i] = p;
-                image_scatter(a, a.image, i, p);
+                __syncthreads();
             }
         }
         ++applied;
+        CPPRL_MARK(13);
         if (step + 1 < a.n_steps)
+        {
+            // gather the next minibatch's first tile before the barrier: its global-memory latency overlaps the
+            // wait for the slowest CTA
+            if (blockIdx.x < n_tiles)
+            {
+                stage_tile(step + 1, blockIdx.x);
+                staged = true;
+            }
+            CPPRL_MARK(14);
             grid_barrier(a.barrier, G);
+            CPPRL_MARK(15);
+        }
     } // steps
 }
 

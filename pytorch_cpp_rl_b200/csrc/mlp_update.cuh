@@ -86,6 +86,8 @@ struct MlpUpdateArgs
     float *gpart;         // [grid][Pstride] per-CTA gradient partials
     unsigned int *barrier;
     UpdateState *state;
+    long long *dbg_clocks; // nullable: [grid][32] clock64() phase markers of step dbg_step (profiling hook)
+    int dbg_step;
     // forward-only outputs (kAlgoForward)
     float *out_value, *out_logp, *out_entropy_sum;
 };

@@ -156,6 +156,8 @@ using namespace cpprl_b200;
 extern "C" int cpprl_b200_gather_rows(const void *d_src, int64_t n_src_rows, int64_t row_bytes, const int64_t *d_idx,
                                       int64_t n_idx, void *d_dst, void *stream)
 {
+    if (n_idx == 0)
+        return 0; // empty minibatch: nothing to copy (pointers of empty tensors may be null)
     if (!d_src || !d_idx || !d_dst)
         return fail(CPPRL_B200_EINVAL, "gather_rows: null pointer");
     if (row_bytes <= 0 || row_bytes % 4 != 0 || n_idx < 0 || n_src_rows <= 0)

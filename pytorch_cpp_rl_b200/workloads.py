@@ -111,3 +111,45 @@ def synth_rollout(w: Workload, seed: int) -> Dict[str, np.ndarray]:
                 next_value=next_value,
                 value_predictions=np.zeros((T + 1, N, 1), np.float32), returns=np.zeros((T + 1, N, 1), np.float32),
                 action_log_probs=np.zeros((T, N, 1), np.float32))
+
+
+def flops_per_row(w: Workload) -> int:
+    """Algorithmic fwd+bwd FLOPs per transition per epoch = 6 x MACs/row."""
+    H, D, A = w.hidden, w.obs_dim, w.num_actions
+    if w.base == "mlp":
+        macs = 2 * (D * H + H * H) + H + A * H
+    elif w.base == "gru":
+        macs = 3 * H * (D + H) + 2 * (H * H + H * H) + H + A * H
+    else:
+        macs = 7640576 + 512 + A * 512
+    return 6 * macs
+
+
+def _orthogonal(rng, rows: int, cols: int, gain: float) -> np.ndarray:
+    a = rng.standard_normal((max(rows, cols), min(rows, cols)))
+    q, r = np.linalg.qr(a)
+    q = q * np.sign(np.diag(r))
+    if rows < cols:
+        q = q.T
+    return (gain * q[:rows, :cols]).astype(np.float32)
+
+
+def init_params(w: Workload, seed: int) -> np.ndarray:
+    """Random-init flat parameters of the workload's architecture, in the reference's registration order, with
+    the reference's init scheme (orthogonal weights with the gains of mlp_base.cpp:40-42 /
+    output_layers.cpp:37,51, zero biases, scale_log = 0).  Used by bench.py (no checkpoints offline)."""
+    from .api import mlp_param_shapes
+    rng = np.random.default_rng(seed)
+    head = "Discrete" if w.head == "categorical" else "Box"
+    out = []
+    for name, shape in mlp_param_shapes(w.obs_dim, w.num_actions, head, w.hidden, w.base == "gru"):
+        if len(shape) == 2:
+            gain = np.sqrt(2.0)
+            if name.startswith("output.linear_loc") or "gru" in name:
+                gain = 1.0
+            elif name.startswith("output.linear"):
+                gain = 0.01
+            out.append(_orthogonal(rng, shape[0], shape[1], gain).ravel())
+        else:
+            out.append(np.zeros(shape, np.float32).ravel())
+    return np.concatenate(out)

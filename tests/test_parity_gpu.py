@@ -133,8 +133,8 @@ def test_observation_normalizer_known_answer():
     n = api.ObservationNormalizer(5)
     rows = [[-10., 0., 5., 3.2, 0.], [-5., 2., 4., 3.7, -3.], [1, 2, 3, 4, 5]]
     for row in rows:
-        n.update(torch.tensor(row, device="cuda"))
-    got = n.process_observation(torch.tensor(rows[2], device="cuda")).cpu().numpy()
+        n.update(torch.tensor(row, dtype=torch.float32, device="cuda"))
+    got = n.process_observation(torch.tensor(rows[2], dtype=torch.float32, device="cuda")).cpu().numpy()
     want = [1.26008659, 0.70712887, -1.2240818, 1.10914509, 1.31322402]
     np.testing.assert_allclose(got, want, rtol=1e-5)
 
@@ -255,13 +255,19 @@ def _run_ppo_case(ref, w, seed, n_updates=2, perturb=0.0):
         np.testing.assert_allclose(got_stats[1], want_stats[1], rtol=1e-4, atol=2e-6)
         np.testing.assert_allclose(got_stats[2], want_stats[2], rtol=1e-4, atol=1.0 / w.rows)
         np.testing.assert_allclose(got_stats[3], want_stats[3], rtol=1e-4)
-        np.testing.assert_allclose(got_stats[4], want_stats[4], rtol=1e-3, atol=2e-6)
+        # "KL divergence" is the mean of (old - new) log-probs of the LAST minibatch: a difference of O(0.1) terms
+        # measured after every sequential optimizer step, so its budget grows with sqrt(steps)
+        np.testing.assert_allclose(got_stats[4], want_stats[4], rtol=1e-4 * max(4.0, w.optimizer_steps ** 0.5),
+                                   atol=2e-6)
         if len(want_stats) > 5:
             assert got_stats[5] == want_stats[5]
         want_p = sess.get_params()
         got_p = policy.params.cpu().numpy()
         err = np.abs(got_p - want_p) / np.maximum(np.abs(want_p), w.learning_rate)
-        assert err.max() <= 1e-4 * max(1, w.optimizer_steps) ** 0.5 + 1e-4, (upd, err.max(), np.argmax(err))
+        budget = 1e-4 * max(1, w.optimizer_steps) ** 0.5 + 1e-4
+        print(f"[parity] {w.name} update {upd}: max param rel err {err.max():.3e} (budget {budget:.1e}), "
+              f"median {np.median(err):.2e}")
+        assert err.max() <= budget, (upd, err.max(), np.argmax(err))
         if w.normalize_obs:
             _, c, m, v = sess.get_normalizer()
             n = policy.observation_normalizer

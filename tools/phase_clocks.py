@@ -1,0 +1,38 @@
+#!/usr/bin/env python
+"""Per-phase cycle breakdown of the fused update kernel (clock64 markers, see cpprl_b200_debug_phase_clocks)."""
+import ctypes as C
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import numpy as np
+import torch
+
+from bench import GpuSide
+from pytorch_cpp_rl_b200 import cabi
+from pytorch_cpp_rl_b200.workloads import CONFIGS
+
+NAMES = ["img+stage", "P1 L1", "P2 L2", "P3 heads", "P4 loss", "P5 head-bwd", "P6 dW2", "P7 dz1", "P8 dW1", "publish",
+         "barrier1", "stats", "reduce+opt", "stage next", "barrier2"]
+cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
+step = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+w = CONFIGS[cfg]
+side = GpuSide(w, 0)
+lib = cabi.load()
+buf = torch.zeros(148 * 32, dtype=torch.int64, device="cuda")
+for _ in range(3):
+    side.step_device()
+torch.cuda.synchronize()
+lib.cpprl_b200_debug_phase_clocks(C.c_void_p(buf.data_ptr()), step)
+side.step_device()
+torch.cuda.synchronize()
+lib.cpprl_b200_debug_phase_clocks(None, 0)
+c = buf.cpu().numpy().reshape(148, 32)
+used = c[:, 0] != 0
+c = c[used]
+print(f"{cfg}: {used.sum()} CTAs, step {step}; cycles per phase (min / median / max over CTAs); multi-tile CTAs show the LAST tile")
+d = np.diff(c[:, :16], axis=1)
+for i, n in enumerate(NAMES):
+    print(f"  {n:12s} {d[:, i].min():8d} {int(np.median(d[:, i])):8d} {d[:, i].max():8d}")
+tot = c[:, 15] - c[:, 0]
+print(f"  total        {tot.min():8d} {int(np.median(tot)):8d} {tot.max():8d}  (= {np.median(tot) / 1.965e3:.1f} us at 1965 MHz)")
