@@ -902,7 +902,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             // wait for the slowest CTA
             if (blockIdx.x < n_tiles)
             {
-                stage_tile(step + 1, blockIdx.x);
+                stage_rows(step + 1, blockIdx.x);
+                __syncthreads();
+                stage_data();
                 staged = true;
             }
             CPPRL_MARK(14);
