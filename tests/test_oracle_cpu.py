@@ -1,0 +1,185 @@
+"""CPU tests pinning the numpy restatement (oracle/cpprl_oracle.py):
+ 1. the reference's own known-answer vectors (file:line cited per test);
+ 2. the golden fixtures generated from the compiled reference (tests/golden/make_golden.py);
+ 3. when oracle/_ref is present, a live cross-check against the compiled reference on another seed.
+"""
+import numpy as np
+import pytest
+
+from oracle import cpprl_oracle as O
+from tests import golden_io as G
+
+
+# ---- 1. the reference's known answers ------------------------------------------------------------------
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_compute_returns_known_answer(use_gae):
+    """src/storage.cpp:341-437: 3 steps x 2 envs, gamma = tau = 0.6, env 1 ends an episode at step 1."""
+    T, N = 3, 2
+    rewards = np.array([[0, 1], [1, 2], [2, 3]], np.float32).reshape(T, N, 1)
+    values = np.zeros((T + 1, N, 1), np.float32)
+    values[:T, :, 0] = [[0, 1], [1, 2], [2, 3]]
+    masks = np.ones((T + 1, N, 1), np.float32)
+    masks[1:, :, 0] = [[1, 1], [1, 0], [1, 1]]
+    returns = np.zeros((T + 1, N, 1), np.float32)
+    O.compute_returns(rewards, values, masks, returns, np.array([[0.0], [1.0]], np.float32), use_gae, 0.6, 0.6)
+    if use_gae:
+        want = [[1.032, 2.2], [2.2, 2.0], [2.0, 3.6], [0.0, 0.0]]  # returns[T] stays untouched
+        assert np.array_equal(values[T, :, 0], [0.0, 1.0])          # value_predictions[T] <- next_value
+    else:
+        want = [[1.32, 2.2], [2.2, 2.0], [2.0, 3.6], [0.0, 1.0]]
+    np.testing.assert_allclose(returns[..., 0], want, rtol=1e-6)
+
+
+def test_categorical_known_answer():
+    """src/distributions/categorical.cpp:142-195 (probs constructor; entropy and broadcast log_prob)."""
+    probs = np.array([[0.5, 0.5, 0.0, 0.0], [0.25, 0.25, 0.25, 0.25]], np.float32)
+    logits, p = O.categorical_from_probs(probs)
+    np.testing.assert_allclose(O.categorical_entropy(logits, p), [0.6931, 1.3863], rtol=1e-3)
+    # log_prob(actions [2,2]) broadcasts the two distributions along the LAST action axis (categorical.cpp:54-61):
+    # out[i][j] = logits[j][actions[i][j]]
+    actions = np.array([[0, 1], [2, 3]])
+    got = np.array([[logits[j, actions[i, j]] for j in range(2)] for i in range(2)])
+    np.testing.assert_allclose(got, [[-0.6931, -1.3863], [-15.9424, -1.3863]], rtol=1e-3)
+
+
+def test_normal_known_answer():
+    """src/distributions/normal.cpp:46-104."""
+    loc = np.array([[0, 1, 2], [3, 4, 5]], np.float32)
+    scale = np.array([[5, 4, 3], [2, 1, 0]], np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        ent = O.normal_entropy(loc, scale)
+        lp = O.normal_log_prob(loc, scale, np.array([[0, 1, 2], [0, 1, 2]], np.float32))
+    np.testing.assert_allclose(ent[0], 8.3512, rtol=1e-3)
+    assert ent[1] == -np.inf
+    np.testing.assert_allclose(lp[0], [-2.5284, -2.3052, -2.0176], rtol=1e-3)
+    np.testing.assert_allclose(lp[1, :2], [-2.7371, -5.4189], rtol=1e-3)
+    assert np.isnan(lp[1, 2])
+
+
+def test_observation_normalizer_known_answer():
+    """src/observation_normalizer.cpp:108-129: three single-row updates, then normalise the last row."""
+    rms = O.RunningMeanStd(5)
+    rows = np.array([[-10., 0., 5., 3.2, 0.], [-5., 2., 4., 3.7, -3.], [1, 2, 3, 4, 5]], np.float32)
+    for row in rows:
+        rms.update(row)
+    got = O.process_observation(rows[2], rms.mean, rms.variance, 10.0)
+    np.testing.assert_allclose(got, [1.26008659, 0.70712887, -1.2240818, 1.10914509, 1.31322402], rtol=1e-5)
+
+
+def test_observation_normalizer_clips():
+    """src/observation_normalizer.cpp:95-106."""
+    out = O.process_observation(np.array([-1000., -100, -10, 0, 10, 100, 1000], np.float32), np.zeros(7, np.float32),
+                                np.ones(7, np.float32), 1.0)
+    assert out.max() <= 1.0 and out.min() >= -1.0
+
+
+def test_running_mean_std_matches_batch_moments():
+    """src/running_mean_std.cpp:47-70: after several updates the running moments ~ the moments of everything seen."""
+    rng = np.random.default_rng(0)
+    rms = O.RunningMeanStd(4)
+    xs = [rng.standard_normal((n, 4)).astype(np.float32) * 3 + 2 for n in (3, 100, 57)]
+    for x in xs:
+        rms.update(x)
+    allx = np.concatenate(xs)
+    np.testing.assert_allclose(rms.mean, allx.mean(0), atol=1e-3)
+    np.testing.assert_allclose(rms.variance, allx.var(0), rtol=1e-3)
+
+
+def test_generator_shapes_and_errors():
+    """src/generators/feed_forward_generator.cpp:82-121, recurrent_generator.cpp:100-137, storage.cpp:146-218."""
+    T, N = 3, 5
+    ro = O.Rollout(np.zeros((T + 1, N, 4, 4), np.float32), np.zeros((T + 1, N, 3), np.float32),
+                   np.zeros((T, N, 1), np.float32), np.zeros((T + 1, N, 1), np.float32), np.zeros((T + 1, N, 1), np.float32),
+                   np.zeros((T, N, 1), np.float32), np.zeros((T, N, 1), np.int64), np.ones((T + 1, N, 1), np.float32))
+    adv = np.zeros((T, N, 1), np.float32)
+    mbs = O.feed_forward_minibatches(ro, adv, 5, np.random.default_rng(0).permutation(15))
+    assert len(mbs) == 5 and mbs[0]["observations"].shape == (3, 4, 4) and mbs[0]["hidden_states"].shape == (3, 3)
+    assert all(mb[k].shape == (3, 1) for mb in mbs for k in ("actions", "value_predictions", "returns", "masks",
+                                                             "action_log_probs", "advantages"))
+    with pytest.raises(RuntimeError, match="greater than or equal to the number of minibatches"):
+        O.feed_forward_minibatches(ro, adv, 16, np.arange(15))
+    rb = O.recurrent_minibatches(ro, adv, 5, np.arange(5))
+    assert len(rb) == 5 and rb[0]["observations"].shape == (3, 4, 4) and rb[0]["hidden_states"].shape == (1, 3)
+    with pytest.raises(RuntimeError):
+        O.recurrent_minibatches(ro, adv, 6, np.arange(5))
+
+
+# ---- 2. golden fixtures from the compiled reference -----------------------------------------------------------
+def test_kats_fixture():
+    d = np.load(G.GOLDEN / "kats.npz")
+    logp_all, probs = O.categorical_from_logits(d["logits"])
+    np.testing.assert_allclose(O.categorical_log_prob(logp_all, d["actions"]), d["c_logp"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(O.categorical_entropy(logp_all, probs), d["c_ent"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(probs, d["c_probs"], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(O.normal_log_prob(d["loc"], d["scale"], d["value"]), d["n_logp"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(O.normal_entropy(d["loc"], np.broadcast_to(d["scale"], d["loc"].shape)), d["n_ent"], rtol=1e-6)
+    D = d["rms_x"].shape[-1]
+    rms = O.RunningMeanStd(D)
+    for i in range(3):
+        rms.update(d["rms_x"][i])
+        np.testing.assert_allclose(np.concatenate([rms.count, rms.mean, rms.variance]), d["rms_states"][i], rtol=2e-5, atol=1e-6)
+        np.testing.assert_allclose(O.process_observation(d["rms_y"], rms.mean, rms.variance, float(d["rms_clip"])),
+                                   d["rms_y_out"][i], rtol=1e-5, atol=1e-5)
+
+
+def run_oracle_case(w, d, dtype=np.float32):
+    """Replays a fixture through the numpy restatement; yields (update index, stats, policy, rollout)."""
+    r = G.rollout_arrays(d)
+    pol = O.Policy(w.obs_dim, w.num_actions, w.head, w.hidden, w.base == "gru", w.normalize_obs, dtype)
+    pol.set_params(d["params_init"])
+    cast = lambda a: a.astype(dtype) if a.dtype == np.float32 else a
+    ro = O.Rollout(**{k: cast(r[k]) for k in ("observations", "hidden_states", "rewards", "value_predictions", "returns",
+                                              "action_log_probs", "actions", "masks")})
+    if w.algo == "ppo":
+        algo = O.PPO(pol, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef,
+                     w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    else:
+        algo = O.A2C(pol, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
+    for u in range(int(d["n_updates"])):
+        O.compute_returns(ro.rewards, ro.value_predictions, ro.masks, ro.returns, cast(r["next_value"]), w.use_gae,
+                          w.gamma, w.tau)
+        stats = algo.update(ro, d[f"perms{u}"]) if w.algo == "ppo" else algo.update(ro)
+        yield u, np.array([v for _, v in stats], np.float32), pol, ro
+
+
+@pytest.mark.parametrize("name", G.CASES)
+def test_golden_fixture(name):
+    w, d = G.load(name)
+    for u, stats, pol, ro in run_oracle_case(w, d):
+        assert np.array_equal(ro.returns, d[f"returns{u}"]), "returns are bit-exact (same operator order, fp32)"
+        want = d[f"stats{u}"]
+        assert len(stats) == len(want)
+        np.testing.assert_allclose(stats, want, rtol=1e-4, atol=5e-6, equal_nan=True)
+        wp = d[f"params{u}"]
+        err = np.abs(pol.flat - wp) / np.maximum(np.abs(wp), w.learning_rate)
+        # two fp32 implementations of a sign-like optimiser step: 1e-4 on all but a handful of near-zero gradients
+        assert np.quantile(err, 0.99) <= 1e-4 and err.max() <= 5e-3, (u, err.max(), np.quantile(err, 0.99))
+        if w.normalize_obs:
+            got = np.concatenate([pol.normalizer.count, pol.normalizer.mean, pol.normalizer.variance])
+            np.testing.assert_allclose(got, d[f"norm{u}"], rtol=2e-5, atol=1e-6)
+
+
+# ---- 3. live cross-check against the compiled reference ----------------------------------------------------------
+def test_live_reference_cross_check(ref):
+    from pytorch_cpp_rl_b200.workloads import CONFIGS, synth_rollout
+    from tests import helpers as H
+    w = CONFIGS["cfg3"].scaled(T=16, N=32, num_epoch=2, num_mini_batch=4)
+    r = synth_rollout(w, 11)
+    sess = H.make_ref_session(ref, w, init_seed=11)
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    pol = O.Policy(w.obs_dim, w.num_actions, w.head, w.hidden, False, True)
+    pol.set_params(sess.get_params())
+    ro = O.Rollout(**{k: r[k].copy() for k in ("observations", "hidden_states", "rewards", "value_predictions", "returns",
+                                               "action_log_probs", "actions", "masks")})
+    algo = O.PPO(pol, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef, w.entropy_coef,
+                 w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    sess.compute_returns(r["next_value"], True, w.gamma, w.tau)
+    want, _ = sess.update(1.0, perm_seed=77)
+    O.compute_returns(ro.rewards, ro.value_predictions, ro.masks, ro.returns, r["next_value"], True, w.gamma, w.tau)
+    assert np.array_equal(ro.returns, sess.get_returns())
+    got = np.array([v for _, v in algo.update(ro, H.draw_perms(77, w.rows, w.num_epoch).numpy())], np.float32)
+    np.testing.assert_allclose(got, want, rtol=1e-4, atol=5e-6)
+    wp = sess.get_params()
+    err = np.abs(pol.flat - wp) / np.maximum(np.abs(wp), w.learning_rate)
+    assert np.quantile(err, 0.99) <= 1e-4
