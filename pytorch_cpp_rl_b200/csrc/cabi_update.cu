@@ -1,5 +1,6 @@
 // cabi_update.cu — C-ABI entry points for evaluate_actions, PPO update and A2C update
 // (host-side orchestration: validation, scratch, permutation staging, launches, statistics read-back).
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <mutex>
@@ -11,7 +12,7 @@
 namespace cpprl_b200
 {
 // from mlp_update.cu / returns_scan.cu
-size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap);
+size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta);
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s);
 int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums,
                              cudaStream_t s);
@@ -158,22 +159,31 @@ struct Scratch
 
 struct Plan
 {
-    int R = 0, grid = 0;
+    int R = 0, grid = 0, n_active = 0, per_cta = 0;
 };
 
 // Tile rows and grid for a minibatch of B rows: the smallest tile that still gives every SM at most one
 // tile, falling back to the smaller tile when the shared-memory plan of the larger one does not fit.
-int choose_plan(int64_t B, const ImageLayout &il, const ParamOffsets &po, int Dp, int Ap, Plan &plan)
+// Training launches keep at least 16 CTAs so that the phase-2 slice of the parameter vector each CTA reduces,
+// steps and keeps resident in shared memory stays small; CTAs beyond the tile count only take part in phase 2.
+int choose_plan(int64_t B, const ImageLayout &il, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan)
 {
     const int sms = sm_count();
     int R = (B <= 32ll * sms) ? 32 : 64;
-    if (R == 64 && mlp_update_smem_bytes(64, il.floats, po.Pstride, Dp, Ap) > 227 * 1024)
+    const int64_t tiles32 = (B + 31) / 32, tiles64 = (B + 63) / 64;
+    auto shape = [&](int r, Plan &pl) {
+        const int64_t tiles = r == 32 ? tiles32 : tiles64;
+        pl.R = r;
+        pl.n_active = static_cast<int>(tiles < sms ? tiles : sms);
+        pl.grid = training ? std::max(pl.n_active, std::min(16, sms)) : pl.n_active;
+        const int p4 = po.Pstride - kNumStats; // parameter count rounded up to 4
+        pl.per_cta = training ? round_up((p4 + pl.grid - 1) / pl.grid, 4) : 0;
+        return mlp_update_smem_bytes(r, il.floats, po.Pstride, Dp, Ap, pl.per_cta);
+    };
+    if (R == 64 && shape(64, plan) > 227 * 1024)
         R = 32;
-    if (mlp_update_smem_bytes(R, il.floats, po.Pstride, Dp, Ap) > 227 * 1024)
+    if (shape(R, plan) > 227 * 1024)
         return fail(CPPRL_B200_EUNSUPPORTED, "update: observation / action size needs more than 227 KB of shared memory");
-    const int64_t tiles = (B + R - 1) / R;
-    plan.R = R;
-    plan.grid = static_cast<int>(tiles < sms ? tiles : sms);
     return 0;
 }
 
@@ -364,10 +374,10 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
     const ImageLayout il = make_image_layout(Dp, Ap);
-    if (int rc = choose_plan(mbs, il, po, Dp, Ap, h->plan))
+    if (int rc = choose_plan(mbs, il, po, Dp, Ap, true, h->plan))
         return rc;
     const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
-    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(h->plan.grid) * po.Pstride, rms_ws))
+    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(h->plan.n_active) * po.Pstride, rms_ws))
         return rc;
 
     MlpUpdateArgs &a = h->args;
@@ -382,6 +392,8 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     a.rows = rows;
     a.B = static_cast<int>(mbs);
     a.n_steps = static_cast<int>(h->n_mb);
+    a.n_active = h->plan.n_active;
+    a.per_cta = h->plan.per_cta;
     a.adv_sums = h->scratch.adv_sums;
     a.algo = kAlgoPPO;
     a.clip_param = opt->clip_param;
@@ -647,10 +659,10 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
     const ImageLayout il = make_image_layout(Dp, Ap);
     Plan plan;
-    if (int rc = choose_plan(rows, il, po, Dp, Ap, plan))
+    if (int rc = choose_plan(rows, il, po, Dp, Ap, true, plan))
         return rc;
     const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
-    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(plan.grid) * po.Pstride, rms_ws))
+    if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(plan.n_active) * po.Pstride, rms_ws))
         return rc;
 
     KernelTimer timer("update", s);
@@ -674,6 +686,8 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.perm = nullptr;
     a.B = static_cast<int>(rows);
     a.n_steps = 1;
+    a.n_active = plan.n_active;
+    a.per_cta = plan.per_cta;
     a.adv_sums = nullptr;
     a.algo = kAlgoA2C;
     a.c_actor = 1.f;
@@ -756,7 +770,7 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
     const ImageLayout il = make_image_layout(Dp, Ap);
     Plan plan;
-    if (int rc = choose_plan(B, il, po, Dp, Ap, plan))
+    if (int rc = choose_plan(B, il, po, Dp, Ap, false, plan))
         return rc;
     if (int rc = g_eval_scratch.ensure(il.floats, 0, 0))
         return rc;
@@ -769,6 +783,8 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     a.rows = B;
     a.B = static_cast<int>(B);
     a.n_steps = 1;
+    a.n_active = plan.n_active;
+    a.per_cta = 0;
     a.algo = kAlgoForward;
     a.barrier = g_eval_scratch.barrier;
     a.out_value = d_value;

@@ -42,16 +42,16 @@ struct Tile
     static_assert(R == 32 || R == 64, "tile rows");
 };
 
-constexpr int kRedSplit = 8;   // warps splitting the partials of one parameter in phase 2
-constexpr int kRedChunk = 128; // parameters reduced per pass by one CTA
+constexpr int kRedSplit = 8;               // warps splitting the partials of one parameter in phase 2
+constexpr int kRedMaxPer = (148 + kRedSplit - 1) / kRedSplit; // partials one warp sums per granule (grid <= 148)
 
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct SmemPlan
 {
-    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, red, misc, total;
+    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, red, own, sig, misc, total;
 };
 
-__host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap)
+__host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
 {
     const int LD = R + 4;
     SmemPlan p;
@@ -73,7 +73,9 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.act = o, o += Ap * LD;
     p.rowid = o, o += 2 * LD; // long long per row
     p.stat = o, o += (5 + Ap) * LD; // per-row loss terms and scale_log gradients, reduced at the start of P5
-    p.red = o, o += kRedSplit * kRedChunk; // phase-2 reduction scratch
+    p.red = o, o += kRedSplit * (per_cta + kNumStats); // phase-2 reduction scratch: [split][owned params + stats]
+    p.own = o, o += 3 * per_cta;                       // this CTA's slice of params / Adam exp_avg / exp_avg_sq
+    p.sig = o, o += 2 * Ap;                            // Normal head: {sigma^2, log sigma} per action
     p.misc = o, o += 32;
     p.total = o;
     return p;
@@ -134,32 +136,57 @@ __device__ __forceinline__ void gemm_cf(const float *__restrict__ Wc, const floa
                                         int rb, float (&acc)[4][Tile<R>::NG * 4])
 {
     constexpr int LD = Tile<R>::LD, NG = Tile<R>::NG;
+    // accumulators as row pairs: one FFMA2 (Blackwell packed fp32x2 FMA) does two rows of one output feature,
+    // halving the issue slots the 32 FMAs of an iteration need
+    float2 acc2[4][NG * 2];
 #pragma unroll
     for (int a = 0; a < 4; ++a)
 #pragma unroll
-        for (int c = 0; c < NG * 4; ++c)
-            acc[a][c] = 0.f;
+        for (int c = 0; c < NG * 2; ++c)
+            acc2[a][c] = make_float2(0.f, 0.f);
     const float *wp = Wc + 4 * jb;
     const float *ip = in + 4 * rb;
+    // operands of iteration k+1 are fetched before the FMAs of iteration k (two warps per scheduler cannot
+    // hide the 29-cycle LDS latency on their own)
+    float4 w_next = *reinterpret_cast<const float4 *>(wp);
+    float4 x_next[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g)
+        x_next[g] = *reinterpret_cast<const float4 *>(ip + 32 * g);
 #pragma unroll 4
     for (int k = 0; k < K; ++k)
     {
-        const float4 w = *reinterpret_cast<const float4 *>(wp + k * kHid);
+        const float4 w = w_next;
+        float4 x[NG];
+#pragma unroll
+        for (int g = 0; g < NG; ++g)
+            x[g] = x_next[g];
+        const int kn = k + 1 < K ? k + 1 : k;
+        w_next = *reinterpret_cast<const float4 *>(wp + kn * kHid);
+#pragma unroll
+        for (int g = 0; g < NG; ++g)
+            x_next[g] = *reinterpret_cast<const float4 *>(ip + kn * LD + 32 * g);
+        const float2 wa[4] = {make_float2(w.x, w.x), make_float2(w.y, w.y), make_float2(w.z, w.z), make_float2(w.w, w.w)};
 #pragma unroll
         for (int g = 0; g < NG; ++g)
         {
-            const float4 x = *reinterpret_cast<const float4 *>(ip + k * LD + 32 * g);
-            const float xs[4] = {x.x, x.y, x.z, x.w};
+            const float2 xlo = make_float2(x[g].x, x[g].y), xhi = make_float2(x[g].z, x[g].w);
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+            for (int a = 0; a < 4; ++a)
             {
-                acc[0][g * 4 + i] = fmaf(w.x, xs[i], acc[0][g * 4 + i]);
-                acc[1][g * 4 + i] = fmaf(w.y, xs[i], acc[1][g * 4 + i]);
-                acc[2][g * 4 + i] = fmaf(w.z, xs[i], acc[2][g * 4 + i]);
-                acc[3][g * 4 + i] = fmaf(w.w, xs[i], acc[3][g * 4 + i]);
+                acc2[a][g * 2] = __ffma2_rn(wa[a], xlo, acc2[a][g * 2]);
+                acc2[a][g * 2 + 1] = __ffma2_rn(wa[a], xhi, acc2[a][g * 2 + 1]);
             }
         }
     }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < NG * 2; ++c)
+        {
+            acc[a][2 * c] = acc2[a][c].x;
+            acc[a][2 * c + 1] = acc2[a][c].y;
+        }
 }
 
 // h = tanh(acc + bias) stored feature-major.
@@ -185,18 +212,20 @@ __device__ __forceinline__ void store_tanh(float *__restrict__ out, const float 
 }
 
 // dW[j][k] += sum_r dz[j][r] * act[k][r]  (64 x 64), thread owns j in {jq + 8a}, k in {kq + 16b}.
+// Each accumulator is a pair (sum over even rows, sum over odd rows) fed by FFMA2 straight from the 16-byte
+// operand loads; the halves are added once at the end.
 template <int R>
 __device__ __forceinline__ void grad_w2(const float *__restrict__ dz, const float *__restrict__ act, int u,
                                         float *__restrict__ gout)
 {
     constexpr int LD = Tile<R>::LD;
     const int kq = u & 15, jq = u >> 4;
-    float acc[8][4];
+    float2 acc[8][4];
 #pragma unroll
     for (int a = 0; a < 8; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b)
-            acc[a][b] = 0.f;
+            acc[a][b] = make_float2(0.f, 0.f);
 #pragma unroll 2
     for (int r = 0; r < R; r += 4)
     {
@@ -208,13 +237,12 @@ __device__ __forceinline__ void grad_w2(const float *__restrict__ dz, const floa
         for (int a = 0; a < 8; ++a)
         {
             const float4 av = *reinterpret_cast<const float4 *>(dz + (jq + 8 * a) * LD + r);
+            const float2 alo = make_float2(av.x, av.y), ahi = make_float2(av.z, av.w);
 #pragma unroll
             for (int b = 0; b < 4; ++b)
             {
-                acc[a][b] = fmaf(av.x, bv[b].x, acc[a][b]);
-                acc[a][b] = fmaf(av.y, bv[b].y, acc[a][b]);
-                acc[a][b] = fmaf(av.z, bv[b].z, acc[a][b]);
-                acc[a][b] = fmaf(av.w, bv[b].w, acc[a][b]);
+                acc[a][b] = __ffma2_rn(alo, make_float2(bv[b].x, bv[b].y), acc[a][b]);
+                acc[a][b] = __ffma2_rn(ahi, make_float2(bv[b].z, bv[b].w), acc[a][b]);
             }
         }
     }
@@ -222,7 +250,7 @@ __device__ __forceinline__ void grad_w2(const float *__restrict__ dz, const floa
     for (int a = 0; a < 8; ++a)
 #pragma unroll
         for (int b = 0; b < 4; ++b)
-            gout[(jq + 8 * a) * kHid + kq + 16 * b] += acc[a][b];
+            gout[(jq + 8 * a) * kHid + kq + 16 * b] += acc[a][b].x + acc[a][b].y;
 }
 
 // dW1[j][k] += sum_r dz[j][r] * x[k][r]  (64 x D), thread owns j = u % 64 and half of the k range.
@@ -235,34 +263,28 @@ __device__ __forceinline__ void grad_w1(const float *__restrict__ dz, const floa
     const int k_begin = half * (Dp >> 1), k_end = k_begin + (Dp >> 1);
     for (int kc = k_begin; kc < k_end; kc += 4)
     {
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+        float2 acc[4];
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+            acc[kk] = make_float2(0.f, 0.f);
 #pragma unroll 4
         for (int r = 0; r < R; r += 4)
         {
             const float4 av = *reinterpret_cast<const float4 *>(dz + j * LD + r);
+            const float2 alo = make_float2(av.x, av.y), ahi = make_float2(av.z, av.w);
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk)
             {
                 const float4 xv = *reinterpret_cast<const float4 *>(x + (kc + kk) * LD + r);
-                acc[kk] = fmaf(av.x, xv.x, acc[kk]);
-                acc[kk] = fmaf(av.y, xv.y, acc[kk]);
-                acc[kk] = fmaf(av.z, xv.z, acc[kk]);
-                acc[kk] = fmaf(av.w, xv.w, acc[kk]);
+                acc[kk] = __ffma2_rn(alo, make_float2(xv.x, xv.y), acc[kk]);
+                acc[kk] = __ffma2_rn(ahi, make_float2(xv.z, xv.w), acc[kk]);
             }
         }
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
             if (kc + kk < D)
-                gout[j * D + kc + kk] += acc[kk];
+                gout[j * D + kc + kk] += acc[kk].x + acc[kk].y;
     }
-}
-
-__device__ __forceinline__ float block_bcast_sum_stats(const float *gpart, int G, int Pstride, int slot, int lane)
-{
-    float s = 0.f;
-    for (int g = lane; g < G; g += 32)
-        s += __ldcg(gpart + static_cast<size_t>(g) * Pstride + slot);
-    return warp_sum(s);
 }
 
 // ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) of the weight image global -> shared ------------------
@@ -300,13 +322,40 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  : "memory");
 }
 
+// ---- grid-wide barrier, split into arrive / wait ------------------------------------------------------
+// `bar` is one unsigned counter zeroed by the host before every launch; barrier number k (0-based) of the
+// launch is complete when the counter reaches G*(k+1).  Work placed between arrive and wait overlaps the
+// round trip of the slowest CTA.
+__device__ __forceinline__ void grid_arrive(unsigned int *bar)
+{
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+        __threadfence();
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
+    }
+}
+__device__ __forceinline__ void grid_wait(unsigned int *bar, unsigned int target)
+{
+    if (threadIdx.x == 0)
+    {
+        unsigned int v;
+        do
+        {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        } while (v < target);
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 // ---- the kernel -------------------------------------------------------------------------------------
 template <int R>
 __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpdateArgs a)
 {
     constexpr int LD = Tile<R>::LD;
     extern __shared__ __align__(16) float smem[];
-    const SmemPlan sp = make_plan(R, a.il.floats, a.po.Pstride, a.Dp, a.Ap);
+    const SmemPlan sp = make_plan(R, a.il.floats, a.po.Pstride, a.Dp, a.Ap, a.per_cta);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tower = tid >> 7, u = tid & 127; // warps 0-3 run the actor tower, 4-7 the critic tower
     const int jb = u & 15, rb = u >> 4;
@@ -319,6 +368,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     float *LOGIT = smem + sp.logit, *DLOGIT = smem + sp.dlogit;
     float *VAL = smem + sp.val, *DVAL = smem + sp.dval, *RET = smem + sp.ret, *OLDLP = smem + sp.oldlp,
           *ADV = smem + sp.adv, *ACT = smem + sp.act, *RED = smem + sp.red, *STAT = smem + sp.stat;
+    float *OWN_P = smem + sp.own, *OWN_M = OWN_P + a.per_cta, *OWN_V = OWN_M + a.per_cta;
+    float *SIG = smem + sp.sig;
     long long *ROWID = reinterpret_cast<long long *>(smem + sp.rowid);
     float *MISC = smem + sp.misc;
     void *mbar = MISC + 24;
@@ -334,6 +385,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
     const int D = a.D, Dp = a.Dp, A = a.A;
     const bool training = a.algo != kAlgoForward;
+    const bool active = static_cast<int>(blockIdx.x) < a.n_active; // owns tiles, publishes a partial
+    const int n_act = a.n_active;
+    // phase-2 ownership: parameters [c0, c0 + n_own) of the flat vector (n_own a multiple of 4, may be 0)
+    const int c0 = min(Pstat, static_cast<int>(blockIdx.x) * a.per_cta);
+    const int n_own = min(Pstat, c0 + a.per_cta) - c0;
+    unsigned int bar_target = 0;
 
     // ---- prologue: read persistent state, build the weight image from the parameters -----------------
     int stopped = 0, applied = 0;
@@ -342,6 +399,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     {
         stopped = a.state->stopped;
         opt_step0 = a.state->opt_step;
+        for (int i = tid; i < n_own; i += kUpdThreads)
+        {
+            const int gi = c0 + i;
+            const bool real = gi < P;
+            OWN_P[i] = real ? a.params[gi] : 0.f;
+            OWN_V[i] = real ? a.opt_v[gi] : 0.f;
+            OWN_M[i] = (real && a.opt == kOptAdam) ? a.opt_m[gi] : 0.f;
+        }
     }
     for (int i = blockIdx.x * kUpdThreads + tid; i < P; i += G * kUpdThreads)
         image_scatter(a, a.image, i, a.params[i]);
@@ -364,7 +429,6 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     }
     const int n_tiles = (a.B + R - 1) / R;
 
-    // P0, split in two so the permutation lookup of the NEXT minibatch can be issued a whole phase early:
     // stage_rows   : row ids of tile `tile` of minibatch `step` through the permutation -> ROWID
     // stage_data   : (after a barrier) everything addressed by those ids: the normalised observation tile
     //                feature-major, actions and per-row scalars.  Global loads are issued in batches before
@@ -456,48 +520,73 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         if (a.dbg_clocks && tid == 0 && step == a.dbg_step)                           \
             a.dbg_clocks[blockIdx.x * 32 + (slot)] = clock64();                       \
     } while (0)
-    grid_barrier(a.barrier, G);
+    grid_arrive(a.barrier); // the image is complete once every CTA has scattered its share of the parameters
+    bar_target += G;
+    grid_wait(a.barrier, bar_target);
     if (stopped)
         return;
     const float inv_b = 1.f / static_cast<float>(a.B);
     uint32_t img_phase = 0;
     bool staged = false;
+    // the optimiser state of this CTA's slice lives in shared memory for the whole launch; it goes back to
+    // global memory on every exit path
+    auto write_back_state = [&]() {
+        for (int i = tid; i < n_own; i += kUpdThreads)
+        {
+            const int gi = c0 + i;
+            if (gi < P)
+            {
+                a.opt_v[gi] = OWN_V[i];
+                if (a.opt == kOptAdam)
+                    a.opt_m[gi] = OWN_M[i];
+            }
+        }
+    };
 
     for (int step = 0; step < a.n_steps; ++step)
     {
         CPPRL_MARK(0);
         // ---- (re)load the weight image with one TMA bulk copy per 32 KB, clear the gradient accumulator ------
-        if (tid == 0)
+        if (active)
         {
-            const uint32_t bytes = static_cast<uint32_t>(a.il.floats) * 4u;
-            // the image was written by generic-proxy stores of other CTAs (ordered by the grid barrier); make
-            // them visible to the async proxy that performs the bulk copy
-            asm volatile("fence.proxy.async;" ::: "memory");
-            mbar_expect_tx(mbar, bytes);
-            for (uint32_t off = 0; off < bytes; off += 32768u)
-                bulk_g2s(reinterpret_cast<char *>(img) + off, reinterpret_cast<const char *>(a.image) + off,
-                         min(32768u, bytes - off), mbar);
+            if (tid == 0)
+            {
+                const uint32_t bytes = static_cast<uint32_t>(a.il.floats) * 4u;
+                // the image was written by generic-proxy stores of other CTAs (ordered by the grid barrier); make
+                // them visible to the async proxy that performs the bulk copy
+                asm volatile("fence.proxy.async;" ::: "memory");
+                mbar_expect_tx(mbar, bytes);
+                for (uint32_t off = 0; off < bytes; off += 32768u)
+                    bulk_g2s(reinterpret_cast<char *>(img) + off, reinterpret_cast<const char *>(a.image) + off,
+                             min(32768u, bytes - off), mbar);
+            }
+            for (int i = tid; i < Pstride; i += kUpdThreads)
+                gsm[i] = 0.f;
+            if (!staged)
+            {
+                stage_rows(step, blockIdx.x);
+                __syncthreads();
+                stage_data();
+            }
+            staged = false;
+            mbar_wait(mbar, img_phase);
+            img_phase ^= 1u;
+            if (a.head == 1 && tid < A)
+            {
+                const float sigma = expf(img[a.il.slog + tid]); // Normal(loc, exp(scale_log))  (output_layers.cpp:54-59)
+                SIG[2 * tid] = sigma * sigma;
+                SIG[2 * tid + 1] = logf(sigma);
+            }
         }
-        for (int i = tid; i < Pstride; i += kUpdThreads)
-            gsm[i] = 0.f;
-        if (!staged && blockIdx.x < n_tiles)
-        {
-            stage_rows(step, blockIdx.x);
-            __syncthreads();
-            stage_data();
-        }
-        staged = false;
-        mbar_wait(mbar, img_phase);
-        img_phase ^= 1u;
         __syncthreads();
         const float ce_b = a.c_entropy * inv_b;
         CPPRL_MARK(1);
 
-        for (int tile = blockIdx.x; tile < n_tiles; tile += G)
+        for (int tile = blockIdx.x; active && tile < n_tiles; tile += G)
         {
             const int row0 = tile * R;
             const int nrows = min(R, a.B - row0);
-            if (tile != blockIdx.x)
+            if (tile != static_cast<int>(blockIdx.x))
             {
                 stage_rows(step, tile);
                 __syncthreads();
@@ -545,12 +634,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
             __syncthreads();
             CPPRL_MARK(4);
-            // ---- P4: log-prob, entropy, loss and its gradient w.r.t. the head outputs (one thread per row).
-            // Per-action scratch lives in the LOGIT / DLOGIT / STAT rows of shared memory (column r is private to
-            // this thread), so the loops over the runtime action count stay compact.
-            if (tid < R)
+            // ---- P4: log-prob, entropy, loss and its gradient w.r.t. the head outputs.  Four lanes per row split
+            // the actions (i = q, q+4, ...) and combine with two shuffles; per-action scratch lives in the
+            // LOGIT / DLOGIT / STAT columns of the row.
+            if (tid < 4 * R)
             {
-                const int r = tid;
+                const int r = tid >> 2, q = tid & 3;
                 const bool valid = r < nrows;
                 const bool live = training && valid;
                 float newlp = 0.f, ent = 0.f;
@@ -561,30 +650,32 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     // Categorical(logits): l = z - logsumexp(z); p = softmax(l)             (categorical.cpp:35-36)
                     act = reinterpret_cast<const int *>(ACT)[r];
                     float m = -INFINITY;
-                    for (int i = 0; i < A; ++i)
+                    for (int i = q; i < A; i += 4)
                         m = fmaxf(m, LOGIT[i * LD + r]);
+                    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
                     float se = 0.f;
-                    for (int i = 0; i < A; ++i)
+                    for (int i = q; i < A; i += 4)
                         se += expf(LOGIT[i * LD + r] - m);
+                    se += __shfl_xor_sync(0xffffffffu, se, 1);
+                    se += __shfl_xor_sync(0xffffffffu, se, 2);
                     const float lse = m + logf(se);
-                    for (int i = 0; i < A; ++i)
+                    for (int i = q; i < A; i += 4)
                     {
                         const float l = LOGIT[i * LD + r] - lse; // normalised log-probability
                         const float pr = expf(l);                // probability
                         ent -= l * pr;                           // entropy = -sum p log p        (categorical.cpp:48-52)
-                        newlp = i == act ? l : newlp;            // log_prob = gather(l, action)  (categorical.cpp:54-61)
+                        newlp += i == act ? l : 0.f;             // log_prob = gather(l, action)  (categorical.cpp:54-61)
                         LOGIT[i * LD + r] = l;
                         DLOGIT[i * LD + r] = pr;
                     }
                 }
                 else
                 {
-                    // Normal(loc, exp(scale_log))                                                (normal.cpp:24-37)
-                    for (int i = 0; i < A; ++i)
+                    // Normal(loc, sigma)                                                          (normal.cpp:24-37)
+                    for (int i = q; i < A; i += 4)
                     {
-                        const float sigma = expf(img[a.il.slog + i]);
-                        const float var = sigma * sigma;
-                        const float log_sigma = logf(sigma);
+                        const float var = SIG[2 * i], log_sigma = SIG[2 * i + 1];
                         const float diff = ACT[i * LD + r] - LOGIT[i * LD + r];
                         newlp += -(diff * diff) / (2.f * var) - log_sigma - 0.91893853320467274178f;
                         ent += 0.5f + 0.5f * 1.8378770664093454836f + log_sigma;
@@ -592,6 +683,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         STAT[(5 + i) * LD + r] = diff * diff / var - 1.f; // d logp / d scale_log
                     }
                 }
+                newlp += __shfl_xor_sync(0xffffffffu, newlp, 1);
+                newlp += __shfl_xor_sync(0xffffffffu, newlp, 2);
+                ent += __shfl_xor_sync(0xffffffffu, ent, 1);
+                ent += __shfl_xor_sync(0xffffffffu, ent, 2);
                 float g_lp = 0.f, dval = 0.f, st_v = 0.f, st_a = 0.f, st_kl = 0.f, st_clip = 0.f;
                 if (live)
                 {
@@ -622,7 +717,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
                 if (a.head == 0)
                 {
-                    for (int i = 0; i < A; ++i)
+                    for (int i = q; i < A; i += 4)
                     {
                         const float l = LOGIT[i * LD + r], pr = DLOGIT[i * LD + r];
                         const float d = g_lp * ((i == act ? 1.f : 0.f) - pr) + ce_b * pr * (l + ent);
@@ -631,26 +726,29 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
                 else
                 {
-                    for (int i = 0; i < A; ++i)
+                    for (int i = q; i < A; i += 4)
                     {
                         DLOGIT[i * LD + r] = live ? g_lp * LOGIT[i * LD + r] : 0.f;
                         STAT[(5 + i) * LD + r] = live ? g_lp * STAT[(5 + i) * LD + r] - ce_b : 0.f;
                     }
                 }
-                DVAL[r] = dval;
-                STAT[0 * LD + r] = st_v;
-                STAT[1 * LD + r] = st_a;
-                STAT[2 * LD + r] = live ? ent : 0.f;
-                STAT[3 * LD + r] = st_kl;
-                STAT[4 * LD + r] = st_clip;
+                if (q == 0)
+                {
+                    DVAL[r] = dval;
+                    STAT[0 * LD + r] = st_v;
+                    STAT[1 * LD + r] = st_a;
+                    STAT[2 * LD + r] = live ? ent : 0.f;
+                    STAT[3 * LD + r] = st_kl;
+                    STAT[4 * LD + r] = st_clip;
+                }
                 if (!training)
                 {
-                    if (valid)
+                    if (valid && q == 0)
                     {
                         a.out_value[row0 + r] = value;
                         a.out_logp[row0 + r] = newlp;
                     }
-                    const float e = warp_sum(valid ? ent : 0.f);
+                    const float e = warp_sum(valid && q == 0 ? ent : 0.f);
                     if (lane == 0)
                         atomicAdd(a.out_entropy_sum, e);
                 }
@@ -776,6 +874,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 
         CPPRL_MARK(9);
         // ---- publish this CTA's partial ----------------------------------------------------------------------
+        if (active)
         {
             float4 *dst = reinterpret_cast<float4 *>(a.gpart + static_cast<size_t>(blockIdx.x) * Pstride);
             const float4 *src = reinterpret_cast<const float4 *>(gsm);
@@ -783,27 +882,64 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 __stcg(dst + i, src[i]);
         }
         CPPRL_MARK(10);
-        grid_barrier(a.barrier, G);
-        CPPRL_MARK(11);
-
-        // ---- phase 2: statistics, KL stop, optimiser on this CTA's slice --------------------------------------
-        if (warp < 5)
+        grid_arrive(a.barrier);
+        if (tid == 0)
         {
-            const float s = block_bcast_sum_stats(a.gpart, G, Pstride, Pstat + warp, lane);
-            if (lane == 0)
-                MISC[8 + warp] = s;
-        }
-        if (tid == 32 * 5)
-        {
-            // bias corrections as host-style doubles (libtorch Adam), t = steps applied so far + 1
+            // bias corrections as host-style doubles (libtorch Adam), t = steps applied so far + 1; computed while
+            // the barrier round trip is in flight
             const double t = static_cast<double>(opt_step0 + applied + 1);
             const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t);
             const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), t);
             MISC[16] = static_cast<float>(a.lr / bc1);
             MISC[17] = static_cast<float>(sqrt(bc2));
         }
+        bar_target += G;
+        grid_wait(a.barrier, bar_target);
+        CPPRL_MARK(11);
+
+        // ---- phase 2: fixed-order reduction of the partials for this CTA's slice + the statistics slots ---------
+        // Granule = 4 consecutive floats.  Warp w sums the partials of CTAs w, w+8, ...; all of a lane's loads are
+        // issued before the first add, so the phase costs one L2 round trip.
+        const int red_ld = a.per_cta + kNumStats;
+        {
+            const int own_gran = n_own >> 2;
+            const int n_gran = own_gran + (kNumStats >> 2);
+            for (int gi = lane; gi < n_gran; gi += 32)
+            {
+                const int off = gi < own_gran ? c0 + 4 * gi : Pstat + 4 * (gi - own_gran);
+                const float4 *src = reinterpret_cast<const float4 *>(a.gpart + off);
+                float4 v[kRedMaxPer];
+#pragma unroll
+                for (int q = 0; q < kRedMaxPer; ++q)
+                {
+                    const int c = warp + kRedSplit * q;
+                    v[q] = c < n_act ? __ldcg(src + static_cast<size_t>(c) * (Pstride >> 2)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                float4 s = v[0];
+#pragma unroll
+                for (int q = 1; q < kRedMaxPer; ++q)
+                {
+                    s.x += v[q].x;
+                    s.y += v[q].y;
+                    s.z += v[q].z;
+                    s.w += v[q].w;
+                }
+                *reinterpret_cast<float4 *>(RED + warp * red_ld + 4 * gi) = s;
+            }
+        }
         __syncthreads();
-        const float sum_v = MISC[8], sum_a = MISC[9], sum_e = MISC[10], sum_kl = MISC[11], sum_clip = MISC[12];
+        float stat_sum[5];
+#pragma unroll
+        for (int s = 0; s < 5; ++s)
+        {
+            float v = 0.f;
+#pragma unroll
+            for (int w = 0; w < kRedSplit; ++w)
+                v += RED[w * red_ld + n_own + s];
+            stat_sum[s] = v;
+        }
+        const float sum_v = stat_sum[0], sum_a = stat_sum[1], sum_e = stat_sum[2], sum_kl = stat_sum[3],
+                    sum_clip = stat_sum[4];
         if (a.algo == kAlgoPPO)
         {
             const float kl = sum_kl * inv_b;
@@ -828,7 +964,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
             }
             if (stop)
+            {
+                write_back_state();
                 return; // identical decision in every CTA (same data, same summation order)
+            }
         }
         else if (blockIdx.x == 0 && tid == 0)
         {
@@ -840,67 +979,45 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         }
         CPPRL_MARK(12);
         {
-            // This CTA owns parameters [c0, c1).  Per pass of kRedChunk parameters, warp w sums the partials of
-            // CTAs w, w+8, ... (independent coalesced loads), then the eight sub-sums are added in a fixed order.
             const float step_size = MISC[16], bc2_sqrt = MISC[17];
             const float lr = static_cast<float>(a.lr);
-            const int per_cta = (P + G - 1) / G;
-            const int c0 = blockIdx.x * per_cta, c1 = min(P, c0 + per_cta);
-            for (int base = c0; base < c1; base += kRedChunk)
+            for (int i = tid; i < n_own; i += kUpdThreads)
             {
-                const int n_here = min(kRedChunk, c1 - base);
-                for (int pl = lane; pl < n_here; pl += 32)
-                {
-                    const float *src = a.gpart + base + pl;
-                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-                    int c = warp;
-                    for (; c + 3 * kRedSplit < G; c += 4 * kRedSplit)
-                    {
-                        s0 += __ldcg(src + static_cast<size_t>(c) * Pstride);
-                        s1 += __ldcg(src + static_cast<size_t>(c + kRedSplit) * Pstride);
-                        s2 += __ldcg(src + static_cast<size_t>(c + 2 * kRedSplit) * Pstride);
-                        s3 += __ldcg(src + static_cast<size_t>(c + 3 * kRedSplit) * Pstride);
-                    }
-                    for (; c < G; c += kRedSplit)
-                        s0 += __ldcg(src + static_cast<size_t>(c) * Pstride);
-                    RED[warp * kRedChunk + pl] = (s0 + s1) + (s2 + s3);
-                }
-                __syncthreads();
-                if (tid < n_here)
-                {
-                    const int i = base + tid;
-                    float g = 0.f;
+                const int gi = c0 + i;
+                if (gi >= P)
+                    continue;
+                float g = 0.f;
 #pragma unroll
-                    for (int w = 0; w < kRedSplit; ++w)
-                        g += RED[w * kRedChunk + tid];
-                    float p = a.params[i];
-                    if (a.opt == kOptAdam)
-                    {
-                        const float m = a.opt_m[i] * a.beta1 + g * (1.f - a.beta1);
-                        const float v = a.opt_v[i] * a.beta2 + (g * g) * (1.f - a.beta2);
-                        a.opt_m[i] = m;
-                        a.opt_v[i] = v;
-                        p -= step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
-                    }
-                    else
-                    {
-                        const float s = a.opt_v[i] * a.alpha + (g * g) * (1.f - a.alpha);
-                        a.opt_v[i] = s;
-                        p -= lr * (g / (sqrtf(s) + a.eps));
-                    }
-                    a.params[i] = p;
-                    image_scatter(a, a.image, i, p);
+                for (int w = 0; w < kRedSplit; ++w)
+                    g += RED[w * red_ld + i];
+                float p = OWN_P[i];
+                if (a.opt == kOptAdam)
+                {
+                    const float m = OWN_M[i] * a.beta1 + g * (1.f - a.beta1);
+                    const float v = OWN_V[i] * a.beta2 + (g * g) * (1.f - a.beta2);
+                    OWN_M[i] = m;
+                    OWN_V[i] = v;
+                    p -= step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
                 }
-                __syncthreads();
+                else
+                {
+                    const float s = OWN_V[i] * a.alpha + (g * g) * (1.f - a.alpha);
+                    OWN_V[i] = s;
+                    p -= lr * (g / (sqrtf(s) + a.eps));
+                }
+                OWN_P[i] = p;
+                a.params[gi] = p;
+                image_scatter(a, a.image, gi, p);
             }
         }
         ++applied;
         CPPRL_MARK(13);
         if (step + 1 < a.n_steps)
         {
-            // gather the next minibatch's first tile before the barrier: its global-memory latency overlaps the
-            // wait for the slowest CTA
-            if (blockIdx.x < n_tiles)
+            grid_arrive(a.barrier);
+            // gather the next minibatch's first tile while the barrier round trip is in flight (the rollout does
+            // not depend on the parameters)
+            if (active)
             {
                 stage_rows(step + 1, blockIdx.x);
                 __syncthreads();
@@ -908,10 +1025,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 staged = true;
             }
             CPPRL_MARK(14);
-            grid_barrier(a.barrier, G);
+            bar_target += G;
+            grid_wait(a.barrier, bar_target);
             CPPRL_MARK(15);
         }
     } // steps
+    if (training)
+        write_back_state();
 }
 
 template <int R>
@@ -923,6 +1043,8 @@ int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaSt
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(mlp_update_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         configured = true;
     }
+    // the grid barrier counts arrivals from zero in every launch
+    CPPRL_CUDA_TRY(cudaMemsetAsync(args.barrier, 0, sizeof(unsigned int), s));
     void *kargs[] = {const_cast<MlpUpdateArgs *>(&args)};
     CPPRL_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(mlp_update_kernel<R>), dim3(grid),
                                                dim3(kUpdThreads), kargs, smem_bytes, s));
@@ -932,14 +1054,14 @@ int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaSt
 } // namespace
 
 // ---- host-side helpers used by cabi_update.cu ------------------------------------------------------------
-size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap)
+size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
 {
-    return sizeof(float) * static_cast<size_t>(make_plan(R, img_floats, Pstride, Dp, Ap).total);
+    return sizeof(float) * static_cast<size_t>(make_plan(R, img_floats, Pstride, Dp, Ap, per_cta).total);
 }
 
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s)
 {
-    const size_t smem = mlp_update_smem_bytes(R, args.il.floats, args.po.Pstride, args.Dp, args.Ap);
+    const size_t smem = mlp_update_smem_bytes(R, args.il.floats, args.po.Pstride, args.Dp, args.Ap, args.per_cta);
     if (smem > 227 * 1024)
         return fail(CPPRL_B200_EUNSUPPORTED, "mlp_update: shared-memory plan exceeds 227 KB for this obs/action size");
     if (R == 64)

@@ -71,6 +71,8 @@ struct MlpUpdateArgs
     const long long *perm; // row ids for this launch, nullable = identity
     int B;                // rows per minibatch
     int n_steps;          // minibatches in this launch
+    int n_active;         // CTAs that own tiles and publish a gradient partial (= min(#tiles, grid))
+    int per_cta;          // parameters owned by each CTA in phase 2 (multiple of 4; grid * per_cta >= P rounded to 4)
     const double *adv_sums; // {sum, sumsq} of raw advantages over all rows (PPO), nullable
     // loss
     int algo;

@@ -13,7 +13,7 @@ from pytorch_cpp_rl_b200 import cabi
 from pytorch_cpp_rl_b200.workloads import CONFIGS
 
 NAMES = ["img+stage", "P1 L1", "P2 L2", "P3 heads", "P4 loss", "P5 head-bwd", "P6 dW2", "P7 dz1", "P8 dW1", "publish",
-         "barrier1", "stats", "reduce+opt", "stage next", "barrier2"]
+         "barrier1", "reduce", "optimiser", "arrive+stage", "barrier2 wait"]
 cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
 step = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 w = CONFIGS[cfg]
