@@ -316,7 +316,7 @@ class PPO:
         check(cabi.load().cpprl_b200_ppo_create(C.byref(self._h), policy.params.numel()))
 
     def __del__(self):
-        if getattr(self, "_h", None) and self._h.value:
+        if getattr(self, "_h", None) and self._h.value and cabi is not None:
             cabi.load().cpprl_b200_ppo_destroy(self._h)
             self._h = C.c_void_p()
 
@@ -338,17 +338,32 @@ class PPO:
 
     def update(self, rollouts: RolloutStorage, decay_level: float = 1.0, perms: Optional[torch.Tensor] = None,
                return_stats: bool = False):
+        """PPO::update (ppo.cpp:44-178).  With `perms` (host int64 [num_epoch, n]) the whole update is one C-ABI call.
+        Without, each epoch's permutation is drawn here with torch.randperm on the CPU generator exactly when the
+        reference's generator constructor would draw it (one per epoch, none after a KL early stop), while the
+        previous epoch's kernel is still running on the device."""
         lib = cabi.load()
         T, N = rollouts.num_steps, rollouts.num_processes
-        if perms is None:
-            n = N if self.policy.is_recurrent() else T * N
-            perms = torch.stack([torch.randperm(n, dtype=torch.int64) for _ in range(self.num_epoch)])
-        perms = perms.contiguous()
-        assert perms.dtype == torch.int64 and not perms.is_cuda
         pd, rd, od = self.policy.desc(), rollouts.desc(), self._options(decay_level)
         stats = cabi.PPOStats()
-        check(lib.cpprl_b200_ppo_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(perms.data_ptr()),
-                                        perms.shape[1], C.byref(stats), _stream()))
+        if perms is not None:
+            perms = perms.contiguous()
+            assert perms.dtype == torch.int64 and not perms.is_cuda
+            check(lib.cpprl_b200_ppo_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(perms.data_ptr()),
+                                            perms.shape[1], C.byref(stats), _stream()))
+        else:
+            n = N if self.policy.is_recurrent() else T * N
+            can_stop = self.kl_target * 1.5 < 1e3  # a mean log-prob difference cannot reach this: no stop possible
+            check(lib.cpprl_b200_ppo_begin(self._h, C.byref(pd), C.byref(rd), C.byref(od), _stream()))
+            for epoch in range(self.num_epoch):
+                if can_stop and epoch > 0:
+                    stopped = C.c_int()
+                    check(lib.cpprl_b200_ppo_stopped(self._h, C.byref(stopped)))
+                    if stopped.value:
+                        break
+                perm = torch.randperm(n, dtype=torch.int64)
+                check(lib.cpprl_b200_ppo_epoch(self._h, C.c_void_p(perm.data_ptr()), n))
+            check(lib.cpprl_b200_ppo_end(self._h, C.byref(stats)))
         if return_stats:
             return stats
         data = [UpdateDatum("Value loss", stats.value_loss), UpdateDatum("Action loss", stats.action_loss),
@@ -389,7 +404,7 @@ class A2C:
         check(cabi.load().cpprl_b200_a2c_create(C.byref(self._h), policy.params.numel()))
 
     def __del__(self):
-        if getattr(self, "_h", None) and self._h.value:
+        if getattr(self, "_h", None) and self._h.value and cabi is not None:
             cabi.load().cpprl_b200_a2c_destroy(self._h)
             self._h = C.c_void_p()
 

@@ -48,7 +48,8 @@ constexpr int kRedMaxPer = (148 + kRedSplit - 1) / kRedSplit; // partials one wa
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct SmemPlan
 {
-    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, red, own, sig, misc, total;
+    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, xn, actn, scn, rowidn, actin, norm, red, own, sig,
+        misc, total;
 };
 
 __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
@@ -73,6 +74,12 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.act = o, o += Ap * LD;
     p.rowid = o, o += 2 * LD; // long long per row
     p.stat = o, o += (5 + Ap) * LD; // per-row loss terms and scale_log gradients, reduced at the start of P5
+    p.xn = o, o += Dp * LD;     // staging buffers of the NEXT work item, filled by cp.async
+    p.actn = o, o += Ap * LD;
+    p.scn = o, o += 3 * LD;     // returns, old log-probs, old value predictions
+    p.rowidn = o, o += 2 * LD;  // long long per row
+    p.actin = o, o += 2 * LD;   // int64 actions (Categorical)
+    p.norm = o, o += 2 * Dp + 4; // observation normaliser: mean[Dp], sqrt(var + 1e-8)[Dp], clip
     p.red = o, o += kRedSplit * (per_cta + kNumStats); // phase-2 reduction scratch: [split][owned params + stats]
     p.own = o, o += 3 * per_cta;                       // this CTA's slice of params / Adam exp_avg / exp_avg_sq
     p.sig = o, o += 2 * Ap;                            // Normal head: {sigma^2, log sigma} per action
@@ -253,37 +260,54 @@ __device__ __forceinline__ void grad_w2(const float *__restrict__ dz, const floa
             gout[(jq + 8 * a) * kHid + kq + 16 * b] += acc[a][b].x + acc[a][b].y;
 }
 
-// dW1[j][k] += sum_r dz[j][r] * x[k][r]  (64 x D), thread owns j = u % 64 and half of the k range.
+// dW1[j][k] += sum_r dz[j][r] * x[k][r]  (64 x D).  Thread owns j in {jq + 8a} and k in {kb + kq, kb + 16 + kq}
+// for successive 32-wide blocks kb of the input features: the dz rows are broadcast loads shared by the 16 kq
+// lanes and by both k columns, so 12 LDS.128 feed 32 FFMA2 per 4 rows.
 template <int R>
 __device__ __forceinline__ void grad_w1(const float *__restrict__ dz, const float *__restrict__ x, int u, int D, int Dp,
                                         float *__restrict__ gout)
 {
     constexpr int LD = Tile<R>::LD;
-    const int j = u & 63, half = u >> 6;
-    const int k_begin = half * (Dp >> 1), k_end = k_begin + (Dp >> 1);
-    for (int kc = k_begin; kc < k_end; kc += 4)
+    const int kq = u & 15, jq = u >> 4;
+    for (int kb = 0; kb < Dp; kb += 32)
     {
-        float2 acc[4];
+        const int k0 = kb + kq, k1 = kb + 16 + kq;
+        const bool two = kb + 16 < Dp; // warp-uniform
+        const float *x0 = x + (k0 < Dp ? k0 : 0) * LD;
+        const float *x1 = x + (k1 < Dp ? k1 : 0) * LD;
+        float2 acc0[8], acc1[8];
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-            acc[kk] = make_float2(0.f, 0.f);
-#pragma unroll 4
+        for (int a = 0; a < 8; ++a)
+            acc0[a] = acc1[a] = make_float2(0.f, 0.f);
+#pragma unroll 2
         for (int r = 0; r < R; r += 4)
         {
-            const float4 av = *reinterpret_cast<const float4 *>(dz + j * LD + r);
-            const float2 alo = make_float2(av.x, av.y), ahi = make_float2(av.z, av.w);
+            const float4 xa = *reinterpret_cast<const float4 *>(x0 + r);
+            const float4 xb = two ? *reinterpret_cast<const float4 *>(x1 + r) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float2 xalo = make_float2(xa.x, xa.y), xahi = make_float2(xa.z, xa.w);
+            const float2 xblo = make_float2(xb.x, xb.y), xbhi = make_float2(xb.z, xb.w);
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
+            for (int a = 0; a < 8; ++a)
             {
-                const float4 xv = *reinterpret_cast<const float4 *>(x + (kc + kk) * LD + r);
-                acc[kk] = __ffma2_rn(alo, make_float2(xv.x, xv.y), acc[kk]);
-                acc[kk] = __ffma2_rn(ahi, make_float2(xv.z, xv.w), acc[kk]);
+                const float4 av = *reinterpret_cast<const float4 *>(dz + (jq + 8 * a) * LD + r);
+                const float2 alo = make_float2(av.x, av.y), ahi = make_float2(av.z, av.w);
+                acc0[a] = __ffma2_rn(alo, xalo, acc0[a]);
+                acc0[a] = __ffma2_rn(ahi, xahi, acc0[a]);
+                if (two)
+                {
+                    acc1[a] = __ffma2_rn(alo, xblo, acc1[a]);
+                    acc1[a] = __ffma2_rn(ahi, xbhi, acc1[a]);
+                }
             }
         }
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-            if (kc + kk < D)
-                gout[j * D + kc + kk] += acc[kk].x + acc[kk].y;
+        for (int a = 0; a < 8; ++a)
+        {
+            if (k0 < D)
+                gout[(jq + 8 * a) * D + k0] += acc0[a].x + acc0[a].y;
+            if (two && k1 < D)
+                gout[(jq + 8 * a) * D + k1] += acc1[a].x + acc1[a].y;
+        }
     }
 }
 
@@ -428,90 +452,126 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         mbar_init(mbar, 1);
     }
     const int n_tiles = (a.B + R - 1) / R;
+    float *NMEAN = smem + sp.norm, *NSTD = NMEAN + Dp, *NCLIP = NSTD + Dp;
+    for (int k = tid; k < Dp; k += kUpdThreads)
+        NMEAN[k] = 0.f, NSTD[k] = 1.f;
+    __syncthreads();
+    if (a.norm_mean)
+    {
+        // the normaliser is constant during an update (PPO refreshes it after the last epoch, A2C before the launch)
+        for (int k = tid; k < D; k += kUpdThreads)
+        {
+            NMEAN[k] = a.norm_mean[k];
+            NSTD[k] = sqrtf(a.norm_var[k] + 1e-8f);
+        }
+        if (tid == 0)
+            NCLIP[0] = a.norm_clip[0];
+    }
 
-    // stage_rows   : row ids of tile `tile` of minibatch `step` through the permutation -> ROWID
-    // stage_data   : (after a barrier) everything addressed by those ids: the normalised observation tile
-    //                feature-major, actions and per-row scalars.  Global loads are issued in batches before
-    //                their shared-memory stores so several are in flight per thread.
-    auto stage_rows = [&](int step, int tile) {
+    // ---- asynchronous gather of the NEXT work item (tile of a minibatch) -------------------------------------
+    // The rollout does not depend on the parameters, so the rows of the next tile are fetched with cp.async
+    // (LDGSTS) into a second set of staging buffers while the current tile computes:
+    //   prefetch_rowid : (top of an item) row id of the next item through the permutation -> register
+    //   prefetch_issue : (two phases later) ids -> ROWIDN, then one 4-byte cp.async per observation / action
+    //                    element and per-row scalar, global-coalesced along the row
+    //   finalize_stage : (top of the next item) wait, then normalise / clamp the observations
+    //                    (observation_normalizer.cpp:71-73) while moving them to the feature-major tile X,
+    //                    form the normalised advantage (ppo.cpp:57) and narrow the int64 actions.
+    float *XN = smem + sp.xn, *ACTN = smem + sp.actn, *SCN = smem + sp.scn;
+    long long *ROWIDN = reinterpret_cast<long long *>(smem + sp.rowidn);
+    long long *ACTIN = reinterpret_cast<long long *>(smem + sp.actin);
+    auto item_rowid = [&](int step, int tile) -> long long {
+        long long row = -1;
         if (tid < R)
         {
             const int row0 = tile * R;
-            long long row = -1;
             if (row0 + tid < a.B)
             {
                 const long long pos = static_cast<long long>(step) * a.B + row0 + tid;
                 row = a.perm ? __ldg(a.perm + pos) : pos;
             }
-            ROWID[tid] = row;
         }
+        return row;
     };
-    auto stage_data = [&]() {
-        float ret = 0.f, vold = 0.f, olp = 0.f;
-        long long act = 0;
-        const long long my_row = tid < R ? ROWID[tid] : -1;
-        if (my_row >= 0)
+    auto cp_async4 = [](float *dst, const float *src) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+    };
+    auto prefetch_issue = [&]() { // ROWIDN must be visible to every thread
         {
-            if (training)
+            constexpr int LPR = kUpdThreads / R; // lanes per row: consecutive lanes fetch consecutive elements of a row
+            const int r = tid / LPR, q = tid % LPR;
+            const long long row = ROWIDN[r];
+            if (row >= 0)
             {
-                ret = __ldg(a.returns + my_row);
-                olp = __ldg(a.old_logp + my_row);
-                if (a.adv_sums)
-                    vold = __ldg(a.value_preds + my_row);
+                const float *src = a.obs + row * D;
+                for (int k = q; k < D; k += LPR)
+                    cp_async4(XN + k * LD + r, src + k);
+                if (a.head == 1)
+                {
+                    const float *asrc = static_cast<const float *>(a.actions) + row * A;
+                    for (int k = q; k < A; k += LPR)
+                        cp_async4(ACTN + k * LD + r, asrc + k);
+                }
             }
-            if (a.head == 0)
-                act = __ldg(static_cast<const long long *>(a.actions) + my_row);
         }
-        const float clip = a.norm_mean ? __ldg(a.norm_clip) : 0.f;
-        for (int e0 = tid; e0 < Dp * R; e0 += 4 * kUpdThreads)
+        if (tid < R)
         {
-            float v[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
+            const long long row = ROWIDN[tid];
+            if (row >= 0)
             {
-                const int e = e0 + j * kUpdThreads;
-                const int k = e / R, r = e - k * R; // R is a power of two
-                v[j] = 0.f;
-                if (e < Dp * R && k < D)
+                if (training)
                 {
-                    const long long row = ROWID[r];
-                    if (row >= 0)
-                        v[j] = __ldg(a.obs + row * D + k);
+                    cp_async4(SCN + tid, a.returns + row);
+                    cp_async4(SCN + LD + tid, a.old_logp + row);
+                    if (a.adv_sums)
+                        cp_async4(SCN + 2 * LD + tid, a.value_preds + row);
                 }
+                if (a.head == 0)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(ACTIN + tid)),
+                                 "l"(static_cast<const long long *>(a.actions) + row)
+                                 : "memory");
             }
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto finalize_stage = [&](int nrows) { // nrows = valid rows of the item (row r is valid iff r < nrows)
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();
+        const float clip = a.norm_mean ? NCLIP[0] : 0.f;
+        const bool norm = a.norm_mean != nullptr;
+#pragma unroll 4
+        for (int e = tid; e < Dp * R; e += kUpdThreads)
+        {
+            const int k = e / R, r = e - k * R; // R is a power of two
+            const bool ok = k < D && r < nrows;
+            float x = XN[k * LD + r];
+            if (norm)
             {
-                const int e = e0 + j * kUpdThreads;
-                const int k = e / R, r = e - k * R;
-                if (e < Dp * R)
-                {
-                    float x = v[j];
-                    if (a.norm_mean && k < D && ROWID[r] >= 0)
-                    {
-                        // clamp((x - mean) / sqrt(var + 1e-8), -clip, clip)    (observation_normalizer.cpp:71-73)
-                        x = (x - __ldg(a.norm_mean + k)) / sqrtf(__ldg(a.norm_var + k) + 1e-8f);
-                        x = fminf(fmaxf(x, -clip), clip);
-                    }
-                    X[k * LD + r] = x;
-                }
+                x = (x - NMEAN[k]) / NSTD[k];
+                x = fminf(fmaxf(x, -clip), clip);
             }
+            X[k * LD + r] = ok ? x : 0.f;
         }
         if (a.head == 1)
+#pragma unroll 2
             for (int e = tid; e < A * R; e += kUpdThreads)
             {
                 const int k = e / R, r = e - k * R;
-                const long long row = ROWID[r];
-                ACT[k * LD + r] = row >= 0 ? __ldg(static_cast<const float *>(a.actions) + row * A + k) : 0.f;
+                ACT[k * LD + r] = r < nrows ? ACTN[k * LD + r] : 0.f;
             }
         if (tid < R)
         {
+            const bool ok = tid < nrows;
+            const float ret = ok && training ? SCN[tid] : 0.f;
+            const float olp = ok && training ? SCN[LD + tid] : 0.f;
+            const float vold = ok && training && a.adv_sums ? SCN[2 * LD + tid] : 0.f;
             RET[tid] = ret;
             OLDLP[tid] = olp;
             ADV[tid] = (ret - vold - MISC[0]) / MISC[1]; // (adv - mean) / (std + 1e-5)              (ppo.cpp:57)
             if (a.head == 0)
-                reinterpret_cast<int *>(ACT)[tid] = static_cast<int>(act);
+                reinterpret_cast<int *>(ACT)[tid] = ok ? static_cast<int>(ACTIN[tid]) : 0;
         }
+        __syncthreads();
     };
 
 #define CPPRL_MARK(slot)                                                              \
@@ -527,7 +587,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         return;
     const float inv_b = 1.f / static_cast<float>(a.B);
     uint32_t img_phase = 0;
-    bool staged = false;
+    bool staged = false; // the first work item of the next step was prefetched during this one
     // the optimiser state of this CTA's slice lives in shared memory for the whole launch; it goes back to
     // global memory on every exit path
     auto write_back_state = [&]() {
@@ -564,9 +624,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 gsm[i] = 0.f;
             if (!staged)
             {
-                stage_rows(step, blockIdx.x);
+                const long long row = item_rowid(step, blockIdx.x);
+                if (tid < R)
+                    ROWIDN[tid] = row;
                 __syncthreads();
-                stage_data();
+                prefetch_issue();
             }
             staged = false;
             mbar_wait(mbar, img_phase);
@@ -586,19 +648,21 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         {
             const int row0 = tile * R;
             const int nrows = min(R, a.B - row0);
-            if (tile != static_cast<int>(blockIdx.x))
-            {
-                stage_rows(step, tile);
-                __syncthreads();
-                stage_data();
-                __syncthreads();
-            }
+            // next work item of this CTA: the following tile of this minibatch, else its first tile of the next one
+            int nstep = step, ntile = tile + G;
+            if (ntile >= n_tiles)
+                nstep = step + 1, ntile = blockIdx.x;
+            const bool has_next = nstep < a.n_steps;
+            finalize_stage(nrows); // the rows of THIS item are in place (waits for their cp.async group)
+            const long long next_row = has_next ? item_rowid(nstep, ntile) : -1;
             // ---- P1: layer 1, both towers ------------------------------------------------------------
             {
                 float acc[4][Tile<R>::NG * 4];
                 gemm_cf<R>(w1t_img, X, Dp, jb, rb, acc);
                 store_tanh<R>(h1t, b1_img, jb, rb, acc);
             }
+            if (tid < R)
+                ROWIDN[tid] = next_row; // read by prefetch_issue after the next barrier
             __syncthreads();
             CPPRL_MARK(2);
             // ---- P2: layer 2 ---------------------------------------------------------------------------
@@ -608,6 +672,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 store_tanh<R>(h2t, b2_img, jb, rb, acc);
             }
             __syncthreads();
+            if (has_next)
+            {
+                prefetch_issue(); // lands during P3..P8 (and phase 2 when it belongs to the next minibatch)
+                staged = nstep != step;
+            }
             CPPRL_MARK(3);
             // ---- P3: heads: logits / loc [A][R] from the actor tower, value [R] from the critic tower ----
             for (int e = tid; e < (A + 1) * R; e += kUpdThreads)
@@ -965,6 +1034,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
             if (stop)
             {
+                asm volatile("cp.async.wait_all;" ::: "memory");
                 write_back_state();
                 return; // identical decision in every CTA (same data, same summation order)
             }
@@ -1015,15 +1085,6 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         if (step + 1 < a.n_steps)
         {
             grid_arrive(a.barrier);
-            // gather the next minibatch's first tile while the barrier round trip is in flight (the rollout does
-            // not depend on the parameters)
-            if (active)
-            {
-                stage_rows(step + 1, blockIdx.x);
-                __syncthreads();
-                stage_data();
-                staged = true;
-            }
             CPPRL_MARK(14);
             bar_target += G;
             grid_wait(a.barrier, bar_target);

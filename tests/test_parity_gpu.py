@@ -345,7 +345,7 @@ def test_ppo_update_cfg3_full(ref):
     # statistics are means over the 320 steps: the CUDA path is as close to float64 as the reference is
     for i in range(5):
         d_ref, d_gpu = abs(want_stats[i] - stats64[i]), abs(got_stats[i] - stats64[i])
-        assert d_gpu <= 2.0 * d_ref + 1e-4 * abs(stats64[i]) + 1e-6, (i, got_stats[i], want_stats[i], stats64[i])
+        assert d_gpu <= 2.0 * d_ref + 1e-4 * abs(stats64[i]) + 5e-6, (i, got_stats[i], want_stats[i], stats64[i])
 
 
 @pytest.mark.parametrize("seed", [0, 1])
