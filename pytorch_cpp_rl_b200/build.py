@@ -79,10 +79,58 @@ def build_kernels(force: bool = False, verbose: bool = False, ptxas_info: bool =
     return KERNEL_LIB
 
 
+HOST_LIB = LIB / "libcpprl_host.so"
+HOST_SRC = PKG / "host"
+CXX = os.environ.get("CXX", "g++")
+
+
+def torch_paths():
+    import torch
+    t = Path(torch.__file__).resolve().parent
+    return t, [t / "include", t / "include" / "torch" / "csrc" / "api" / "include"], t / "lib"
+
+
+def host_cxxflags():
+    _, incs, _ = torch_paths()
+    flags = ["-O2", "-std=c++17", "-fPIC", "-w", "-D_GLIBCXX_USE_CXX11_ABI=1", "-I", INCLUDE, "-I", HOST_SRC,
+             "-I", "/usr/local/cuda/include"]
+    for i in incs:
+        flags += ["-I", i]
+    return flags
+
+
+def host_ldflags():
+    _, _, tlib = torch_paths()
+    return ["-L", LIB, "-lcpprl_b200", "-L", tlib, "-ltorch", "-ltorch_cpu", "-lc10", "-lc10_cuda", "-ltorch_cuda",
+            f"-Wl,-rpath,{tlib}", "-Wl,-rpath,$ORIGIN", "-Wl,--no-as-needed"]
+
+
+def build_host(force: bool = False, verbose: bool = False) -> Path:
+    """The C++ drop-in (namespace cpprl, include/cpprl/*.h) over the C ABI: lib/libcpprl_host.so."""
+    build_kernels(force=False, verbose=verbose)
+    srcs = sorted(HOST_SRC.glob("*.cpp"))
+    headers = list(HOST_SRC.glob("*.h")) + list(INCLUDE.rglob("*.h"))
+    if not force and _newer(HOST_LIB, srcs + headers + [Path(__file__), KERNEL_LIB]):
+        return HOST_LIB
+    objs, jobs = [], []
+    for src in srcs:
+        obj = OBJ / ("host_" + src.stem + ".o")
+        objs.append(obj)
+        if force or not _newer(obj, [src] + headers + [Path(__file__)]):
+            jobs.append([CXX, *host_cxxflags(), "-c", src, "-o", obj])
+    with ThreadPoolExecutor(max_workers=min(8, max(1, len(jobs)))) as ex:
+        list(ex.map(lambda c: _run(c, verbose), jobs))
+    _run([CXX, "-shared", "-o", HOST_LIB, *objs, *host_ldflags()], verbose)
+    return HOST_LIB
+
+
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_kernels(force=force, verbose=verbose)
+    build_host(force=force, verbose=verbose)
 
 
 if __name__ == "__main__":
     build_kernels(force="--force" in sys.argv, verbose=True, ptxas_info="--ptxas" in sys.argv)
     print(f"built {KERNEL_LIB}")
+    if "--host" in sys.argv:
+        print(f"built {build_host(force='--force' in sys.argv, verbose=True)}")
