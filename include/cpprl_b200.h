@@ -260,6 +260,32 @@ int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_policy *poli
                                 void *stream);
 int cpprl_b200_a2c_fetch_stats(cpprl_b200_a2c *h, cpprl_b200_a2c_stats *stats);
 
+/* ---- (e) multi-GPU: rollouts sharded by environment over the GPUs of one box -----------------------------
+ * The reference has no distributed path; this is new.  One process per GPU; rank r
+ * holds environments [env_offset, env_offset + N_local) of a GLOBAL rollout of global_envs environments, all T steps.
+ * Semantics are those of ONE reference process over the global rollout: minibatch k of an epoch is rows
+ * perm[k*mbs .. (k+1)*mbs) of the GLOBAL permutation over flat ids t*global_envs + env (every rank passes the same
+ * permutation, length T*global_envs); each rank processes the ids whose environment it owns, every mean divides by
+ * the global count, and the per-minibatch gradient (with the loss / KL partial sums appended) is all-reduced INSIDE
+ * the fused update kernel over NVLink peer memory: CTA b of every rank publishes its slice in an exchange area
+ * mapped into its peers (CUDA IPC), waits for the b-th flag of each peer and adds the records in rank order — all
+ * ranks take bit-identical optimiser steps and the same KL-stop decision.  The advantage moments (ppo.cpp:57) and the
+ * RunningMeanStd batch moments (running_mean_std.cpp:20-43) are merged the same way.
+ * Setup: comm_create on every rank -> comm_export (64-byte handle) -> exchange the handles with any host transport
+ * (torch.distributed all_gather in the Python mirror) -> comm_connect(world x 64 bytes, rank order). */
+typedef struct cpprl_b200_comm cpprl_b200_comm; /* opaque */
+int cpprl_b200_comm_create(cpprl_b200_comm **out, int rank, int world, int64_t max_params);
+int cpprl_b200_comm_export(cpprl_b200_comm *c, void *handle_out_64_bytes);
+int cpprl_b200_comm_connect(cpprl_b200_comm *c, const void *handles_world_x_64_bytes);
+int cpprl_b200_comm_info(const cpprl_b200_comm *c, int *rank, int *world);
+void cpprl_b200_comm_destroy(cpprl_b200_comm *c);
+/* comm == NULL switches back to the single-GPU update. */
+int cpprl_b200_ppo_set_comm(cpprl_b200_ppo *h, cpprl_b200_comm *comm, int64_t env_offset, int64_t global_envs);
+int cpprl_b200_a2c_set_comm(cpprl_b200_a2c *h, cpprl_b200_comm *comm, int64_t global_envs);
+/* RunningMeanStd update whose batch is the union of every rank's rows x [M_local, D]. */
+int cpprl_b200_rms_update_sharded(cpprl_b200_comm *comm, const float *d_x, int64_t M, int64_t D, float *d_count,
+                                  float *d_mean, float *d_var, void *d_workspace, void *stream);
+
 /* ---- timing hooks ---------------------------------------------------------------------------------
  * The fused kernels record CUDA events on the caller's stream around each launch; these return the
  * accumulated device time and launch count of the named kernel family since the last reset

@@ -290,6 +290,52 @@ def rmsprop_step(params, grads, square_avg, lr: float, alpha: float = 0.99, eps:
 
 
 # ---------------------------------------------------------------------------------------------------
+# multi-GPU: environments sharded over the GPUs of one box (include/cpprl_b200.h, section (e))
+# ---------------------------------------------------------------------------------------------------
+def shard_range(num_envs: int, rank: int, world: int):
+    """Environments [lo, hi) owned by `rank`: contiguous, sizes differ by at most one."""
+    base, extra = divmod(num_envs, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def exchange_handles(handle: bytes, group=None):
+    """All-gather the 64-byte IPC handles of every rank's exchange area (torch.distributed; any backend)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    backend = dist.get_backend(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+    out = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(out, mine, group=group)
+    return b"".join(bytes(t.cpu().tolist()) for t in out)
+
+
+class Communicator:
+    """One per rank (one process per GPU).  Owns the peer-mapped exchange area the fused update kernel reduces
+    gradients through; torch.distributed is only used to hand the IPC handles around."""
+
+    def __init__(self, max_params: int, group=None):
+        import torch.distributed as dist
+        distributed = dist.is_available() and dist.is_initialized()
+        self.rank, self.world = (dist.get_rank(group), dist.get_world_size(group)) if distributed else (0, 1)
+        lib = cabi.load()
+        self._h = C.c_void_p()
+        check(lib.cpprl_b200_comm_create(C.byref(self._h), self.rank, self.world, max_params))
+        if self.world > 1:
+            buf = C.create_string_buffer(64)
+            check(lib.cpprl_b200_comm_export(self._h, buf))
+            self._handles = exchange_handles(buf.raw, group)
+            check(lib.cpprl_b200_comm_connect(self._h, C.c_char_p(self._handles)))
+            dist.barrier(group)
+
+    def __del__(self):
+        if getattr(self, "_h", None) and self._h.value and cabi is not None:
+            cabi.load().cpprl_b200_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+# ---------------------------------------------------------------------------------------------------
 # algorithms
 # ---------------------------------------------------------------------------------------------------
 @dataclass
@@ -331,6 +377,12 @@ class PPO:
         o.epsilon, o.kl_target = self.epsilon, self.kl_target
         return o
 
+    def set_communicator(self, comm: Optional["Communicator"], env_offset: int = 0, global_envs: int = 0):
+        """Env-sharded update: this rank's storage holds envs [env_offset, env_offset + N) of `global_envs`;
+        permutations passed to update() are then over the GLOBAL rollout (T * global_envs ids)."""
+        self._comm, self._global_envs = comm, global_envs
+        check(cabi.load().cpprl_b200_ppo_set_comm(self._h, comm._h if comm else None, env_offset, global_envs))
+
     def optimizer_state(self):
         m, v, step = C.c_void_p(), C.c_void_p(), C.c_int64()
         check(cabi.load().cpprl_b200_ppo_state(self._h, C.byref(m), C.byref(v), C.byref(step)))
@@ -352,7 +404,7 @@ class PPO:
             check(lib.cpprl_b200_ppo_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(perms.data_ptr()),
                                             perms.shape[1], C.byref(stats), _stream()))
         else:
-            n = N if self.policy.is_recurrent() else T * N
+            n = N if self.policy.is_recurrent() else T * (getattr(self, "_global_envs", 0) or N)
             can_stop = self.kl_target * 1.5 < 1e3  # a mean log-prob difference cannot reach this: no stop possible
             check(lib.cpprl_b200_ppo_begin(self._h, C.byref(pd), C.byref(rd), C.byref(od), _stream()))
             for epoch in range(self.num_epoch):
@@ -407,6 +459,10 @@ class A2C:
         if getattr(self, "_h", None) and self._h.value and cabi is not None:
             cabi.load().cpprl_b200_a2c_destroy(self._h)
             self._h = C.c_void_p()
+
+    def set_communicator(self, comm: Optional["Communicator"], global_envs: int = 0):
+        self._comm = comm
+        check(cabi.load().cpprl_b200_a2c_set_comm(self._h, comm._h if comm else None, global_envs))
 
     def _options(self, decay_level: float) -> cabi.A2COptions:
         import numpy as np

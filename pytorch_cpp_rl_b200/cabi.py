@@ -99,6 +99,14 @@ SIGNATURES = {
     "cpprl_b200_a2c_update": (C.c_int, [C.c_void_p, C.POINTER(Policy), C.POINTER(Rollout), C.POINTER(A2COptions), C.POINTER(A2CStats), C.c_void_p]),
     "cpprl_b200_a2c_update_async": (C.c_int, [C.c_void_p, C.POINTER(Policy), C.POINTER(Rollout), C.POINTER(A2COptions), C.c_void_p]),
     "cpprl_b200_a2c_fetch_stats": (C.c_int, [C.c_void_p, C.POINTER(A2CStats)]),
+    "cpprl_b200_comm_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int64]),
+    "cpprl_b200_comm_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cpprl_b200_comm_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "cpprl_b200_comm_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "cpprl_b200_comm_destroy": (None, [C.c_void_p]),
+    "cpprl_b200_ppo_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
+    "cpprl_b200_a2c_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
+    "cpprl_b200_rms_update_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64] + [C.c_void_p] * 5),
     "cpprl_b200_kernel_time_ms": (C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cpprl_b200_kernel_time_reset": (None, []),
     "cpprl_b200_kernel_time_enable": (None, [C.c_int]),

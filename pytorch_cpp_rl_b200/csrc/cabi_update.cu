@@ -9,6 +9,8 @@
 #include "common.cuh"
 #include "mlp_update.cuh"
 
+struct cpprl_b200_comm;
+
 namespace cpprl_b200
 {
 // from mlp_update.cu / returns_scan.cu
@@ -16,6 +18,14 @@ size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap,
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s);
 int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums,
                              cudaStream_t s);
+int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean, float *d_var,
+                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s);
+int launch_shard_permutation(const int64_t *d_perm, int64_t n_mb, int64_t B, int64_t n_global, int64_t env0,
+                             int64_t n_local, int64_t *d_out, int *d_counts, cudaStream_t s);
+CommView comm_view(const cpprl_b200_comm *c);
+unsigned int *comm_step_seq(cpprl_b200_comm *c);
+unsigned int *comm_update_seq(cpprl_b200_comm *c);
+double *comm_local_adv(cpprl_b200_comm *c);
 
 namespace
 {
@@ -248,6 +258,12 @@ struct cpprl_b200_ppo
     int64_t mbs = 0, n_mb = 0;
     int epoch = 0;
     int64_t host_step = 0;
+    // env-sharded (multi-GPU) update: this rank holds envs [env_offset, env_offset + rollout.N) of global_envs
+    cpprl_b200_comm *comm = nullptr;
+    int64_t env_offset = 0, global_envs = 0;
+    int64_t *d_lperm = nullptr; // the global permutation compacted to this rank's rows, [n_mb][mbs]
+    int *d_counts = nullptr;    // rows of each minibatch owned by this rank
+    size_t lperm_cap = 0, counts_cap = 0;
 };
 
 extern "C" int cpprl_b200_ppo_create(cpprl_b200_ppo **out, int64_t n_params)
@@ -288,6 +304,7 @@ extern "C" void cpprl_b200_ppo_destroy(cpprl_b200_ppo *h)
     if (!h)
         return;
     cudaFree(h->d_m), cudaFree(h->d_v);
+    cudaFree(h->d_lperm), cudaFree(h->d_counts);
     for (int b = 0; b < 2; ++b)
     {
         cudaFree(h->d_perm[b]);
@@ -319,6 +336,20 @@ extern "C" int cpprl_b200_ppo_state(cpprl_b200_ppo *h, float **d_exp_avg, float 
     return 0;
 }
 
+extern "C" int cpprl_b200_ppo_set_comm(cpprl_b200_ppo *h, cpprl_b200_comm *comm, int64_t env_offset, int64_t global_envs)
+{
+    if (!h)
+        return fail(CPPRL_B200_EINVAL, "ppo_set_comm: null handle");
+    if (h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_set_comm called inside an update");
+    if (comm && (env_offset < 0 || global_envs <= 0))
+        return fail(CPPRL_B200_EINVAL, "ppo_set_comm: bad environment range");
+    h->comm = comm;
+    h->env_offset = env_offset;
+    h->global_envs = global_envs;
+    return 0;
+}
+
 extern "C" int cpprl_b200_ppo_set_step(cpprl_b200_ppo *h, int64_t step)
 {
     if (!h || step < 0)
@@ -347,9 +378,14 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         return fail(CPPRL_B200_EINVAL, "ppo_update: non-positive rollout size");
     if (opt->num_epoch < 0 || opt->num_mini_batch <= 0)
         return fail(CPPRL_B200_EINVAL, "ppo_update: bad epoch / minibatch count");
-    const int64_t rows = ro->T * ro->N;
+    const bool sharded = h->comm != nullptr;
+    const int64_t n_envs = sharded ? h->global_envs : ro->N; // minibatches are defined on the GLOBAL rollout
+    if (sharded && (h->env_offset < 0 || h->env_offset + ro->N > h->global_envs))
+        return fail(CPPRL_B200_EINVAL, "ppo_update: this rank's environment range lies outside the global rollout");
+    const int64_t rows = ro->T * n_envs;
+    const int64_t local_rows = ro->T * ro->N;
     if (rows < opt->num_mini_batch)
-        return fail(CPPRL_B200_EINVAL, "PPO needs the number of processes (" + std::to_string(ro->N) +
+        return fail(CPPRL_B200_EINVAL, "PPO needs the number of processes (" + std::to_string(n_envs) +
                                            ") * the number of steps (" + std::to_string(ro->T) + ") = " +
                                            std::to_string(rows) +
                                            " to be greater than or equal to the number of minibatches (" +
@@ -374,8 +410,25 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
     const ImageLayout il = make_image_layout(Dp, Ap);
-    if (int rc = choose_plan(mbs, il, po, Dp, Ap, true, h->plan))
+    const CommView view = comm_view(h->comm);
+    // sharded: tiles are sized for the expected local share of a minibatch; the grid (identical on every rank, CTA b
+    // pairs with CTA b of the peers) covers the whole box-wide slice of parameters, and ragged minibatches that
+    // exceed it simply take more than one tile per CTA
+    const int64_t plan_rows = sharded ? (mbs + view.world - 1) / view.world : mbs;
+    if (int rc = choose_plan(plan_rows, il, po, Dp, Ap, true, h->plan))
         return rc;
+    if (sharded)
+    {
+        const int sms = sm_count();
+        h->plan.grid = std::min(sms, std::max(h->plan.grid, static_cast<int>(std::min<int64_t>(sms, (plan_rows * 5 / 4 + h->plan.R - 1) / h->plan.R))));
+        h->plan.grid = std::max(h->plan.grid, std::min(16, sms));
+        h->plan.n_active = h->plan.grid;
+        h->plan.per_cta = round_up((po.Pstride - kNumStats + h->plan.grid - 1) / h->plan.grid, 4);
+        if (mlp_update_smem_bytes(h->plan.R, il.floats, po.Pstride, Dp, Ap, h->plan.per_cta) > 227 * 1024)
+            return fail(CPPRL_B200_EUNSUPPORTED, "update: observation / action size needs more than 227 KB of shared memory");
+        if (static_cast<int64_t>(h->plan.grid) * (h->plan.per_cta + kNumStats) > view.x_stride)
+            return fail(CPPRL_B200_EINVAL, "ppo_update: the communicator was created for fewer parameters than this policy has");
+    }
     const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
     if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(h->plan.n_active) * po.Pstride, rms_ws))
         return rc;
@@ -389,12 +442,19 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     a.value_preds = ro->d_value_preds;
     a.returns = ro->d_returns;
     a.old_logp = ro->d_action_log_probs;
-    a.rows = rows;
+    a.rows = local_rows;
+    a.rows_norm = rows;
     a.B = static_cast<int>(mbs);
+    a.B_norm = static_cast<int>(mbs);
+    a.perm_stride = mbs;
+    a.step_rows = nullptr;
+    a.comm = view;
     a.n_steps = static_cast<int>(h->n_mb);
     a.n_active = h->plan.n_active;
     a.per_cta = h->plan.per_cta;
-    a.adv_sums = h->scratch.adv_sums;
+    a.adv_sums = sharded ? comm_local_adv(h->comm) : h->scratch.adv_sums;
+    if (sharded)
+        a.adv_seq = ++*comm_update_seq(h->comm);
     a.algo = kAlgoPPO;
     a.clip_param = opt->clip_param;
     // clamp(ratio, 1.0 - clip, 1.0 + clip): bounds formed in double, applied to a float tensor (ppo.cpp:111-113)
@@ -420,8 +480,8 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
     reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
     CPPRL_LAUNCH_CHECK("reset_state_kernel");
-    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 4 * sizeof(double), s));
-    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, rows, h->scratch.adv_sums, s))
+    CPPRL_CUDA_TRY(cudaMemsetAsync(const_cast<double *>(a.adv_sums), 0, 2 * sizeof(double), s));
+    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, const_cast<double *>(a.adv_sums), s))
         return rc;
     h->active = true;
     return 0;
@@ -437,6 +497,35 @@ extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
 
 static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
+    if (h->comm)
+    {
+        // compact the global permutation to the rows this rank owns (stable, one CTA per minibatch)
+        const size_t need = static_cast<size_t>(h->mbs * h->n_mb);
+        if (need > h->lperm_cap)
+        {
+            CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+            cudaFree(h->d_lperm);
+            h->d_lperm = nullptr;
+            CPPRL_CUDA_TRY(cudaMalloc(&h->d_lperm, need * sizeof(int64_t)));
+            h->lperm_cap = need;
+        }
+        if (static_cast<size_t>(h->n_mb) > h->counts_cap)
+        {
+            CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+            cudaFree(h->d_counts);
+            h->d_counts = nullptr;
+            CPPRL_CUDA_TRY(cudaMalloc(&h->d_counts, h->n_mb * sizeof(int)));
+            h->counts_cap = h->n_mb;
+        }
+        if (int rc = launch_shard_permutation(d_perm, h->n_mb, h->mbs, h->global_envs, h->env_offset, h->rollout.N,
+                                              h->d_lperm, h->d_counts, h->stream))
+            return rc;
+        d_perm = h->d_lperm;
+        h->args.step_rows = h->d_counts;
+        unsigned int *seq = comm_step_seq(h->comm);
+        h->args.xseq0 = *seq;
+        *seq += static_cast<unsigned int>(h->n_mb);
+    }
     h->args.perm = reinterpret_cast<const long long *>(d_perm);
     h->args.dbg_clocks = g_dbg_clocks;
     h->args.dbg_step = g_dbg_step;
@@ -525,8 +614,8 @@ extern "C" int cpprl_b200_ppo_end_async(cpprl_b200_ppo *h)
     {
         // finish_update: the normaliser sees ALL (T+1)*N observation rows (ppo.cpp:149-154)
         const int64_t M = (h->rollout.T + 1) * h->rollout.N;
-        if (int rc = cpprl_b200_rms_update(h->rollout.d_observations, M, p.obs_dim, p.d_norm_count, p.d_norm_mean,
-                                           p.d_norm_var, h->scratch.rms_ws, h->stream))
+        if (int rc = launch_rms_update(h->rollout.d_observations, M, p.obs_dim, p.d_norm_count, p.d_norm_mean,
+                                       p.d_norm_var, h->scratch.rms_ws, h->comm, h->stream))
             return rc;
     }
     CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, h->stream));
@@ -540,6 +629,8 @@ extern "C" int cpprl_b200_ppo_fetch_stats(cpprl_b200_ppo *h, cpprl_b200_ppo_stat
         return fail(CPPRL_B200_EINVAL, "ppo_fetch_stats: null argument");
     CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
     const UpdateState &st = *h->h_state;
+    if (st.comm_error)
+        return fail(CPPRL_B200_ENCCL, "ppo_update: a peer rank never published its exchange record (bounded wait expired)");
     const float n = static_cast<float>(st.num_updates);
     // means over the applied updates; 0/0 = NaN when the first minibatch tripped the KL stop (ppo.cpp:156-159)
     stats->value_loss = st.total_value_loss / n;
@@ -587,6 +678,8 @@ struct cpprl_b200_a2c
     Scratch scratch;
     UpdateState *h_state = nullptr;
     cudaStream_t stream = nullptr;
+    cpprl_b200_comm *comm = nullptr;
+    int64_t global_envs = 0;
 };
 
 extern "C" int cpprl_b200_a2c_create(cpprl_b200_a2c **out, int64_t n_params)
@@ -624,6 +717,15 @@ extern "C" void cpprl_b200_a2c_destroy(cpprl_b200_a2c *h)
     delete h;
 }
 
+extern "C" int cpprl_b200_a2c_set_comm(cpprl_b200_a2c *h, cpprl_b200_comm *comm, int64_t global_envs)
+{
+    if (!h || (comm && global_envs <= 0))
+        return fail(CPPRL_B200_EINVAL, "a2c_set_comm: bad arguments");
+    h->comm = comm;
+    h->global_envs = global_envs;
+    return 0;
+}
+
 extern "C" int cpprl_b200_a2c_state(cpprl_b200_a2c *h, float **d_square_avg)
 {
     if (!h || !d_square_avg)
@@ -648,7 +750,9 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     if (ro->T <= 0 || ro->N <= 0)
         return fail(CPPRL_B200_EINVAL, "a2c_update: non-positive rollout size");
     const int64_t rows = ro->T * ro->N;
-    if (rows > 0x7fffffffll)
+    const bool sharded = h->comm != nullptr;
+    const int64_t rows_global = sharded ? ro->T * h->global_envs : rows;
+    if (rows_global > 0x7fffffffll)
         return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: more than 2^31 rows");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->stream = s;
@@ -661,6 +765,14 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     Plan plan;
     if (int rc = choose_plan(rows, il, po, Dp, Ap, true, plan))
         return rc;
+    const CommView view = comm_view(h->comm);
+    if (sharded)
+    {
+        // identical grid on every rank (CTA b pairs with CTA b of the peers); shards have equal shapes
+        plan.n_active = plan.grid;
+        if (static_cast<int64_t>(plan.grid) * (plan.per_cta + kNumStats) > view.x_stride)
+            return fail(CPPRL_B200_EINVAL, "a2c_update: the communicator was created for fewer parameters than this policy has");
+    }
     const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
     if (int rc = h->scratch.ensure(il.floats, static_cast<size_t>(plan.n_active) * po.Pstride, rms_ws))
         return rc;
@@ -669,8 +781,8 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     if (policy->d_norm_mean)
     {
         // the normaliser is updated BEFORE the forward pass (a2c.cpp:52-55)
-        if (int rc = cpprl_b200_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
-                                           policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, s))
+        if (int rc = launch_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
+                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, h->comm, s))
             return rc;
     }
     MlpUpdateArgs a;
@@ -685,6 +797,17 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.rows = rows;
     a.perm = nullptr;
     a.B = static_cast<int>(rows);
+    a.B_norm = static_cast<int>(rows_global);
+    a.rows_norm = rows_global;
+    a.perm_stride = rows;
+    a.step_rows = nullptr;
+    a.comm = view;
+    if (sharded)
+    {
+        unsigned int *seq = comm_step_seq(h->comm);
+        a.xseq0 = *seq;
+        *seq += 1u;
+    }
     a.n_steps = 1;
     a.n_active = plan.n_active;
     a.per_cta = plan.per_cta;
@@ -716,6 +839,8 @@ extern "C" int cpprl_b200_a2c_fetch_stats(cpprl_b200_a2c *h, cpprl_b200_a2c_stat
     if (!h || !stats)
         return fail(CPPRL_B200_EINVAL, "a2c_fetch_stats: null argument");
     CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    if (h->h_state->comm_error)
+        return fail(CPPRL_B200_ENCCL, "a2c_update: a peer rank never published its exchange record (bounded wait expired)");
     stats->value_loss = h->h_state->a2c_value_loss;
     stats->action_loss = h->h_state->a2c_action_loss;
     stats->entropy = h->h_state->a2c_entropy;
@@ -785,6 +910,10 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     a.n_steps = 1;
     a.n_active = plan.n_active;
     a.per_cta = 0;
+    a.B_norm = static_cast<int>(B);
+    a.rows_norm = B;
+    a.perm_stride = B;
+    a.comm.world = 1;
     a.algo = kAlgoForward;
     a.barrier = g_eval_scratch.barrier;
     a.out_value = d_value;

@@ -409,8 +409,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
     const int D = a.D, Dp = a.Dp, A = a.A;
     const bool training = a.algo != kAlgoForward;
-    const bool active = static_cast<int>(blockIdx.x) < a.n_active; // owns tiles, publishes a partial
-    const int n_act = a.n_active;
+    // rows / tiles / publishing CTAs of minibatch `step` (ragged when the rollout is sharded by environment)
+    auto rows_of = [&](int step) { return a.step_rows ? __ldg(a.step_rows + step) : a.B; };
+    const int world = a.comm.world, my_rank = a.comm.rank;
     // phase-2 ownership: parameters [c0, c0 + n_own) of the flat vector (n_own a multiple of 4, may be 0)
     const int c0 = min(Pstat, static_cast<int>(blockIdx.x) * a.per_cta);
     const int n_own = min(Pstat, c0 + a.per_cta) - c0;
@@ -439,9 +440,25 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         float mean = 0.f, denom = 1.f;
         if (a.adv_sums)
         {
-            const double cnt = static_cast<double>(a.rows);
-            const double m = a.adv_sums[0] / cnt;
-            double var = (a.adv_sums[1] - a.adv_sums[0] * m) / (cnt - 1.0); // unbiased (ppo.cpp:57)
+            double s1 = a.adv_sums[0], s2 = a.adv_sums[1];
+            if (world > 1)
+            {
+                // global moments: every rank publishes its shard's sums once per update (CTA 0), reads all of them in
+                // rank order (identical value everywhere)
+                if (blockIdx.x == 0)
+                    flag_publish(&a.comm.area[my_rank]->adv_flag, a.adv_seq);
+                s1 = 0.0, s2 = 0.0;
+                for (int r = 0; r < world; ++r)
+                {
+                    if (r != my_rank && !flag_wait(&a.comm.area[r]->adv_flag, a.adv_seq))
+                        a.state->comm_error = 1;
+                    s1 += r == my_rank ? a.adv_sums[0] : peer_load(a.comm.area[r]->adv);
+                    s2 += r == my_rank ? a.adv_sums[1] : peer_load(a.comm.area[r]->adv + 1);
+                }
+            }
+            const double cnt = static_cast<double>(a.rows_norm);
+            const double m = s1 / cnt;
+            double var = (s2 - s1 * m) / (cnt - 1.0); // unbiased (ppo.cpp:57)
             if (var < 0.0)
                 var = 0.0;
             mean = static_cast<float>(m);
@@ -451,7 +468,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         MISC[1] = denom;
         mbar_init(mbar, 1);
     }
-    const int n_tiles = (a.B + R - 1) / R;
+    const int n_tiles_max = (a.B + R - 1) / R;
+    (void)n_tiles_max;
     float *NMEAN = smem + sp.norm, *NSTD = NMEAN + Dp, *NCLIP = NSTD + Dp;
     for (int k = tid; k < Dp; k += kUpdThreads)
         NMEAN[k] = 0.f, NSTD[k] = 1.f;
@@ -485,9 +503,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         if (tid < R)
         {
             const int row0 = tile * R;
-            if (row0 + tid < a.B)
+            if (row0 + tid < rows_of(step))
             {
-                const long long pos = static_cast<long long>(step) * a.B + row0 + tid;
+                const long long pos = static_cast<long long>(step) * a.perm_stride + row0 + tid;
                 row = a.perm ? __ldg(a.perm + pos) : pos;
             }
         }
@@ -585,7 +603,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     grid_wait(a.barrier, bar_target);
     if (stopped)
         return;
-    const float inv_b = 1.f / static_cast<float>(a.B);
+    const float inv_b = 1.f / static_cast<float>(a.B_norm);
     uint32_t img_phase = 0;
     bool staged = false; // the first work item of the next step was prefetched during this one
     // the optimiser state of this CTA's slice lives in shared memory for the whole launch; it goes back to
@@ -605,6 +623,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 
     for (int step = 0; step < a.n_steps; ++step)
     {
+        const int n_tiles = (rows_of(step) + R - 1) / R;
+        const int n_act = min(n_tiles, G);
+        const bool active = static_cast<int>(blockIdx.x) < n_act; // owns tiles of this minibatch, publishes a partial
         CPPRL_MARK(0);
         // ---- (re)load the weight image with one TMA bulk copy per 32 KB, clear the gradient accumulator ------
         if (active)
@@ -647,12 +668,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         for (int tile = blockIdx.x; active && tile < n_tiles; tile += G)
         {
             const int row0 = tile * R;
-            const int nrows = min(R, a.B - row0);
+            const int nrows = min(R, rows_of(step) - row0);
             // next work item of this CTA: the following tile of this minibatch, else its first tile of the next one
             int nstep = step, ntile = tile + G;
             if (ntile >= n_tiles)
                 nstep = step + 1, ntile = blockIdx.x;
-            const bool has_next = nstep < a.n_steps;
+            const bool has_next = nstep < a.n_steps && (nstep == step || ntile * R < rows_of(nstep));
             finalize_stage(nrows); // the rows of THIS item are in place (waits for their cp.async group)
             const long long next_row = has_next ? item_rowid(nstep, ntile) : -1;
             // ---- P1: layer 1, both towers ------------------------------------------------------------
@@ -997,16 +1018,48 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
         }
         __syncthreads();
+        // fold the split rows into row 0: RED[i] = gradient of owned parameter i (i < n_own) / statistic i - n_own
+        for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
+        {
+            float g = 0.f;
+#pragma unroll
+            for (int w = 0; w < kRedSplit; ++w)
+                g += RED[w * red_ld + i];
+            RED[i] = g;
+        }
+        __syncthreads();
+        if (world > 1)
+        {
+            // ---- gradient all-reduce across the GPUs of the box, inside the kernel, over NVLink peer memory ------
+            // CTA b of every rank owns the same slice of the parameter vector: it publishes its rank-local sums in its
+            // own exchange area, waits for the b-th flag of every peer, and adds the R records in rank order, so all
+            // ranks obtain bit-identical gradients and take the same optimiser step (and the same KL decision).
+            const unsigned int seq = a.xseq0 + static_cast<unsigned int>(step) + 1u;
+            const int rec = static_cast<int>(seq & 1u) * a.comm.x_stride + static_cast<int>(blockIdx.x) * (a.per_cta + kNumStats);
+            float *mine = exchange_xbuf(a.comm.area[my_rank]) + rec;
+            for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
+                mine[i] = RED[i];
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0)
+                flag_publish(&a.comm.area[my_rank]->step_flag[blockIdx.x], seq);
+            if (tid < world && tid != my_rank && *reinterpret_cast<volatile int *>(&a.state->comm_error) == 0)
+                if (!flag_wait(&a.comm.area[tid]->step_flag[blockIdx.x], seq))
+                    a.state->comm_error = 1;
+            __syncthreads();
+            for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
+            {
+                float g = 0.f;
+                for (int r = 0; r < world; ++r)
+                    g += r == my_rank ? RED[i] : peer_load(exchange_xbuf(a.comm.area[r]) + rec + i);
+                RED[i] = g;
+            }
+            __syncthreads();
+        }
         float stat_sum[5];
 #pragma unroll
         for (int s = 0; s < 5; ++s)
-        {
-            float v = 0.f;
-#pragma unroll
-            for (int w = 0; w < kRedSplit; ++w)
-                v += RED[w * red_ld + n_own + s];
-            stat_sum[s] = v;
-        }
+            stat_sum[s] = RED[n_own + s];
         const float sum_v = stat_sum[0], sum_a = stat_sum[1], sum_e = stat_sum[2], sum_kl = stat_sum[3],
                     sum_clip = stat_sum[4];
         if (a.algo == kAlgoPPO)
@@ -1056,10 +1109,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 const int gi = c0 + i;
                 if (gi >= P)
                     continue;
-                float g = 0.f;
-#pragma unroll
-                for (int w = 0; w < kRedSplit; ++w)
-                    g += RED[w * red_ld + i];
+                const float g = RED[i];
                 float p = OWN_P[i];
                 if (a.opt == kOptAdam)
                 {

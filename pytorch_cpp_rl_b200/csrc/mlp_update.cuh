@@ -2,6 +2,8 @@
 #pragma once
 #include <stdint.h>
 
+#include "comm.cuh"
+
 namespace cpprl_b200
 {
 constexpr int kHid = 64;           // MlpBase hidden size this kernel is specialised for
@@ -43,13 +45,13 @@ struct ImageLayout
 struct UpdateState
 {
     int stopped;          // KL early stop triggered (ppo.cpp:100-104)
+    int comm_error;       // a peer never published its exchange record (bounded wait expired)
     int num_updates;      // optimizer steps applied in this update
     float total_value_loss, total_action_loss, total_entropy, total_clip_fraction;
     float last_kl;
     float kl_stop_update; // num_updates at the stop, -1 otherwise
     long long opt_step;   // Adam step count (persists across updates)
     float a2c_value_loss, a2c_action_loss, a2c_entropy;
-    int pad;
 };
 
 struct MlpUpdateArgs
@@ -71,6 +73,13 @@ struct MlpUpdateArgs
     const long long *perm; // row ids for this launch, nullable = identity
     int B;                // rows per minibatch
     int n_steps;          // minibatches in this launch
+    const int *step_rows; // nullable: rows of each minibatch owned by THIS rank (env-sharded update); else B for all
+    long long perm_stride; // distance between the row lists of consecutive minibatches inside `perm`
+    int B_norm;           // rows of the GLOBAL minibatch: every mean of the loss divides by this
+    long long rows_norm;  // rows of the GLOBAL rollout (advantage normalisation)
+    CommView comm;        // world == 1: single GPU
+    unsigned int xseq0;   // gradient-exchange sequence number before the first minibatch of this launch
+    unsigned int adv_seq; // advantage-moment exchange sequence number of this update
     int n_active;         // CTAs that own tiles and publish a gradient partial (= min(#tiles, grid))
     int per_cta;          // parameters owned by each CTA in phase 2 (multiple of 4; grid * per_cta >= P rounded to 4)
     const double *adv_sums; // {sum, sumsq} of raw advantages over all rows (PPO), nullable

@@ -1,6 +1,14 @@
 // stream_kernels.cu — the remaining bandwidth-bound stages: minibatch row gather, observation
 // normaliser (column moments + Chan merge, normalise/clamp) and flat-buffer Adam / RMSprop steps.
+#include "comm.cuh"
 #include "common.cuh"
+
+struct cpprl_b200_comm;
+namespace cpprl_b200
+{
+CommView comm_view(const cpprl_b200_comm *c);
+unsigned int *comm_rms_seq(cpprl_b200_comm *c);
+} // namespace cpprl_b200
 
 namespace cpprl_b200
 {
@@ -35,7 +43,7 @@ constexpr int kRmsThreads = 256;
 __global__ void __launch_bounds__(kRmsThreads)
     rms_update_kernel(const float *__restrict__ x, int64_t M, int D, double *__restrict__ ws,
                       unsigned int *__restrict__ done_counter, float *__restrict__ count,
-                      float *__restrict__ mean, float *__restrict__ var)
+                      float *__restrict__ mean, float *__restrict__ var, const CommView comm, unsigned int seq)
 {
     extern __shared__ double sh[]; // [2][lanes_used]
     // threads 0..lanes_used-1 each stay on one column: lanes_used is a multiple of D
@@ -76,14 +84,49 @@ __global__ void __launch_bounds__(kRmsThreads)
     if (!is_last)
         return;
     __threadfence();
+    double rows_total = static_cast<double>(M);
+    __shared__ double sh_rows;
+    if (comm.world > 1)
+    {
+        // env-sharded update: the batch is the union of every rank's rows.  Publish this rank's column sums and row
+        // count, wait for the peers', and add them in rank order (identical merge on every rank).
+        ExchangeArea *mine = comm.area[comm.rank];
+        for (int c = tid; c < 2 * D; c += kRmsThreads)
+            mine->rms[c] = __ldcg(&ws[c]);
+        if (tid == 0)
+            mine->rms[2 * D] = static_cast<double>(M);
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0)
+            flag_publish(&mine->rms_flag, seq);
+        if (tid < comm.world && tid != comm.rank)
+            flag_wait(&comm.area[tid]->rms_flag, seq);
+        __syncthreads();
+        for (int c = tid; c < 2 * D; c += kRmsThreads)
+        {
+            double sum = 0.0;
+            for (int r = 0; r < comm.world; ++r)
+                sum += r == comm.rank ? __ldcg(&ws[c]) : peer_load(&comm.area[r]->rms[c]);
+            ws[c] = sum;
+        }
+        if (tid == 0)
+        {
+            double rows = 0.0;
+            for (int r = 0; r < comm.world; ++r)
+                rows += r == comm.rank ? static_cast<double>(M) : peer_load(&comm.area[r]->rms[2 * D]);
+            sh_rows = rows;
+        }
+        __syncthreads();
+        rows_total = sh_rows;
+    }
     const float old_count = count[0];
-    const float batch_count = static_cast<float>(M);
+    const float batch_count = static_cast<float>(rows_total);
     const float total_count = __fadd_rn(old_count, batch_count);
     for (int c = tid; c < D; c += kRmsThreads)
     {
         const double sum = __ldcg(&ws[c]), sumsq = __ldcg(&ws[D + c]);
-        const double bm_d = sum / static_cast<double>(M);
-        double bv_d = sumsq / static_cast<double>(M) - bm_d * bm_d; // population variance (var(0,false))
+        const double bm_d = sum / rows_total;
+        double bv_d = sumsq / rows_total - bm_d * bm_d; // population variance (var(0,false))
         if (bv_d < 0.0)
             bv_d = 0.0;
         const float batch_mean = static_cast<float>(bm_d), batch_var = static_cast<float>(bv_d);
@@ -191,18 +234,19 @@ extern "C" int64_t cpprl_b200_rms_workspace_bytes(int64_t /*M*/, int64_t D)
     return D <= 0 ? 0 : static_cast<int64_t>(sizeof(double)) * 2 * D + 16;
 }
 
-extern "C" int cpprl_b200_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean,
-                                     float *d_var, void *d_workspace, void *stream)
+namespace cpprl_b200
+{
+int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean, float *d_var,
+                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s)
 {
     if (!d_x || !d_count || !d_mean || !d_var || !d_workspace)
         return fail(CPPRL_B200_EINVAL, "rms_update: null pointer");
     if (M <= 0 || D <= 0)
         return fail(CPPRL_B200_EINVAL, "rms_update: non-positive size");
-    if (D > kRmsThreads)
+    if (D > kRmsThreads || D > kXMaxDim)
         return fail(CPPRL_B200_EUNSUPPORTED, "rms_update: D > 256 is not implemented");
     if (int rc = require_device())
         return rc;
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int64_t ws_bytes = cpprl_b200_rms_workspace_bytes(M, D);
     KernelTimer timer("rms", s);
     CPPRL_CUDA_TRY(cudaMemsetAsync(d_workspace, 0, ws_bytes, s));
@@ -215,10 +259,25 @@ extern "C" int cpprl_b200_rms_update(const float *d_x, int64_t M, int64_t D, flo
         blocks = 1;
     double *ws = static_cast<double *>(d_workspace);
     unsigned int *counter = reinterpret_cast<unsigned int *>(ws + 2 * D);
+    const CommView view = comm_view(comm);
+    const unsigned int seq = view.world > 1 ? ++*comm_rms_seq(comm) : 0u;
     rms_update_kernel<<<static_cast<unsigned>(blocks), kRmsThreads, sizeof(double) * 2 * lanes_used, s>>>(
-        d_x, M, static_cast<int>(D), ws, counter, d_count, d_mean, d_var);
+        d_x, M, static_cast<int>(D), ws, counter, d_count, d_mean, d_var, view, seq);
     CPPRL_LAUNCH_CHECK("rms_update_kernel");
     return 0;
+}
+} // namespace cpprl_b200
+
+extern "C" int cpprl_b200_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean,
+                                     float *d_var, void *d_workspace, void *stream)
+{
+    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int cpprl_b200_rms_update_sharded(cpprl_b200_comm *comm, const float *d_x, int64_t M, int64_t D,
+                                             float *d_count, float *d_mean, float *d_var, void *d_workspace, void *stream)
+{
+    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, comm, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int cpprl_b200_normalize_observations(const float *d_x, int64_t M, int64_t D, const float *d_mean,

@@ -382,3 +382,28 @@ def test_unsupported_configs_fail_loudly():
     assert e.value.code == cabi.EUNSUPPORTED
     with pytest.raises(RuntimeError):
         api.gather_rows(torch.zeros(4, 4), torch.zeros(2, dtype=torch.int64))  # CPU tensors: no fallback
+
+
+# ---- (e) env-sharded path on one rank: the whole rollout is "this rank's shard" --------------------------------------
+def test_sharded_update_world1_matches_plain(ref):
+    """Communicator of world size 1: the permutation-compaction + ragged-minibatch code path must reproduce the plain
+    update (same rows in the same order)."""
+    w = CONFIGS["cfg3"].scaled(T=32, N=64, num_epoch=3, num_mini_batch=4)
+    r = synth_rollout(w, 0)
+    sess = H.make_ref_session(ref, w, init_seed=0)
+    H.fill_policy_outputs(sess, w, r)
+    results = []
+    for sharded in (False, True):
+        policy, st = H.make_gpu_side(w, r, sess.get_params(), sess.get_normalizer())
+        algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef,
+                       w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
+        if sharded:
+            comm = api.Communicator(policy.params.numel())
+            algo.set_communicator(comm, 0, w.N)
+        st.compute_returns(torch.from_numpy(r["next_value"]).cuda(), True, w.gamma, w.tau)
+        stats = algo.update(st, 1.0, perms=H.draw_perms(7, w.rows, w.num_epoch))
+        results.append((policy.params.clone(), [d.value for d in stats], policy.observation_normalizer.rms.mean.clone()))
+    # same rows in the same tiles; only the grid (and with it the summation order of the partials) differs
+    np.testing.assert_allclose(results[0][1], results[1][1], rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(results[0][0].cpu().numpy(), results[1][0].cpu().numpy(), rtol=1e-5, atol=1e-7)
+    assert torch.equal(results[0][2], results[1][2])
