@@ -143,14 +143,18 @@ def run_reference(args, w: Workload, rank: int, world: int):
 class GpuSide:
     """Policy, storage and algorithm resident on one GPU, plus pinned host copies of the rollout for the e2e leg."""
 
-    def __init__(self, w: Workload, seed: int):
+    def __init__(self, w: Workload, seed: int, rank: int = 0, world: int = 1):
+        """world > 1: this rank holds w.N environments of a global rollout of world * w.N (weak scaling); parameters
+        are replicated (same init seed), the rollout shard is seeded per rank."""
         import torch
         from pytorch_cpp_rl_b200 import api
         self.torch, self.api, self.w = torch, api, w
+        self.rank, self.world = rank, world
+        param_seed, seed = seed, seed + rank
         space = api.ActionSpace("Discrete" if w.head == "categorical" else "Box", [w.num_actions])
         self.policy = api.Policy(space, w.obs_dim, normalize_observations=w.normalize_obs, hidden=w.hidden,
                                  recurrent=(w.base == "gru"))
-        self.policy.params.copy_(torch.from_numpy(init_params(w, seed)))
+        self.policy.params.copy_(torch.from_numpy(init_params(w, param_seed)))
         self.st = api.RolloutStorage(w.T, w.N, w.obs_shape, space, w.storage_hidden)
         r = synth_rollout(w, seed)
         self.fields = ["observations", "rewards", "masks", "actions", "value_predictions", "action_log_probs"]
@@ -169,13 +173,22 @@ class GpuSide:
         if w.algo == "ppo":
             self.algo = api.PPO(self.policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef,
                                 w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
-            g = torch.Generator().manual_seed(seed)
-            self.d_perms = [torch.randperm(w.rows, generator=g).cuda() for _ in range(w.num_epoch)]
+            g = torch.Generator().manual_seed(param_seed)  # the same GLOBAL permutations on every rank
+            self.d_perms = [torch.randperm(w.rows * world, generator=g).cuda() for _ in range(w.num_epoch)]
         else:
             self.algo = api.A2C(self.policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
+        self.comm = None
+        if world > 1:
+            # environments sharded over the GPUs of the box; gradient all-reduce inside the fused kernel (NVLink)
+            self.comm = api.Communicator(self.policy.params.numel())
+            if w.algo == "ppo":
+                self.algo.set_communicator(self.comm, rank * w.N, world * w.N)
+            else:
+                self.algo.set_communicator(self.comm, world * w.N)
+        self.e2e_calls = 0
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.pinned.values()) + self.pinned_nv.numel() * 4
         if w.algo == "ppo":
-            self.h2d_bytes += w.num_epoch * w.rows * 8
+            self.h2d_bytes += w.num_epoch * w.rows * world * 8
         self.d2h_bytes = 64
 
     def step_device(self):
@@ -197,6 +210,10 @@ class GpuSide:
             getattr(self.st, n).copy_(self.pinned[n], non_blocking=True)
         self.next_value.copy_(self.pinned_nv, non_blocking=True)
         self.st.compute_returns(self.next_value, w.use_gae, w.gamma, w.tau)
+        if self.world > 1:
+            # every rank must draw the same global permutations from its CPU generator
+            self.e2e_calls += 1
+            self.torch.manual_seed(12345 + self.e2e_calls)
         return self.algo.update(self.st)
 
 
@@ -238,7 +255,7 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     lib = cabi.load()
     hbm_peak, peak_src, sm_max = measured_peaks()
-    side = GpuSide(w, seed=rank)
+    side = GpuSide(w, seed=0, rank=rank, world=world)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def barrier():
@@ -267,7 +284,11 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         launches = lib.cpprl_b200_launch_count() - launches0
         lib.cpprl_b200_kernel_time_enable(0)
         # keep the sampler alive long enough to see the load on very short runs
-        if t_wall < 1.0:
+        if world > 1:
+            for _ in range(20):  # the same count on every rank: the sharded kernels of all ranks must run in lock step
+                side.step_device()
+            torch.cuda.synchronize()
+        elif t_wall < 1.0:
             t_end = time.perf_counter() + 1.0
             while time.perf_counter() < t_end:
                 side.step_device()
@@ -335,7 +356,10 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "data": "synthetic",
         "config": {"workload": f"{w.name}: {w.description}", "rows_per_step": w.rows, "optimizer_steps": w.optimizer_steps,
                    "l2": "flushed between timed iterations (256 MiB write)",
-                   "parallelism": "single GPU" if world == 1 else f"{world} independent env shards (replicas)"},
+                   "parallelism": "single GPU" if world == 1 else
+                   f"dp{world}: {world * w.N} envs sharded by environment over {world} GPUs ({w.N} per GPU), global "
+                   f"minibatch {world * w.rows // max(1, w.num_mini_batch)} rows, gradient all-reduce inside the fused kernel "
+                   "over NVLink peer memory"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": side.h2d_bytes, "d2h_bytes_per_step": side.d2h_bytes,
                 "ms_per_step": e2e_s * 1e3},
         "gpu_launches": int(launches), "roofline": roofline, "stages": stages, "kernel_time_share": shares,

@@ -118,7 +118,7 @@ extern "C" int cpprl_b200_comm_create(cpprl_b200_comm **out, int rank, int world
     c->world = world;
     // every CTA's record is its slice of the parameters (rounded to 4, at least 4) plus the statistics slots
     c->x_stride = static_cast<int>(((max_params + 3) / 4) * 4 + (4 + 8) * kMaxCtas);
-    c->bytes = sizeof(ExchangeArea) + sizeof(float) * 2 * static_cast<size_t>(c->x_stride);
+    c->bytes = sizeof(ExchangeArea) + sizeof(LLWord) * 2 * static_cast<size_t>(world) * static_cast<size_t>(c->x_stride);
     if (cudaMalloc(&c->local, c->bytes) != cudaSuccess || cudaMemset(c->local, 0, c->bytes) != cudaSuccess)
     {
         delete c;

@@ -22,7 +22,15 @@ struct ExchangeArea
     unsigned int adv_flag, rms_flag, pad0, pad1;
     // observation-normaliser exchange: column sums, column sums of squares, row count
     double rms[2 * kXMaxDim + 2];
-    // followed by float xbuf[2][x_stride]
+    // followed by the gradient exchange: LLWord xbuf[2 (parity)][world (sender)][x_stride]
+};
+
+// Low-latency exchange word: value and sequence number travel in ONE 8-byte store, so a reader that sees the
+// expected sequence number also sees the value — no fence, no separate flag (the NCCL "LL" idea).
+struct LLWord
+{
+    float value;
+    unsigned int seq;
 };
 
 struct CommView // passed by value to kernels
@@ -33,7 +41,30 @@ struct CommView // passed by value to kernels
 };
 
 #ifdef __CUDACC__
-__device__ __forceinline__ float *exchange_xbuf(ExchangeArea *a) { return reinterpret_cast<float *>(a + 1); }
+__device__ __forceinline__ LLWord *exchange_xbuf(ExchangeArea *a) { return reinterpret_cast<LLWord *>(a + 1); }
+
+// PUSH a word into (possibly peer) memory / poll a word of LOCAL memory a peer pushes into.
+__device__ __forceinline__ void ll_store(LLWord *dst, float value, unsigned int seq)
+{
+    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(dst), "r"(__float_as_uint(value)), "r"(seq) : "memory");
+}
+__device__ __forceinline__ bool ll_load(const LLWord *src, unsigned int seq, float &value)
+{
+    for (long long spins = 0; spins < (1ll << 24); ++spins)
+    {
+        unsigned int v, s;
+        asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(v), "=r"(s) : "l"(src) : "memory");
+        if (s == seq)
+        {
+            value = __uint_as_float(v);
+            return true;
+        }
+        if (spins > 8192)
+            __nanosleep(200);
+    }
+    value = 0.f;
+    return false;
+}
 
 __device__ __forceinline__ void flag_publish(unsigned int *flag, unsigned int seq)
 {
@@ -50,7 +81,8 @@ __device__ __forceinline__ bool flag_wait(const unsigned int *flag, unsigned int
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
         if (static_cast<int>(v - seq) >= 0)
             return true;
-        __nanosleep(100);
+        if (spins > 4096)
+            __nanosleep(200);
     }
     return false;
 }

@@ -1031,30 +1031,43 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         if (world > 1)
         {
             // ---- gradient all-reduce across the GPUs of the box, inside the kernel, over NVLink peer memory ------
-            // CTA b of every rank owns the same slice of the parameter vector: it publishes its rank-local sums in its
-            // own exchange area, waits for the b-th flag of every peer, and adds the R records in rank order, so all
-            // ranks obtain bit-identical gradients and take the same optimiser step (and the same KL decision).
+            // CTA b of every rank owns the same slice of the parameter vector: it pushes its rank-local sums into the
+            // exchange area of every peer as 8-byte {value, sequence} words (no fence, no flag), polls its own area for
+            // the peers' words and adds the R records in rank order, so all ranks obtain bit-identical gradients and
+            // take the same optimiser step (and the same KL decision).
             const unsigned int seq = a.xseq0 + static_cast<unsigned int>(step) + 1u;
-            const int rec = static_cast<int>(seq & 1u) * a.comm.x_stride + static_cast<int>(blockIdx.x) * (a.per_cta + kNumStats);
-            float *mine = exchange_xbuf(a.comm.area[my_rank]) + rec;
+            // word i of CTA b's record from sender r lives at xbuf[parity][r][b * (per_cta + stats) + i] of the
+            // RECEIVER's area: senders push with one-way NVLink stores, receivers poll their own HBM
+            const int cta_off = static_cast<int>(blockIdx.x) * (a.per_cta + kNumStats);
+            const size_t par_off = static_cast<size_t>(seq & 1u) * world * a.comm.x_stride;
+            CPPRL_MARK(16);
             for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
-                mine[i] = RED[i];
-            __threadfence_system();
-            __syncthreads();
-            if (tid == 0)
-                flag_publish(&a.comm.area[my_rank]->step_flag[blockIdx.x], seq);
-            if (tid < world && tid != my_rank && *reinterpret_cast<volatile int *>(&a.state->comm_error) == 0)
-                if (!flag_wait(&a.comm.area[tid]->step_flag[blockIdx.x], seq))
-                    a.state->comm_error = 1;
-            __syncthreads();
+            {
+                const float mine = RED[i];
+#pragma unroll
+                for (int r = 0; r < kMaxRanks; ++r)
+                    if (r < world && r != my_rank)
+                        ll_store(exchange_xbuf(a.comm.area[r]) + par_off + static_cast<size_t>(my_rank) * a.comm.x_stride + cta_off + i,
+                                 mine, seq);
+            }
+            CPPRL_MARK(17);
+            const bool comm_ok = *reinterpret_cast<volatile int *>(&a.state->comm_error) == 0;
             for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
             {
                 float g = 0.f;
-                for (int r = 0; r < world; ++r)
-                    g += r == my_rank ? RED[i] : peer_load(exchange_xbuf(a.comm.area[r]) + rec + i);
+                for (int r = 0; r < world; ++r) // rank order: bit-identical sums on every rank
+                {
+                    float v = RED[i];
+                    if (r != my_rank && comm_ok &&
+                        !ll_load(exchange_xbuf(a.comm.area[my_rank]) + par_off + static_cast<size_t>(r) * a.comm.x_stride + cta_off + i, seq, v))
+                        a.state->comm_error = 1;
+                    g += v;
+                }
                 RED[i] = g;
             }
+            CPPRL_MARK(18);
             __syncthreads();
+            CPPRL_MARK(19);
         }
         float stat_sum[5];
 #pragma unroll

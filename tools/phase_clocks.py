@@ -14,10 +14,16 @@ from pytorch_cpp_rl_b200.workloads import CONFIGS
 
 NAMES = ["img+stage", "P1 L1", "P2 L2", "P3 heads", "P4 loss", "P5 head-bwd", "P6 dW2", "P7 dz1", "P8 dW1", "publish",
          "barrier1", "reduce", "optimiser", "arrive+stage", "barrier2 wait"]
+import os
 cfg = sys.argv[1] if len(sys.argv) > 1 else "cfg3"
 step = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 w = CONFIGS[cfg]
-side = GpuSide(w, 0)
+rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+if world > 1:
+    import torch.distributed as dist
+    dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ["LOCAL_RANK"])))
+side = GpuSide(w, 0, rank, world)
 lib = cabi.load()
 buf = torch.zeros(148 * 32, dtype=torch.int64, device="cuda")
 for _ in range(3):
@@ -30,9 +36,16 @@ lib.cpprl_b200_debug_phase_clocks(None, 0)
 c = buf.cpu().numpy().reshape(148, 32)
 used = c[:, 0] != 0
 c = c[used]
+if rank != 0:
+    torch.cuda.synchronize()
+    sys.exit(0)
 print(f"{cfg}: {used.sum()} CTAs, step {step}; cycles per phase (min / median / max over CTAs); multi-tile CTAs show the LAST tile")
 d = np.diff(c[:, :16], axis=1)
 for i, n in enumerate(NAMES):
     print(f"  {n:12s} {d[:, i].min():8d} {int(np.median(d[:, i])):8d} {d[:, i].max():8d}")
 tot = c[:, 15] - c[:, 0]
+if world > 1:
+    x = np.diff(c[:, 16:20], axis=1)
+    for i, n in enumerate(["x: push to peers", "x: poll + add", "x: barrier"]):
+        print(f"  {n:16s} {x[:, i].min():8d} {int(np.median(x[:, i])):8d} {x[:, i].max():8d}")
 print(f"  total        {tot.min():8d} {int(np.median(tot)):8d} {tot.max():8d}  (= {np.median(tot) / 1.965e3:.1f} us at 1965 MHz)")
