@@ -167,10 +167,15 @@ class Policy:
         entropy = torch.empty(1, dtype=torch.float32, device=inputs.device)
         d = self.desc()
         n_hxs = 0 if rnn_hxs is None else rnn_hxs.shape[0]
+        hxs_out = None
+        if self.recurrent:
+            _need_cuda(rnn_hxs, masks)
+            rnn_hxs, masks = rnn_hxs.contiguous(), masks.contiguous()
+            hxs_out = torch.empty_like(rnn_hxs)  # new state in step mode, a copy of rnn_hxs in sequence mode
         check(cabi.load().cpprl_b200_evaluate_actions(C.byref(d), _ptr(inputs), _ptr(rnn_hxs), n_hxs, _ptr(masks),
                                                       _ptr(actions), B, _ptr(value), _ptr(logp), _ptr(entropy),
-                                                      None, _stream()))
-        return [value, logp, entropy.view(()), rnn_hxs]
+                                                      _ptr(hxs_out), _stream()))
+        return [value, logp, entropy.view(()), hxs_out if self.recurrent else rnn_hxs]
 
 
 # ---------------------------------------------------------------------------------------------------

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "gru_update.cuh"
 #include "mlp_update.cuh"
 
 struct cpprl_b200_comm;
@@ -59,6 +60,37 @@ bool mlp_param_offsets(const cpprl_b200_policy &p, ParamOffsets &po)
     return true;
 }
 
+// Parameter offsets of the GRU-fronted MlpBase: the GRU's four tensors are registered first (nn_base.cpp:13-21), the
+// towers then take the H GRU outputs as inputs (mlp_base.cpp:14-17).
+bool gru_param_offsets(const cpprl_b200_policy &p, GruParamOffsets &po)
+{
+    if (p.base_kind != CPPRL_B200_BASE_GRU_MLP || p.hidden != kHid)
+        return false;
+    const int D = static_cast<int>(p.obs_dim), A = static_cast<int>(p.num_actions);
+    int o = 0;
+    po.wih = o, o += kGruGates * D;
+    po.whh = o, o += kGruGates * kHid;
+    po.bih = o, o += kGruGates;
+    po.bhh = o, o += kGruGates;
+    for (int t = 0; t < 2; ++t)
+    {
+        po.w1[t] = o, o += kHid * kHid;
+        po.b1[t] = o, o += kHid;
+        po.w2[t] = o, o += kHid * kHid;
+        po.b2[t] = o, o += kHid;
+    }
+    po.wv = o, o += kHid;
+    po.bv = o, o += 1;
+    if (p.head_kind == CPPRL_B200_HEAD_NORMAL)
+        po.slog = o, o += A;
+    else
+        po.slog = -1;
+    po.wo = o, o += A * kHid;
+    po.bo = o, o += A;
+    po.P = o;
+    return true;
+}
+
 ImageLayout make_image_layout(int Dp, int Ap)
 {
     ImageLayout il;
@@ -84,11 +116,10 @@ int validate_policy(const cpprl_b200_policy *p, const char *who)
 {
     if (!p || !p->d_params)
         return fail(CPPRL_B200_EINVAL, std::string(who) + ": null policy / parameter buffer");
-    if (p->base_kind == CPPRL_B200_BASE_GRU_MLP)
-        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": recurrent (GRU) MlpBase is not implemented on the GPU path yet");
     if (p->base_kind == CPPRL_B200_BASE_CNN)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": CnnBase is not implemented on the GPU path yet");
-    if (p->base_kind != CPPRL_B200_BASE_MLP)
+    const bool gru = p->base_kind == CPPRL_B200_BASE_GRU_MLP;
+    if (p->base_kind != CPPRL_B200_BASE_MLP && !gru)
         return fail(CPPRL_B200_EINVAL, std::string(who) + ": unknown base kind");
     if (p->head_kind != CPPRL_B200_HEAD_CATEGORICAL && p->head_kind != CPPRL_B200_HEAD_NORMAL)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": only Categorical and Normal heads are implemented (Bernoulli is out of scope)");
@@ -96,13 +127,26 @@ int validate_policy(const cpprl_b200_policy *p, const char *who)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": MlpBase hidden size must be 64 on the GPU path");
     if (p->obs_dim < 1 || p->obs_dim > 256)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": obs_dim must be in [1, 256]");
+    if (gru && p->obs_dim > kGruMaxObs)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": the recurrent (GRU) path takes at most 32 observation columns");
     if (p->num_actions < 1 || p->num_actions > kMaxActions)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": num_actions must be in [1, 16]");
-    ParamOffsets po;
-    mlp_param_offsets(*p, po);
-    if (p->n_params != po.P)
+    int expect_p = 0;
+    if (gru)
+    {
+        GruParamOffsets gpo;
+        gru_param_offsets(*p, gpo);
+        expect_p = gpo.P;
+    }
+    else
+    {
+        ParamOffsets po;
+        mlp_param_offsets(*p, po);
+        expect_p = po.P;
+    }
+    if (p->n_params != expect_p)
         return fail(CPPRL_B200_EINVAL, std::string(who) + ": n_params does not match the policy layout (expected " +
-                                           std::to_string(po.P) + ", got " + std::to_string(p->n_params) + ")");
+                                           std::to_string(expect_p) + ", got " + std::to_string(p->n_params) + ")");
     const bool any = p->d_norm_clip || p->d_norm_count || p->d_norm_mean || p->d_norm_var;
     const bool all = p->d_norm_clip && p->d_norm_count && p->d_norm_mean && p->d_norm_var;
     if (any && !all)
@@ -122,6 +166,21 @@ struct Scratch
     double *adv_sums = nullptr;
     void *rms_ws = nullptr;
     size_t rms_ws_bytes = 0;
+    float *tape = nullptr; // GRU path: per-CTA activation tapes
+    size_t tape_floats = 0;
+
+    int ensure_tape(size_t n)
+    {
+        if (n > tape_floats)
+        {
+            if (tape)
+                cudaFree(tape);
+            tape = nullptr, tape_floats = 0;
+            CPPRL_CUDA_TRY(cudaMalloc(&tape, n * sizeof(float)));
+            tape_floats = n;
+        }
+        return 0;
+    }
 
     int ensure(size_t img, size_t gp, size_t rms)
     {
@@ -159,7 +218,8 @@ struct Scratch
     void release()
     {
         cudaFree(image), cudaFree(gpart), cudaFree(barrier), cudaFree(state), cudaFree(adv_sums), cudaFree(rms_ws);
-        image = gpart = nullptr;
+        cudaFree(tape);
+        image = gpart = tape = nullptr;
         barrier = nullptr;
         state = nullptr;
         adv_sums = nullptr;
@@ -213,6 +273,24 @@ void fill_policy_args(MlpUpdateArgs &a, const cpprl_b200_policy &p, const ParamO
     a.norm_clip = p.d_norm_clip;
 }
 
+int fill_gru_policy_args(GruUpdateArgs &a, const cpprl_b200_policy &p, int64_t T, const char *who)
+{
+    std::memset(&a, 0, sizeof(a));
+    gru_param_offsets(p, a.po);
+    a.params = p.d_params;
+    a.D = static_cast<int>(p.obs_dim);
+    a.Dp = round_up(a.D, 8);
+    a.A = static_cast<int>(p.num_actions);
+    a.Ap = round_up(a.A, 4);
+    a.head = p.head_kind == CPPRL_B200_HEAD_NORMAL ? 1 : 0;
+    a.norm_mean = p.d_norm_mean;
+    a.norm_var = p.d_norm_var;
+    a.norm_clip = p.d_norm_clip;
+    if (T > 0x7fffffffll / (kGruGates * 8) || gru_update_smem_bytes(a.Dp, a.A, a.Ap, static_cast<int>(T)) > 227 * 1024)
+        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": sequence length x observation size needs more than 227 KB of shared memory on the recurrent path");
+    return 0;
+}
+
 __global__ void reset_state_kernel(UpdateState *st)
 {
     const long long keep = st->opt_step;
@@ -254,6 +332,8 @@ struct cpprl_b200_ppo
     cpprl_b200_rollout rollout;
     cpprl_b200_ppo_options opt;
     MlpUpdateArgs args;
+    GruUpdateArgs gargs; // recurrent policies
+    bool gru = false;
     Plan plan;
     int64_t mbs = 0, n_mb = 0;
     int epoch = 0;
@@ -361,6 +441,86 @@ extern "C" int cpprl_b200_ppo_set_step(cpprl_b200_ppo *h, int64_t step)
     return 0;
 }
 
+// Recurrent policies: RolloutStorage::recurrent_generator (storage.cpp:195-218) + RecurrentGenerator
+// (recurrent_generator.cpp:30-98).  The generator always walks all N entries of randperm(N), each minibatch being
+// num_processes / num_mini_batch environments starting at the drawn index; only one environment per minibatch
+// survives the reference's own flatten, so that is the only shape accepted here.
+static int ppo_begin_gru(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *ro,
+                         const cpprl_b200_ppo_options *opt, void *stream)
+{
+    if (h->comm)
+        return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: the recurrent path is single-GPU (its minibatch chain is serial)");
+    if (!ro->d_hidden_states || !ro->d_masks)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: recurrent policy needs the rollout's hidden_states and masks");
+    if (ro->hidden_dim != kHid)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: rollout hidden_dim must equal the GRU hidden size (64)");
+    if (ro->N < opt->num_mini_batch)
+        return fail(CPPRL_B200_EINVAL, "PPO needs the number of processes (" + std::to_string(ro->N) +
+                                           ") to be greater than or equal to the number of minibatches (" +
+                                           std::to_string(opt->num_mini_batch) + ")");
+    if (ro->N / opt->num_mini_batch != 1)
+        return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: the recurrent generator only works with one environment per "
+                                             "minibatch (num_mini_batch must equal the number of processes)");
+    const int64_t expect_cols = policy->head_kind == CPPRL_B200_HEAD_CATEGORICAL ? 1 : policy->num_actions;
+    if (ro->action_cols != expect_cols)
+        return fail(CPPRL_B200_EINVAL, "ppo_update: rollout action_cols does not match the policy head");
+    if (ro->T * ro->N > 0x7fffffffll)
+        return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: more than 2^31 rows");
+    h->policy = *policy;
+    h->rollout = *ro;
+    h->opt = *opt;
+    h->stream = static_cast<cudaStream_t>(stream);
+    h->mbs = 1; // perm_len = mbs * n_mb = N
+    h->n_mb = ro->N;
+    h->epoch = 0;
+    GruUpdateArgs &a = h->gargs;
+    if (int rc = fill_gru_policy_args(a, *policy, ro->T, "ppo_update"))
+        return rc;
+    const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
+    if (int rc = h->scratch.ensure(0, 0, rms_ws))
+        return rc;
+    if (int rc = h->scratch.ensure_tape(static_cast<size_t>(kGruTapes) * ro->T * kHid))
+        return rc;
+    a.obs = ro->d_observations;
+    a.hxs = ro->d_hidden_states; // hidden_states[0] (recurrent_generator.cpp:62-64)
+    a.masks = ro->d_masks;
+    a.actions = ro->d_actions;
+    a.value_preds = ro->d_value_preds;
+    a.returns = ro->d_returns;
+    a.old_logp = ro->d_action_log_probs;
+    a.T = static_cast<int>(ro->T);
+    a.N = static_cast<int>(ro->N);
+    a.cut_over_all_agents = 0;
+    a.n_mb = static_cast<int>(ro->N);
+    a.adv_sums = h->scratch.adv_sums;
+    a.rows = ro->T * ro->N;
+    a.algo = kAlgoPPO;
+    a.clip_param = opt->clip_param;
+    a.clip_lo = static_cast<float>(1.0 - static_cast<double>(opt->clip_param));
+    a.clip_hi = static_cast<float>(1.0 + static_cast<double>(opt->clip_param));
+    a.c_actor = opt->actor_loss_coef;
+    a.c_value = opt->value_loss_coef;
+    a.c_entropy = opt->entropy_coef;
+    a.kl_limit = static_cast<double>(opt->kl_target) * 1.5;
+    a.opt_m = h->d_m;
+    a.opt_v = h->d_v;
+    a.lr = static_cast<double>(opt->learning_rate);
+    a.beta1 = 0.9f;
+    a.beta2 = 0.999f;
+    a.eps = opt->epsilon;
+    a.tape = h->scratch.tape;
+    a.state = h->scratch.state;
+    cudaStream_t s = h->stream;
+    KernelTimer timer("prologue", s);
+    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+    CPPRL_LAUNCH_CHECK("reset_state_kernel");
+    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 2 * sizeof(double), s));
+    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, ro->T * ro->N, h->scratch.adv_sums, s))
+        return rc;
+    h->active = true;
+    return 0;
+}
+
 extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *ro,
                                     const cpprl_b200_ppo_options *opt, void *stream)
 {
@@ -379,6 +539,9 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     if (opt->num_epoch < 0 || opt->num_mini_batch <= 0)
         return fail(CPPRL_B200_EINVAL, "ppo_update: bad epoch / minibatch count");
     const bool sharded = h->comm != nullptr;
+    h->gru = policy->base_kind == CPPRL_B200_BASE_GRU_MLP;
+    if (h->gru)
+        return ppo_begin_gru(h, policy, ro, opt, stream);
     const int64_t n_envs = sharded ? h->global_envs : ro->N; // minibatches are defined on the GLOBAL rollout
     if (sharded && (h->env_offset < 0 || h->env_offset + ro->N > h->global_envs))
         return fail(CPPRL_B200_EINVAL, "ppo_update: this rank's environment range lies outside the global rollout");
@@ -497,6 +660,15 @@ extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
 
 static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
+    if (h->gru)
+    {
+        h->gargs.perm = reinterpret_cast<const long long *>(d_perm);
+        KernelTimer timer("update", h->stream);
+        int rc = launch_gru_update(h->gargs, 1, h->stream);
+        if (rc == 0)
+            ++h->epoch;
+        return rc;
+    }
     if (h->comm)
     {
         // compact the global permutation to the rows this rank owns (stable, one CTA per minibatch)
@@ -543,7 +715,8 @@ extern "C" int cpprl_b200_ppo_epoch_device(cpprl_b200_ppo *h, const int64_t *d_p
     if (!h->active)
         return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
     if (perm_len != h->mbs * h->n_mb)
-        return fail(CPPRL_B200_EINVAL, "ppo_epoch: permutation length must be T*N");
+        return fail(CPPRL_B200_EINVAL, h->gru ? "ppo_epoch: permutation length must be N for recurrent policies"
+                                              : "ppo_epoch: permutation length must be T*N");
     return ppo_launch_epoch(h, d_perm);
 }
 
@@ -554,7 +727,8 @@ extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, in
     if (!h->active)
         return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
     if (perm_len != h->mbs * h->n_mb)
-        return fail(CPPRL_B200_EINVAL, "ppo_epoch: permutation length must be T*N");
+        return fail(CPPRL_B200_EINVAL, h->gru ? "ppo_epoch: permutation length must be N for recurrent policies"
+                                              : "ppo_epoch: permutation length must be T*N");
     if (static_cast<size_t>(perm_len) > h->perm_cap)
     {
         CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -734,6 +908,63 @@ extern "C" int cpprl_b200_a2c_state(cpprl_b200_a2c *h, float **d_square_avg)
     return 0;
 }
 
+// Recurrent A2C: evaluate_actions sees all T*N rows in sequence mode with hidden_states[0] (a2c.cpp:58-63), so runs
+// are cut where ANY environment's mask is zero.  One CTA per environment; the CTAs add their gradients into one
+// buffer and the stand-alone RMSprop kernel applies it.
+static int a2c_update_gru(cpprl_b200_a2c *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *ro,
+                          const cpprl_b200_a2c_options *opt, cudaStream_t s)
+{
+    if (h->comm)
+        return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: the recurrent path is single-GPU");
+    if (!ro->d_hidden_states || !ro->d_masks)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: recurrent policy needs the rollout's hidden_states and masks");
+    if (ro->hidden_dim != kHid)
+        return fail(CPPRL_B200_EINVAL, "a2c_update: rollout hidden_dim must equal the GRU hidden size (64)");
+    GruUpdateArgs a;
+    if (int rc = fill_gru_policy_args(a, *policy, ro->T, "a2c_update"))
+        return rc;
+    const size_t rms_ws = policy->d_norm_mean ? cpprl_b200_rms_workspace_bytes((ro->T + 1) * ro->N, policy->obs_dim) : 0;
+    if (int rc = h->scratch.ensure(0, static_cast<size_t>(a.po.P), rms_ws))
+        return rc;
+    if (int rc = h->scratch.ensure_tape(static_cast<size_t>(ro->N) * kGruTapes * ro->T * kHid))
+        return rc;
+    KernelTimer timer("update", s);
+    if (policy->d_norm_mean)
+    {
+        if (int rc = launch_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
+                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, nullptr, s))
+            return rc;
+    }
+    a.obs = ro->d_observations;
+    a.hxs = ro->d_hidden_states;
+    a.masks = ro->d_masks;
+    a.actions = ro->d_actions;
+    a.value_preds = ro->d_value_preds;
+    a.returns = ro->d_returns;
+    a.T = static_cast<int>(ro->T);
+    a.N = static_cast<int>(ro->N);
+    a.cut_over_all_agents = 1;
+    a.n_mb = 1;
+    a.rows = ro->T * ro->N;
+    a.algo = kAlgoA2C;
+    a.grad_out = h->scratch.gpart;
+    a.c_actor = 1.f;
+    a.c_value = opt->value_loss_coef;
+    a.c_entropy = opt->entropy_coef;
+    a.tape = h->scratch.tape;
+    a.state = h->scratch.state;
+    CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.gpart, 0, a.po.P * sizeof(float), s));
+    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+    CPPRL_LAUNCH_CHECK("reset_state_kernel");
+    if (int rc = launch_gru_update(a, static_cast<int>(ro->N), s))
+        return rc;
+    if (int rc = cpprl_b200_rmsprop_step(policy->d_params, h->scratch.gpart, h->d_sq, a.po.P, opt->learning_rate,
+                                         opt->alpha, opt->epsilon, s))
+        return rc;
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, s));
+    return 0;
+}
+
 extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_policy *policy,
                                            const cpprl_b200_rollout *ro, const cpprl_b200_a2c_options *opt, void *stream)
 {
@@ -756,6 +987,8 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
         return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: more than 2^31 rows");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->stream = s;
+    if (policy->base_kind == CPPRL_B200_BASE_GRU_MLP)
+        return a2c_update_gru(h, policy, ro, opt, s);
 
     ParamOffsets po;
     mlp_param_offsets(*policy, po);
@@ -868,14 +1101,17 @@ extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
     if (!policy)
         return 0;
     ParamOffsets po;
+    GruParamOffsets gpo;
+    if (gru_param_offsets(*policy, gpo))
+        return gpo.P;
     if (!mlp_param_offsets(*policy, po))
         return 0;
     return po.P;
 }
 
-extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float * /*d_hxs*/,
-                                           int64_t /*n_hxs*/, const float * /*d_masks*/, const void *d_actions, int64_t B,
-                                           float *d_value, float *d_logp, float *d_entropy, float * /*d_hxs_out*/,
+extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs,
+                                           int64_t n_hxs, const float *d_masks, const void *d_actions, int64_t B,
+                                           float *d_value, float *d_logp, float *d_entropy, float *d_hxs_out,
                                            void *stream)
 {
     if (int rc = require_device())
@@ -888,6 +1124,47 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
         return fail(CPPRL_B200_EINVAL, "evaluate_actions: bad batch size");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     std::lock_guard<std::mutex> lock(g_eval_mu);
+
+    if (policy->base_kind == CPPRL_B200_BASE_GRU_MLP)
+    {
+        // NNBase::forward_gru (nn_base.cpp:47-114): n_hxs == B is the one-step mode, otherwise x is [T, n_hxs] flattened
+        if (!d_hxs || !d_masks || n_hxs <= 0)
+            return fail(CPPRL_B200_EINVAL, "evaluate_actions: recurrent policy needs hidden states and masks");
+        if (B % n_hxs != 0)
+            return fail(CPPRL_B200_EINVAL, "evaluate_actions: batch size is not a multiple of the number of hidden states");
+        const int64_t T = B / n_hxs;
+        GruUpdateArgs a;
+        if (int rc = fill_gru_policy_args(a, *policy, T, "evaluate_actions"))
+            return rc;
+        if (int rc = g_eval_scratch.ensure(0, 0, 0))
+            return rc;
+        if (int rc = g_eval_scratch.ensure_tape(static_cast<size_t>(n_hxs) * T * kHid))
+            return rc;
+        a.obs = d_obs;
+        a.hxs = d_hxs;
+        a.masks = d_masks;
+        a.actions = d_actions;
+        a.T = static_cast<int>(T);
+        a.N = static_cast<int>(n_hxs);
+        a.cut_over_all_agents = 1;
+        a.rows = B;
+        a.algo = kAlgoForward;
+        a.tape = g_eval_scratch.tape;
+        a.out_value = d_value;
+        a.out_logp = d_logp;
+        a.out_entropy_sum = d_entropy;
+        a.out_hxs = d_hxs_out;
+        a.step_mode = T == 1;
+        CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
+        if (int rc = launch_gru_update(a, static_cast<int>(n_hxs), s))
+            return rc;
+        // sequence mode hands the incoming hidden states back unchanged (nn_base.cpp:110-112)
+        if (T != 1 && d_hxs_out && d_hxs_out != d_hxs)
+            CPPRL_CUDA_TRY(cudaMemcpyAsync(d_hxs_out, d_hxs, n_hxs * kHid * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        finish_entropy_kernel<<<1, 1, 0, s>>>(d_entropy, 1.f / static_cast<float>(B));
+        CPPRL_LAUNCH_CHECK("finish_entropy_kernel");
+        return 0;
+    }
 
     ParamOffsets po;
     mlp_param_offsets(*policy, po);

@@ -293,16 +293,17 @@ std::vector<torch::Tensor> PolicyImpl::evaluate_actions(torch::Tensor inputs, to
                              "evaluate_actions: actions");
     auto opts = obs.options();
     auto value = torch::empty({B, 1}, opts), logp = torch::empty({B, 1}, opts), entropy = torch::empty({1}, opts);
-    torch::Tensor hxs, msk;
+    torch::Tensor hxs, msk, hxs_out;
     if (base->is_recurrent())
     {
-        hxs = detail::dense(rnn_hxs, "evaluate_actions: rnn_hxs");
-        msk = detail::dense(masks.reshape({-1}), "evaluate_actions: masks");
+        hxs = detail::dense(rnn_hxs.to(torch::kFloat), "evaluate_actions: rnn_hxs");
+        msk = detail::dense(masks.to(torch::kFloat).reshape({-1}), "evaluate_actions: masks");
+        hxs_out = torch::empty_like(hxs); // new state in step mode, the incoming one in sequence mode (nn_base.cpp:55,112)
     }
     check(cpprl_b200_evaluate_actions(&desc, fptr(obs), hxs.defined() ? fptr(hxs) : nullptr, hxs.defined() ? hxs.size(0) : 0,
                                       msk.defined() ? fptr(msk) : nullptr, act.data_ptr(), B, fptr(value), fptr(logp),
-                                      fptr(entropy), nullptr, current_stream(obs)));
-    return {value, logp, entropy.squeeze(0), rnn_hxs};
+                                      fptr(entropy), hxs_out.defined() ? fptr(hxs_out) : nullptr, current_stream(obs)));
+    return {value, logp, entropy.squeeze(0), hxs_out.defined() ? hxs_out : rnn_hxs};
 }
 
 torch::Tensor PolicyImpl::get_probs(torch::Tensor inputs, torch::Tensor rnn_hxs, torch::Tensor masks) const

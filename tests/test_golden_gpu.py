@@ -1,0 +1,48 @@
+"""GPU parity against the COMMITTED golden fixtures (tests/golden/*.npz, written by tests/golden/make_golden.py from the
+compiled reference): needs neither /root/reference nor oracle/_ref at run time.
+
+Every fixture replays the reference's update(s) on the recorded rollout with the recorded permutations: returns
+bit-exact, statistics 1e-4, parameters 1e-4 relative to max(|ref|, lr) on all but the near-zero-gradient tail
+(two fp32 implementations of Adam's sign-like first steps; same criterion as the oracle's own fixture test).
+"""
+import numpy as np
+import pytest
+import torch
+
+from pytorch_cpp_rl_b200 import api
+from tests import golden_io as G
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", G.CASES)
+def test_golden_fixture_gpu(name):
+    w, d = G.load(name)
+    r = G.rollout_arrays(d)
+    policy, st = H.make_gpu_side(w, r, d["params_init"])
+    if w.algo == "ppo":
+        algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef,
+                       w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    else:
+        algo = api.A2C(policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    for u in range(int(d["n_updates"])):
+        st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        assert np.array_equal(st.returns.cpu().numpy(), d[f"returns{u}"]), "returns are bit-exact"
+        if w.algo == "ppo":
+            got = algo.update(st, 1.0, perms=torch.from_numpy(np.ascontiguousarray(d[f"perms{u}"])))
+        else:
+            got = algo.update(st, 1.0)
+        stats = np.array([x.value for x in got], np.float32)
+        want = d[f"stats{u}"]
+        assert len(stats) == len(want), (stats, want)
+        np.testing.assert_allclose(stats, want, rtol=1e-4, atol=5e-6, equal_nan=True)
+        wp = d[f"params{u}"]
+        err = np.abs(policy.params.cpu().numpy() - wp) / np.maximum(np.abs(wp), w.learning_rate)
+        print(f"[golden] {name} update {u}: max {err.max():.2e} q99 {np.quantile(err, 0.99):.2e}")
+        assert np.quantile(err, 0.99) <= 1e-4 and err.max() <= 5e-3, (u, err.max(), np.quantile(err, 0.99))
+        if w.normalize_obs:
+            n = policy.observation_normalizer.rms
+            got_n = np.concatenate([n.count.cpu().numpy().ravel(), n.mean.cpu().numpy(), n.variance.cpu().numpy()])
+            np.testing.assert_allclose(got_n, d[f"norm{u}"], rtol=2e-5, atol=1e-6)

@@ -378,7 +378,14 @@ def test_unsupported_configs_fail_loudly():
     policy = api.Policy(space, 8, recurrent=True)
     st = api.RolloutStorage(4, 4, [8], space, 64)
     with pytest.raises(cabi.CpprlB200Error) as e:
-        api.PPO(policy, 0.2, 1, 4, 1, 0.5, 0.01, 3e-4).update(st)
+        # two environments per recurrent minibatch: the reference's own flatten throws there
+        api.PPO(policy, 0.2, 1, 2, 1, 0.5, 0.01, 3e-4).update(st)
+    assert e.value.code == cabi.EUNSUPPORTED
+    d = policy.desc()  # CnnBase has no GPU kernel yet: the C ABI refuses the descriptor
+    d.base_kind = cabi.BASE_CNN
+    with pytest.raises(cabi.CpprlB200Error) as e:
+        cabi.check(cabi.load().cpprl_b200_evaluate_actions(__import__("ctypes").byref(d), None, None, 0, None, None, 4,
+                                                           None, None, None, None, None))
     assert e.value.code == cabi.EUNSUPPORTED
     with pytest.raises(RuntimeError):
         api.gather_rows(torch.zeros(4, 4), torch.zeros(2, dtype=torch.int64))  # CPU tensors: no fallback
