@@ -163,7 +163,10 @@ class GpuSide:
         self.next_value = torch.from_numpy(r["next_value"]).cuda()
         # value_predictions[:T] / action_log_probs = this policy's own outputs at its initial weights (§8d)
         T, N = w.T, w.N
-        out = self.policy.evaluate_actions(self.st.observations[:T].reshape(T * N, -1), None, None,
+        gru = w.base == "gru"
+        out = self.policy.evaluate_actions(self.st.observations[:T].reshape(T * N, -1),
+                                           self.st.hidden_states[0].contiguous() if gru else None,
+                                           self.st.masks[:T].reshape(T * N, 1).contiguous() if gru else None,
                                            self.st.actions.reshape(T * N, -1))
         self.st.value_predictions[:T].copy_(out[0].view(T, N, 1))
         self.st.action_log_probs.copy_(out[1].view(T, N, 1))
@@ -174,7 +177,9 @@ class GpuSide:
             self.algo = api.PPO(self.policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef,
                                 w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
             g = torch.Generator().manual_seed(param_seed)  # the same GLOBAL permutations on every rank
-            self.d_perms = [torch.randperm(w.rows * world, generator=g).cuda() for _ in range(w.num_epoch)]
+            # recurrent policies draw randperm(N) per epoch (recurrent_generator.cpp:38), the others randperm(T*N)
+            self.perm_len = w.N if gru else w.rows * world
+            self.d_perms = [torch.randperm(self.perm_len, generator=g).cuda() for _ in range(w.num_epoch)]
         else:
             self.algo = api.A2C(self.policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
         self.comm = None
@@ -188,7 +193,7 @@ class GpuSide:
         self.e2e_calls = 0
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.pinned.values()) + self.pinned_nv.numel() * 4
         if w.algo == "ppo":
-            self.h2d_bytes += w.num_epoch * w.rows * world * 8
+            self.h2d_bytes += w.num_epoch * self.perm_len * 8
         self.d2h_bytes = 64
 
     def step_device(self):

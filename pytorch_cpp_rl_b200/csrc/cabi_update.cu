@@ -286,7 +286,7 @@ int fill_gru_policy_args(GruUpdateArgs &a, const cpprl_b200_policy &p, int64_t T
     a.norm_mean = p.d_norm_mean;
     a.norm_var = p.d_norm_var;
     a.norm_clip = p.d_norm_clip;
-    if (T > 0x7fffffffll / (kGruGates * 8) || gru_update_smem_bytes(a.Dp, a.A, a.Ap, static_cast<int>(T)) > 227 * 1024)
+    if (T > 0x7fffffffll / (kGruGates * 8) || gru_update_smem_bytes(a.Dp, a.A, a.Ap, a.head, static_cast<int>(T)) > 227 * 1024)
         return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": sequence length x observation size needs more than 227 KB of shared memory on the recurrent path");
     return 0;
 }
@@ -663,6 +663,8 @@ static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
     if (h->gru)
     {
         h->gargs.perm = reinterpret_cast<const long long *>(d_perm);
+        h->gargs.dbg_clocks = g_dbg_clocks;
+        h->gargs.dbg_step = g_dbg_step;
         KernelTimer timer("update", h->stream);
         int rc = launch_gru_update(h->gargs, 1, h->stream);
         if (rc == 0)

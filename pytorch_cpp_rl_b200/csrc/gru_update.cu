@@ -1,24 +1,26 @@
-// gru_update.cu — fused PPO update (and forward evaluation) for the GRU-fronted MlpBase.
+// gru_update.cu — fused PPO / A2C update (and forward evaluation) for the GRU-fronted MlpBase.
 //
 // Replaces, for recurrent policies:
 //   RecurrentGenerator::next       src/generators/recurrent_generator.cpp:47-98   (one environment per minibatch)
 //   NNBase::forward_gru            src/model/nn_base.cpp:47-114   (run splitting at mask zeros, state never carried
 //                                                                  across runs: every run restarts from hxs * mask)
-//   MlpBase::forward, heads, log-prob / entropy, PPO loss, autograd backward (BPTT), Adam step, KL stop, statistics
-//                                  src/model/mlp_base.cpp:47-64, src/algorithms/ppo.cpp:86-146
+//   MlpBase::forward, heads, log-prob / entropy, PPO / A2C loss, autograd backward (BPTT), Adam step, KL stop,
+//   statistics                     src/model/mlp_base.cpp:47-64, src/algorithms/ppo.cpp:86-146, a2c.cpp:58-85
 //
 // The reference's recurrent PPO is a strictly serial chain: N minibatches per epoch, each ONE environment's T steps,
 // each followed by an optimiser step.  One CTA therefore walks the whole epoch (no grid barrier, no partial-gradient
-// exchange): per minibatch it
-//   1. runs the GRU forward over the T steps (W_hh rows in registers, one matrix-vector product per step), keeping
-//      h, r, z, n and W_hn h + b_hn on a tape in L2;
-//   2. pushes the T outputs through both towers, heads, loss and the hand-derived backward in tiles of 32 rows out of
-//      shared memory (same building blocks as mlp_update.cu), accumulating the 64x64 weight gradients in registers
-//      and writing dL/dh_t to the tape;
-//   3. decides the KL stop (ppo.cpp:100-104), applies Adam to the tower / head parameters from registers;
-//   4. back-propagates through time (W_hh columns in registers; dW_hh accumulated in the same registers' twins) and
-//      applies Adam to the GRU parameters.
-// Forward evaluation (Policy::evaluate_actions / get_values) launches one CTA per agent.
+// exchange) with every tower / head / GRU-input parameter RESIDENT in shared memory for the whole launch: Adam
+// writes the new value to the shared-memory images and to the flat parameter buffer at the same time.  Per minibatch:
+//   1. GRU forward over the T steps (W_hh rows in registers, one matrix-vector product per step); h, r, z, n and
+//      W_hn h + b_hn go to a tape in L2;
+//   2. the T outputs run through both towers, heads, loss and the hand-derived backward in tiles of 32 rows out of
+//      shared memory (the building blocks of mlp_update.cu); the 64x64 weight gradients accumulate in registers,
+//      dL/dh_t goes to the tape;
+//   3. KL stop (ppo.cpp:100-104), Adam on the tower / head parameters straight from the registers;
+//   4. back-propagation through time: the tape streams back through shared memory in chunks of 8 steps (cp.async,
+//      double buffered), W_hh columns and dW_hh live in registers; Adam on the GRU parameters.
+// A2C and forward evaluation (Policy::evaluate_actions / get_values) launch one CTA per environment; A2C sums the
+// per-environment gradients in global memory and the stand-alone RMSprop kernel applies them.
 #include <math.h>
 
 #include "common.cuh"
@@ -31,67 +33,50 @@ namespace
 {
 constexpr int GR = 32; // tile rows of the tower phases
 constexpr int GLD = Tile<GR>::LD;
+constexpr int kMat = kHid * kHid;
+// per-tower weight image: W1 forward / backward layouts, W2 forward / backward layouts, permuted biases
+constexpr int kW1T = 0, kW1N = kMat, kW2T = 2 * kMat, kW2N = 3 * kMat, kB1 = 4 * kMat, kB2 = 4 * kMat + kHid;
+constexpr int kTowerImg = 4 * kMat + 2 * kHid;
+// "tile" region: tower tiles X, H1[2], H2[2] (5 x 64 x GLD floats) during phase 2; during BPTT two staging buffers
+// of kChunk steps x 6 tape rows and the dW_ih accumulator
+constexpr int kTileMat = kHid * GLD;
+constexpr int kChunk = 8;
+constexpr int kChunkFloats = 6 * kChunk * kHid;
+constexpr int kTileFloats = 2 * kChunkFloats + kGruGates * kGruMaxObs; // 12288 >= 5 * kTileMat = 11520
+static_assert(kTileFloats >= 5 * kTileMat, "tile region");
+// small-gradient vector: biases of the towers, then a mirror of the parameter tail [wv, bv, (scale_log), wo, bo]
+constexpr int kGsBias = 0, kGsTail = 4 * kHid;
+
+// Padded shared-memory layouts of the per-step vectors: the four lanes of a quad read four different slices with
+// 16-byte loads, so consecutive slices start 4 banks past a multiple of 16 (conflict-free)
+constexpr int kHcStride = 80;   // hidden state: slices of 16 floats, padded to 20
+constexpr int kDghStride = 208; // dL/d(W_hh h + b_hh): slices of 48 floats, padded to 52
+__device__ __forceinline__ int hc_pos(int j) { return j + 4 * (j >> 4); }
+__device__ __forceinline__ int dgh_pos(int g) { return g + 4 * (g / 48); }
 
 struct GruSmem
 {
-    int w1t[2], w1n[2], w2t[2], w2n[2], b1[2], b2[2], wo, bo, wv, bv, slog, sig; // weight image
-    int bih, bhh, gwih;                                                          // GRU biases, gradient of W_ih
-    int x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, stat;    // tower tile
-    int gs;                                                                       // small gradients + statistics
-    int hcur, gate, dgi, dgh, dhz, dhn, hprev, xseq, mseq, cut, misc, total;      // GRU step state
+    int tw, wo, bo, wv, bv, sig;                                        // resident weights
+    int wiht, bih, bhh;                                                 // resident GRU input weights [d][gate], biases
+    int tile, logit, dlogit, val, dval, ret, oldlp, adv, act, stat, gs; // tower tile, small gradients + statistics
+    int gs_stat, tail_len;
+    int hcur, dgh, xseq, mseq, cut, total;                              // GRU step state
 };
 
-// offsets (in floats) inside `gs`
-struct GsLayout
-{
-    int b1[2], b2[2], wv, bv, wo, bo, slog, stat, bih, bhh, total;
-};
-
-__host__ __device__ inline GsLayout make_gs(int A)
-{
-    GsLayout g;
-    int o = 0;
-    for (int t = 0; t < 2; ++t)
-        g.b1[t] = o, o += kHid, g.b2[t] = o, o += kHid;
-    g.wv = o, o += kHid;
-    g.bv = o, o += 4;
-    g.wo = o, o += A * kHid;
-    g.bo = o, o += (A + 3) & ~3;
-    g.slog = o, o += (A + 3) & ~3;
-    g.stat = o, o += 8;
-    g.bih = o, o += kGruGates;
-    g.bhh = o, o += kGruGates;
-    g.total = o;
-    return g;
-}
-
-__host__ __device__ inline GruSmem make_gru_smem(int Dp, int A, int Ap, int T)
+__host__ __device__ inline GruSmem make_gru_smem(int Dp, int A, int Ap, int head, int T)
 {
     GruSmem s;
     int o = 0;
-    for (int t = 0; t < 2; ++t)
-    {
-        s.w1t[t] = o, o += kHid * kHid;
-        s.w1n[t] = o, o += kHid * kHid;
-        s.w2t[t] = o, o += kHid * kHid;
-        s.w2n[t] = o, o += kHid * kHid;
-        s.b1[t] = o, o += kHid;
-        s.b2[t] = o, o += kHid;
-    }
+    s.tw = o, o += 2 * kTowerImg;
     s.wo = o, o += Ap * kHid;
     s.bo = o, o += Ap;
     s.wv = o, o += kHid;
     s.bv = o, o += 4;
-    s.slog = o, o += Ap;
     s.sig = o, o += 2 * Ap;
+    s.wiht = o, o += kGruGates * Dp;
     s.bih = o, o += kGruGates;
     s.bhh = o, o += kGruGates;
-    s.x = o, o += kHid * GLD;
-    s.gwih = s.x; // dW_ih accumulates during BPTT, when the tower tiles (5 * 64 * GLD floats >= 192 * Dp) are dead
-    for (int t = 0; t < 2; ++t)
-        s.h1[t] = o, o += kHid * GLD;
-    for (int t = 0; t < 2; ++t)
-        s.h2[t] = o, o += kHid * GLD;
+    s.tile = o, o += kTileFloats;
     s.logit = o, o += Ap * GLD;
     s.dlogit = o, o += Ap * GLD;
     s.val = o, o += GLD;
@@ -101,53 +86,71 @@ __host__ __device__ inline GruSmem make_gru_smem(int Dp, int A, int Ap, int T)
     s.adv = o, o += GLD;
     s.act = o, o += Ap * GLD;
     s.stat = o, o += (5 + Ap) * GLD;
-    s.gs = o, o += (make_gs(A).total + 3) & ~3;
-    s.hcur = o, o += kHid;
-    s.gate = o, o += 4 * kHid;
-    s.dgi = o, o += kGruGates;
-    s.dgh = o, o += kGruGates;
-    s.dhz = o, o += kHid;
-    s.dhn = o, o += kHid;
-    s.hprev = o, o += kHid;
+    s.tail_len = kHid + 1 + (head == 1 ? A : 0) + A * kHid + A;
+    s.gs = o;
+    s.gs_stat = kGsTail + ((s.tail_len + 3) & ~3);
+    o += s.gs_stat + 8;
+    s.hcur = o, o += 2 * kHcStride; // double buffered state
+    s.dgh = o, o += 2 * kDghStride; // double buffered dL/d(W_hh h + b_hh)
     s.xseq = o, o += ((T * Dp) + 3) & ~3;
     s.mseq = o, o += (T + 3) & ~3;
     s.cut = o, o += (T + 4) & ~3;
-    s.misc = o, o += 32;
     s.total = o;
     return s;
 }
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+// Gate non-linearities of the serial recurrence: every instruction here is on the per-step latency chain, so the
+// exponential is the two-instruction ex2 form and the quotient the approximate division (2 ulp); the absolute error
+// stays below 2e-7, the level of the correctly rounded functions' own rounding.
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float tanhf_(float x)
+{
+    const float e = __expf(2.f * fminf(fmaxf(x, -15.f), 15.f)); // tanh(+-15) = +-1 in fp32
+    return 1.f - __fdividef(2.f, e + 1.f);
+}
 
-__global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpdateArgs a)
+__device__ __forceinline__ void cp_async16(float *dst_smem, const float *src)
+{
+    const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(dst_smem));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const __grid_constant__ GruUpdateArgs a)
 {
     extern __shared__ __align__(16) float smem[];
-    const GruSmem sp = make_gru_smem(a.Dp, a.A, a.Ap, a.T);
-    const GsLayout gl = make_gs(a.A);
+    const GruSmem sp = make_gru_smem(a.Dp, a.A, a.Ap, a.head, a.T);
     const GruParamOffsets &po = a.po;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tower = tid >> 7, u = tid & 127, jb = u & 15, rb = u >> 4;
     const int D = a.D, Dp = a.Dp, A = a.A, T = a.T, N = a.N;
     const bool training = a.algo != kAlgoForward;
+    // PPO: one environment per minibatch, T rows.  A2C: one batch of all T * N rows, one CTA per environment, the
+    // gradient summed over the CTAs in global memory (grad_out) and applied by the RMSprop kernel that follows.
+    const bool ppo = a.algo == kAlgoPPO;
     float *GS = smem + sp.gs;
-    float *HCUR = smem + sp.hcur, *GATE = smem + sp.gate, *DGI = smem + sp.dgi, *DGH = smem + sp.dgh;
-    float *DHZ = smem + sp.dhz, *DHN = smem + sp.dhn, *HPREV = smem + sp.hprev;
-    float *XSEQ = smem + sp.xseq, *MSEQ = smem + sp.mseq, *MISC = smem + sp.misc;
+    float *HCUR = smem + sp.hcur, *DGH = smem + sp.dgh;
+    float *XSEQ = smem + sp.xseq, *MSEQ = smem + sp.mseq;
     int *CUT = reinterpret_cast<int *>(smem + sp.cut);
-    float *BIH = smem + sp.bih, *BHH = smem + sp.bhh, *GWIH = smem + sp.gwih;
-    float *X = smem + sp.x;
-    float *h1t = smem + sp.h1[0] + tower * (kHid * GLD), *h2t = smem + sp.h2[0] + tower * (kHid * GLD);
+    float *WIHT = smem + sp.wiht, *BIH = smem + sp.bih, *BHH = smem + sp.bhh;
+    float *TILE = smem + sp.tile;
+    float *X = TILE;
+    float *h1t = TILE + (1 + tower) * kTileMat, *h2t = TILE + (3 + tower) * kTileMat;
     float *LOGIT = smem + sp.logit, *DLOGIT = smem + sp.dlogit, *VAL = smem + sp.val, *DVAL = smem + sp.dval;
     float *RET = smem + sp.ret, *OLDLP = smem + sp.oldlp, *ADV = smem + sp.adv, *ACT = smem + sp.act, *STAT = smem + sp.stat;
     float *SIG = smem + sp.sig;
-    const float *w1t_img = smem + sp.w1t[tower], *w1n_img = smem + sp.w1n[tower];
-    const float *w2t_img = smem + sp.w2t[tower], *w2n_img = smem + sp.w2n[tower];
-    const float *b1_img = smem + sp.b1[tower], *b2_img = smem + sp.b2[tower];
-    const float *wo_img = smem + sp.wo, *bo_img = smem + sp.bo, *wv_img = smem + sp.wv, *bv_img = smem + sp.bv;
+    float *tw_img = smem + sp.tw + tower * kTowerImg; // this thread's tower
+    float *wo_img = smem + sp.wo, *bo_img = smem + sp.bo, *wv_img = smem + sp.wv, *bv_img = smem + sp.bv;
+    // small-gradient vector: offsets of the tail mirror [wv, bv, (scale_log), wo, bo]
+    const int gt_wv = kGsTail, gt_bv = kGsTail + kHid, gt_slog = gt_bv + 1, gt_wo = gt_slog + (a.head == 1 ? A : 0),
+              gt_bo = gt_wo + A * kHid;
     // forward evaluation keeps only the hidden states (one tape per CTA), training all six
     float *tape = a.tape + static_cast<size_t>(blockIdx.x) * (training ? kGruTapes : 1) * T * kHid;
-    float *TH = tape, *TR = tape + T * kHid, *TZ = tape + 2 * T * kHid, *TN = tape + 3 * T * kHid,
-          *TG = tape + 4 * T * kHid, *TDX = tape + 5 * T * kHid;
+    // tape rows: h [T][64]; {r, z, n, W_hn h + b_hn} interleaved [T][64][4] (one 16-byte store per step and unit);
+    // dL/dh from the towers [T][64]
+    float *TH = tape, *TRZNG = tape + T * kHid, *TDX = tape + 5 * T * kHid;
 
     float adv_mean = 0.f, adv_denom = 1.f;
     long long opt_step0 = 0;
@@ -168,56 +171,69 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             adv_denom = static_cast<float>(sqrt(var)) + 1e-5f;
         }
     }
-    // PPO: one environment per minibatch, T rows.  A2C: one batch of all T * N rows, one CTA per environment, the
-    // gradient summed over the CTAs in global memory (grad_out) and applied by the RMSprop kernel that follows.
-    const bool ppo = a.algo == kAlgoPPO;
     const float inv_b = 1.f / static_cast<float>(ppo ? T : T * N);
     const float ce_b = a.c_entropy * inv_b;
     const int n_seq = ppo ? a.n_mb : 1;
 
+    // ---- (0) once per launch: weight images from the flat parameters ---------------------------------------------
+    for (int i = tid; i < 2 * 2 * kMat; i += kGruThreads)
+    {
+        const int t = i >> 13, layer = (i >> 12) & 1, e = i & 4095, j = e >> 6, k = e & 63;
+        const float v = a.params[(layer ? po.w2[t] : po.w1[t]) + e];
+        float *img = smem + sp.tw + t * kTowerImg;
+        img[(layer ? kW2T : kW1T) + k * kHid + perm16(j)] = v; // forward:  out[j] += W[j][k] in[k]
+        img[(layer ? kW2N : kW1N) + j * kHid + perm16(k)] = v; // backward: out[k] += W[j][k] dz[j]
+    }
+    for (int i = tid; i < 2 * kHid; i += kGruThreads)
+    {
+        const int t = i >> 6, j = i & 63;
+        float *img = smem + sp.tw + t * kTowerImg;
+        img[kB1 + perm16(j)] = a.params[po.b1[t] + j];
+        img[kB2 + perm16(j)] = a.params[po.b2[t] + j];
+    }
+    for (int i = tid; i < A * kHid; i += kGruThreads)
+        wo_img[i] = a.params[po.wo + i];
+    for (int i = tid; i < kHid; i += kGruThreads)
+        wv_img[i] = a.params[po.wv + i];
+    if (tid < A)
+    {
+        bo_img[tid] = a.params[po.bo + tid];
+        if (a.head == 1)
+        {
+            const float sigma = expf(a.params[po.slog + tid]);
+            SIG[2 * tid] = sigma * sigma;
+            SIG[2 * tid + 1] = logf(sigma);
+        }
+    }
+    if (tid == 0)
+        bv_img[0] = a.params[po.bv];
+    for (int i = tid; i < kGruGates * Dp; i += kGruThreads)
+    {
+        const int d = i / kGruGates, g = i - d * kGruGates;
+        WIHT[i] = d < D ? a.params[po.wih + g * D + d] : 0.f; // [d][gate]: conflict-free for gate-per-thread reads
+    }
+    for (int i = tid; i < kGruGates; i += kGruThreads)
+    {
+        BIH[i] = a.params[po.bih + i];
+        BHH[i] = a.params[po.bhh + i];
+    }
+    float norm_clip = 0.f;
+    if (a.norm_mean)
+        norm_clip = __ldg(a.norm_clip);
+
+#define GRU_MARK(slot)                                                  \
+    do                                                                  \
+    {                                                                   \
+        if (a.dbg_clocks && tid == 0 && mb == a.dbg_step)               \
+            a.dbg_clocks[blockIdx.x * 32 + (slot)] = clock64();         \
+    } while (0)
     for (int mb = 0; mb < n_seq; ++mb)
     {
+        GRU_MARK(0);
         const int agent = ppo ? static_cast<int>(a.perm[mb]) : static_cast<int>(blockIdx.x);
-        // ---- (0) weight image from the current parameters (L2 loads: the previous minibatch's Adam wrote them) ----
-        for (int i = tid; i < 2 * 2 * kHid * kHid; i += kGruThreads)
-        {
-            const int t = i >> 13, layer = (i >> 12) & 1, e = i & 4095, j = e >> 6, k = e & 63;
-            const float v = __ldcg(a.params + (layer ? po.w2[t] : po.w1[t]) + e);
-            smem[(layer ? sp.w2t[t] : sp.w1t[t]) + k * kHid + perm16(j)] = v; // forward:  out[j] += W[j][k] in[k]
-            smem[(layer ? sp.w2n[t] : sp.w1n[t]) + j * kHid + perm16(k)] = v; // backward: out[k] += W[j][k] dz[j]
-        }
-        for (int i = tid; i < 2 * kHid; i += kGruThreads)
-        {
-            const int t = i >> 6, j = i & 63;
-            smem[sp.b1[t] + perm16(j)] = __ldcg(a.params + po.b1[t] + j);
-            smem[sp.b2[t] + perm16(j)] = __ldcg(a.params + po.b2[t] + j);
-        }
-        for (int i = tid; i < A * kHid; i += kGruThreads)
-            smem[sp.wo + i] = __ldcg(a.params + po.wo + i);
-        for (int i = tid; i < kHid; i += kGruThreads)
-            smem[sp.wv + i] = __ldcg(a.params + po.wv + i);
-        if (tid < A)
-        {
-            smem[sp.bo + tid] = __ldcg(a.params + po.bo + tid);
-            if (a.head == 1)
-            {
-                const float sl = __ldcg(a.params + po.slog + tid);
-                const float sigma = expf(sl);
-                smem[sp.slog + tid] = sl;
-                SIG[2 * tid] = sigma * sigma;
-                SIG[2 * tid + 1] = logf(sigma);
-            }
-        }
-        if (tid == 0)
-            smem[sp.bv] = __ldcg(a.params + po.bv);
-        for (int i = tid; i < kGruGates; i += kGruThreads)
-        {
-            BIH[i] = __ldcg(a.params + po.bih + i);
-            BHH[i] = __ldcg(a.params + po.bhh + i);
-        }
-        for (int i = tid; i < gl.total; i += kGruThreads)
+        // ---- stage the sequence: observations (normalised), masks, run boundaries; clear the small gradients -------
+        for (int i = tid; i < sp.gs_stat + 8; i += kGruThreads)
             GS[i] = 0.f;
-        // the sequence's observations, masks and run boundaries
         for (int i = tid; i < T * Dp; i += kGruThreads)
         {
             const int t = i / Dp, d = i - t * Dp;
@@ -228,9 +244,8 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                 if (a.norm_mean)
                 {
                     // ObservationNormalizer::process_observation (observation_normalizer.cpp:69-74)
-                    const float clip = __ldg(a.norm_clip);
                     x = (x - __ldg(a.norm_mean + d)) / sqrtf(__ldg(a.norm_var + d) + 1e-8f);
-                    x = fminf(fmaxf(x, -clip), clip);
+                    x = fminf(fmaxf(x, -norm_clip), norm_clip);
                 }
             }
             XSEQ[i] = x;
@@ -251,86 +266,89 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
         }
         if (tid == 0)
             CUT[T] = 1;
-        const float hx0 = tid < kHid ? __ldg(a.hxs + static_cast<size_t>(agent) * kHid + tid) : 0.f;
         __syncthreads();
 
-        // ---- (1) GRU forward: thread g < 192 owns row g of W_hh (registers) ---------------------------------------
+        GRU_MARK(1);
+        // ---- (1) GRU forward ----------------------------------------------------------------------------------------
+        // Thread (k = tid / 4, p = tid % 4): the four lanes of a quad share hidden unit k and split the 64 recurrent
+        // inputs (and the observation columns) four ways; W_hh[{r,z,n} x 64 + k][16p .. 16p+15] lives in registers.
+        // Per step: partial dot products (FFMA2), two shuffles, the gate math in every lane, ONE barrier (the state
+        // is double buffered).
+        const int kk = tid >> 2, pp = tid & 3;
+        const float hx0 = __ldg(a.hxs + static_cast<size_t>(agent) * kHid + kk);
         {
-            float whh[kHid], wih[kGruMaxObs];
+            float2 wr[8], wz[8], wn[8];
 #pragma unroll
-            for (int d = 0; d < kGruMaxObs; ++d)
-                wih[d] = (tid < kGruGates && d < D) ? __ldcg(a.params + po.wih + tid * D + d) : 0.f;
-            if (tid < kGruGates)
+            for (int q = 0; q < 4; ++q)
             {
-#pragma unroll
-                for (int k = 0; k < kHid; k += 4)
-                {
-                    const float4 w = __ldcg(reinterpret_cast<const float4 *>(a.params + po.whh + tid * kHid + k));
-                    whh[k] = w.x, whh[k + 1] = w.y, whh[k + 2] = w.z, whh[k + 3] = w.w;
-                }
+                const float4 r4 = __ldcg(reinterpret_cast<const float4 *>(a.params + po.whh + (kk) * kHid + 16 * pp) + q);
+                const float4 z4 = __ldcg(reinterpret_cast<const float4 *>(a.params + po.whh + (kHid + kk) * kHid + 16 * pp) + q);
+                const float4 n4 = __ldcg(reinterpret_cast<const float4 *>(a.params + po.whh + (2 * kHid + kk) * kHid + 16 * pp) + q);
+                wr[2 * q] = make_float2(r4.x, r4.y), wr[2 * q + 1] = make_float2(r4.z, r4.w);
+                wz[2 * q] = make_float2(z4.x, z4.y), wz[2 * q + 1] = make_float2(z4.z, z4.w);
+                wn[2 * q] = make_float2(n4.x, n4.y), wn[2 * q + 1] = make_float2(n4.z, n4.w);
             }
+            // input-side partial sums of step t for this lane's observation columns d = p, p+4, ...; lane 0 also carries
+            // the biases (b_ir + b_hr, b_iz + b_hz, b_in; b_hn goes with the recurrent part of the n gate)
+            const float b_r = pp == 0 ? BIH[kk] + BHH[kk] : 0.f, b_z = pp == 0 ? BIH[kHid + kk] + BHH[kHid + kk] : 0.f;
+            const float b_in = pp == 0 ? BIH[2 * kHid + kk] : 0.f, b_hn = pp == 0 ? BHH[2 * kHid + kk] : 0.f;
+            float gir, giz, gin;
+            auto input_partials = [&](int t)
+            {
+                gir = b_r, giz = b_z, gin = b_in;
+                for (int d = pp; d < Dp; d += 4)
+                {
+                    const float x = XSEQ[t * Dp + d];
+                    gir = fmaf(WIHT[d * kGruGates + kk], x, gir);
+                    giz = fmaf(WIHT[d * kGruGates + kHid + kk], x, giz);
+                    gin = fmaf(WIHT[d * kGruGates + 2 * kHid + kk], x, gin);
+                }
+            };
+            input_partials(0);
+            // every run restarts from the ORIGINAL hxs times the run's first mask (nn_base.cpp:98-102)
+            if (pp == 0)
+                HCUR[hc_pos(kk)] = hx0 * MSEQ[0];
+            __syncthreads();
             for (int t = 0; t < T; ++t)
             {
-                if (t == 0 || CUT[t])
-                {
-                    // every run restarts from the ORIGINAL hxs times the run's first mask (nn_base.cpp:98-102)
-                    if (tid < kHid)
-                        HCUR[tid] = hx0 * MSEQ[t];
-                    __syncthreads();
-                }
-                if (tid < kGruGates)
-                {
-                    float gi = BIH[tid];
+                const float *hc = HCUR + (t & 1) * kHcStride;
+                const float hp = hc[hc_pos(kk)];
+                float2 sr = make_float2(gir, 0.f), sz = make_float2(giz, 0.f), sn = make_float2(b_hn, 0.f);
 #pragma unroll
-                    for (int d = 0; d < kGruMaxObs; d += 4)
-                        if (d < Dp)
-                        {
-                            const float4 x = *reinterpret_cast<const float4 *>(XSEQ + t * Dp + d);
-                            gi = fmaf(wih[d], x.x, gi);
-                            gi = fmaf(wih[d + 1], x.y, gi);
-                            gi = fmaf(wih[d + 2], x.z, gi);
-                            gi = fmaf(wih[d + 3], x.w, gi);
-                        }
-                    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-                    for (int k = 0; k < kHid; k += 4)
-                    {
-                        const float4 h = *reinterpret_cast<const float4 *>(HCUR + k);
-                        a0 = fmaf(whh[k], h.x, a0);
-                        a1 = fmaf(whh[k + 1], h.y, a1);
-                        a2 = fmaf(whh[k + 2], h.z, a2);
-                        a3 = fmaf(whh[k + 3], h.w, a3);
-                    }
-                    const float gh = BHH[tid] + ((a0 + a1) + (a2 + a3));
-                    if (tid < 2 * kHid)
-                        GATE[tid] = gi + gh; // r, z pre-activations
-                    else
-                    {
-                        GATE[tid] = gi;       // W_in x + b_in
-                        GATE[tid + kHid] = gh; // W_hn h + b_hn
-                    }
-                }
-                __syncthreads();
-                if (tid < kHid)
+                for (int q = 0; q < 4; ++q)
                 {
-                    const float r = sigmoidf_(GATE[tid]), z = sigmoidf_(GATE[kHid + tid]);
-                    const float ghn = GATE[3 * kHid + tid];
-                    const float n = tanhf(GATE[2 * kHid + tid] + r * ghn);
-                    const float hp = HCUR[tid];
-                    const float hn = (1.f - z) * n + z * hp;
-                    const int o = t * kHid + tid;
+                    const float4 h = *reinterpret_cast<const float4 *>(hc + 20 * pp + 4 * q);
+                    const float2 lo = make_float2(h.x, h.y), hi = make_float2(h.z, h.w);
+                    sr = __ffma2_rn(wr[2 * q], lo, sr), sr = __ffma2_rn(wr[2 * q + 1], hi, sr);
+                    sz = __ffma2_rn(wz[2 * q], lo, sz), sz = __ffma2_rn(wz[2 * q + 1], hi, sz);
+                    sn = __ffma2_rn(wn[2 * q], lo, sn), sn = __ffma2_rn(wn[2 * q + 1], hi, sn);
+                }
+                float pr = sr.x + sr.y, pz = sz.x + sz.y, pn = sn.x + sn.y, pi = gin;
+                pr += __shfl_xor_sync(0xffffffffu, pr, 1), pz += __shfl_xor_sync(0xffffffffu, pz, 1);
+                pn += __shfl_xor_sync(0xffffffffu, pn, 1), pi += __shfl_xor_sync(0xffffffffu, pi, 1);
+                pr += __shfl_xor_sync(0xffffffffu, pr, 2), pz += __shfl_xor_sync(0xffffffffu, pz, 2);
+                pn += __shfl_xor_sync(0xffffffffu, pn, 2), pi += __shfl_xor_sync(0xffffffffu, pi, 2);
+                const float r = sigmoidf_(pr), z = sigmoidf_(pz);
+                const float n = tanhf_(pi + r * pn); // n = tanh(W_in x + b_in + r * (W_hn h + b_hn))
+                const float hn = (1.f - z) * n + z * hp;
+                const int o = t * kHid + kk;
+                if (pp == 0)
+                {
                     TH[o] = hn;
-                    if (training)
-                        TR[o] = r, TZ[o] = z, TN[o] = n, TG[o] = ghn;
-                    HCUR[tid] = hn;
+                    // state seen by step t+1: a run boundary restarts from hxs
+                    HCUR[((t + 1) & 1) * kHcStride + hc_pos(kk)] = (t + 1 < T && CUT[t + 1]) ? hx0 * MSEQ[t + 1] : hn;
                 }
+                else if (training && pp == 1)
+                    *reinterpret_cast<float4 *>(TRZNG + 4 * o) = make_float4(r, z, n, pn);
+                if (t + 1 < T)
+                    input_partials(t + 1);
                 __syncthreads();
             }
-            if (!training && a.step_mode && a.out_hxs && tid < kHid)
-                a.out_hxs[static_cast<size_t>(agent) * kHid + tid] = HCUR[tid];
+            if (!training && a.step_mode && a.out_hxs && pp == 0)
+                a.out_hxs[static_cast<size_t>(agent) * kHid + kk] = HCUR[(T & 1) * kHcStride + hc_pos(kk)];
         }
-        __syncthreads();
 
+        GRU_MARK(2);
         // ---- (2) towers over tiles of 32 steps: forward, loss, backward; dW1 / dW2 accumulate in registers -----------
         float2 accW1[8][4], accW2[8][4];
 #pragma unroll
@@ -371,14 +389,14 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             // P1 / P2: both layers of both towers
             {
                 float acc[4][4];
-                gemm_cf<GR>(w1t_img, X, kHid, jb, rb, acc);
-                store_tanh<GR>(h1t, b1_img, jb, rb, acc);
+                gemm_cf<GR>(tw_img + kW1T, X, kHid, jb, rb, acc);
+                store_tanh<GR>(h1t, tw_img + kB1, jb, rb, acc);
             }
             __syncthreads();
             {
                 float acc[4][4];
-                gemm_cf<GR>(w2t_img, h1t, kHid, jb, rb, acc);
-                store_tanh<GR>(h2t, b2_img, jb, rb, acc);
+                gemm_cf<GR>(tw_img + kW2T, h1t, kHid, jb, rb, acc);
+                store_tanh<GR>(h2t, tw_img + kB2, jb, rb, acc);
             }
             __syncthreads();
             // P3: heads
@@ -387,7 +405,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                 const int o = e / GR, r = e - o * GR;
                 const bool is_value = o == A;
                 const float *w = is_value ? wv_img : wo_img + o * kHid;
-                const float *h = smem + (is_value ? sp.h2[1] : sp.h2[0]) + r;
+                const float *h = TILE + (is_value ? 4 : 3) * kTileMat + r;
                 float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll 4
                 for (int k = 0; k < kHid; k += 4)
@@ -529,13 +547,13 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                     const float *src;
                     int dst;
                     if (item < 5)
-                        src = STAT + item * GLD, dst = gl.stat + item;
+                        src = STAT + item * GLD, dst = sp.gs_stat + item;
                     else if (item < 5 + A)
-                        src = DLOGIT + (item - 5) * GLD, dst = gl.bo + (item - 5);
+                        src = DLOGIT + (item - 5) * GLD, dst = gt_bo + (item - 5);
                     else if (item == 5 + A)
-                        src = DVAL, dst = gl.bv;
+                        src = DVAL, dst = gt_bv;
                     else
-                        src = STAT + (5 + item - (6 + A)) * GLD, dst = gl.slog + (item - (6 + A));
+                        src = STAT + (5 + item - (6 + A)) * GLD, dst = gt_slog + (item - (6 + A));
                     const float sum = warp_sum(src[lane]);
                     if (lane == 0)
                         GS[dst] += sum;
@@ -549,7 +567,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                 const float *dout = (tower == 0 ? DLOGIT : DVAL) + half * (GR / 2);
                 const float *wh = (tower == 0 ? wo_img : wv_img) + k;
                 float *h2 = h2t + k * GLD + half * (GR / 2);
-                const int gbase = (tower == 0 ? gl.wo : gl.wv) + k;
+                const int gbase = (tower == 0 ? gt_wo : gt_wv) + k;
                 float4 h[NQ], dh[NQ];
 #pragma unroll
                 for (int qd = 0; qd < NQ; ++qd)
@@ -588,7 +606,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                     bsum += (dz.x + dz.y) + (dz.z + dz.w);
                     *reinterpret_cast<float4 *>(h2 + 4 * qd) = dz;
                 }
-                atomicAdd(&GS[gl.b2[tower] + k], bsum);
+                atomicAdd(&GS[kGsBias + tower * 2 * kHid + kHid + k], bsum);
             }
             __syncthreads();
             // P6: dW2 += dz2 h1^T
@@ -597,7 +615,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             // P7: dz1 = (W2^T dz2) * (1 - h1^2), in place over H1; db1
             {
                 float acc[4][4];
-                gemm_cf<GR>(w2n_img, h2t, kHid, jb, rb, acc);
+                gemm_cf<GR>(tw_img + kW2N, h2t, kHid, jb, rb, acc);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                 {
@@ -609,7 +627,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
                     dz.z = acc[q][2] * (1.f - h.z * h.z);
                     dz.w = acc[q][3] * (1.f - h.w * h.w);
                     *reinterpret_cast<float4 *>(hp) = dz;
-                    atomicAdd(&GS[gl.b1[tower] + jb + 16 * q], (dz.x + dz.y) + (dz.z + dz.w));
+                    atomicAdd(&GS[kGsBias + tower * 2 * kHid + jb + 16 * q], (dz.x + dz.y) + (dz.z + dz.w));
                 }
             }
             __syncthreads();
@@ -617,7 +635,7 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             grad_w2_acc<GR>(h1t, X, u, accW1);
             {
                 float acc[4][4];
-                gemm_cf<GR>(w1n_img, h1t, kHid, jb, rb, acc);
+                gemm_cf<GR>(tw_img + kW1N, h1t, kHid, jb, rb, acc);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                     *reinterpret_cast<float4 *>(h2t + (jb + 16 * q) * GLD + 4 * rb) =
@@ -628,16 +646,18 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             {
                 const int r = i >> 6, k = i & 63;
                 if (r < nrows)
-                    TDX[(t0 + r) * kHid + k] = smem[sp.h2[0] + k * GLD + r] + smem[sp.h2[1] + k * GLD + r];
+                    TDX[(t0 + r) * kHid + k] = TILE[3 * kTileMat + k * GLD + r] + TILE[4 * kTileMat + k * GLD + r];
             }
             __syncthreads();
         } // tiles
         if (!training)
             break;
 
+
+        GRU_MARK(3);
         // ---- (3) KL early stop (ppo.cpp:100-104), statistics, Adam on the tower / head parameters -----------------------
-        const float sum_v = GS[gl.stat + 0], sum_a = GS[gl.stat + 1], sum_e = GS[gl.stat + 2], sum_kl = GS[gl.stat + 3],
-                    sum_clip = GS[gl.stat + 4];
+        const float sum_v = GS[sp.gs_stat + 0], sum_a = GS[sp.gs_stat + 1], sum_e = GS[sp.gs_stat + 2],
+                    sum_kl = GS[sp.gs_stat + 3], sum_clip = GS[sp.gs_stat + 4];
         const float kl = sum_kl * inv_b;
         const bool stop = ppo && static_cast<double>(kl) > a.kl_limit;
         if (tid == 0 && !ppo)
@@ -672,159 +692,303 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const GruUpd
             return;
         // bias corrections as host-style doubles (libtorch Adam), t = steps applied so far + 1
         const double tstep = static_cast<double>(opt_step0 + applied + 1);
-        const float step_size = static_cast<float>(a.lr / (1.0 - pow(static_cast<double>(a.beta1), tstep)));
-        const float bc2_sqrt = static_cast<float>(sqrt(1.0 - pow(static_cast<double>(a.beta2), tstep)));
-        auto adam = [&](int gi, float g)
+        const float step_size = ppo ? static_cast<float>(a.lr / (1.0 - pow(static_cast<double>(a.beta1), tstep))) : 0.f;
+        const float bc2_sqrt = ppo ? static_cast<float>(sqrt(1.0 - pow(static_cast<double>(a.beta2), tstep))) : 1.f;
+        // one Adam step of a parameter whose value the caller already holds: state loaded by the caller in batches so
+        // that the L2 round trips overlap; returns the new value
+        auto adam_core = [&](int gi, float g, float p, float m_old, float v_old) -> float
         {
-            if (!ppo)
-            {
-                atomicAdd(a.grad_out + gi, g);
-                return;
-            }
-            const float m = __ldcg(a.opt_m + gi) * a.beta1 + g * (1.f - a.beta1);
-            const float v = __ldcg(a.opt_v + gi) * a.beta2 + (g * g) * (1.f - a.beta2);
+            const float m = m_old * a.beta1 + g * (1.f - a.beta1);
+            const float v = v_old * a.beta2 + (g * g) * (1.f - a.beta2);
             a.opt_m[gi] = m;
             a.opt_v[gi] = v;
-            a.params[gi] = __ldcg(a.params + gi) - step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
-        };
-        auto adam_range = [&](int gs_off, int p_off, int n)
-        {
-            for (int i = tid; i < n; i += kGruThreads)
-                adam(p_off + i, GS[gs_off + i]);
+            const float pn = p - step_size * (m / (sqrtf(v) / bc2_sqrt + a.eps));
+            a.params[gi] = pn;
+            return pn;
         };
         {
             const int kq = u & 15, jq = u >> 4;
+            const int p1 = po.w1[tower], p2 = po.w2[tower];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                {
-                    const int e = (jq + 8 * i) * kHid + kq + 16 * j;
-                    adam(po.w1[tower] + e, accW1[i][j].x + accW1[i][j].y);
-                    adam(po.w2[tower] + e, accW2[i][j].x + accW2[i][j].y);
-                }
-        }
-        for (int t = 0; t < 2; ++t)
-        {
-            adam_range(gl.b1[t], po.b1[t], kHid);
-            adam_range(gl.b2[t], po.b2[t], kHid);
-        }
-        adam_range(gl.wv, po.wv, kHid);
-        adam_range(gl.bv, po.bv, 1);
-        adam_range(gl.wo, po.wo, A * kHid);
-        adam_range(gl.bo, po.bo, A);
-        if (a.head == 1)
-            adam_range(gl.slog, po.slog, A);
-
-        // ---- (4) back-propagation through time ------------------------------------------------------------------------
-        // phase A (threads k < 64): gate derivatives of step t from the tape; phase B (all threads, k = tid / 4, p = tid % 4):
-        // dh_{t-1}[k] = dh_t[k] z[k] + sum_g W_hh[g][k] dgh[g] with gates [48p, 48p + 48) per thread (two shuffles),
-        // dW_hh[g][k] += dgh[g] h_{t-1}[k] in registers.
-        for (int i = tid; i < kGruGates * Dp; i += kGruThreads)
-            GWIH[i] = 0.f; // aliases the tower tiles, dead from here on
-        {
-            const int kk = tid >> 2, pp = tid & 3;
-            float wcol[48], gw[48];
-#pragma unroll
-            for (int i = 0; i < 48; ++i)
             {
-                wcol[i] = __ldcg(a.params + po.whh + (pp * 48 + i) * kHid + kk);
-                gw[i] = 0.f;
+                const int j = jq + 8 * i;
+                if (!ppo)
+                {
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj)
+                    {
+                        const int e = j * kHid + kq + 16 * jj;
+                        atomicAdd(a.grad_out + p1 + e, accW1[i][jj].x + accW1[i][jj].y);
+                        atomicAdd(a.grad_out + p2 + e, accW2[i][jj].x + accW2[i][jj].y);
+                    }
+                    continue;
+                }
+                float m1[4], v1[4], m2[4], v2[4];
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj)
+                {
+                    const int e = j * kHid + kq + 16 * jj;
+                    m1[jj] = __ldcg(a.opt_m + p1 + e), v1[jj] = __ldcg(a.opt_v + p1 + e);
+                    m2[jj] = __ldcg(a.opt_m + p2 + e), v2[jj] = __ldcg(a.opt_v + p2 + e);
+                }
+#pragma unroll
+                for (int jj = 0; jj < 4; ++jj)
+                {
+                    const int k = kq + 16 * jj, e = j * kHid + k;
+                    const int in = j * kHid + perm16(k), it = k * kHid + perm16(j);
+                    const float n1 = adam_core(p1 + e, accW1[i][jj].x + accW1[i][jj].y, tw_img[kW1N + in], m1[jj], v1[jj]);
+                    tw_img[kW1N + in] = n1, tw_img[kW1T + it] = n1;
+                    const float n2 = adam_core(p2 + e, accW2[i][jj].x + accW2[i][jj].y, tw_img[kW2N + in], m2[jj], v2[jj]);
+                    tw_img[kW2N + in] = n2, tw_img[kW2T + it] = n2;
+                }
+            }
+        }
+        {
+            // tower biases: one element per thread
+            const int t = tid >> 7, layer = (tid >> 6) & 1, j = tid & 63;
+            const int gi = (layer ? po.b2[t] : po.b1[t]) + j;
+            float *slot = smem + sp.tw + t * kTowerImg + (layer ? kB2 : kB1) + perm16(j);
+            const float g = GS[kGsBias + tid];
+            if (ppo)
+                *slot = adam_core(gi, g, *slot, __ldcg(a.opt_m + gi), __ldcg(a.opt_v + gi));
+            else
+                atomicAdd(a.grad_out + gi, g);
+        }
+        for (int i = tid; i < sp.tail_len; i += kGruThreads)
+        {
+            // parameter tail [critic_linear.weight, .bias, (scale_log), head weight, head bias]
+            const int gi = po.wv + i;
+            const float g = GS[kGsTail + i];
+            if (!ppo)
+            {
+                atomicAdd(a.grad_out + gi, g);
+                continue;
+            }
+            const float pn = adam_core(gi, g, __ldcg(a.params + gi), __ldcg(a.opt_m + gi), __ldcg(a.opt_v + gi));
+            if (i < kHid)
+                wv_img[i] = pn;
+            else if (i == kHid)
+                bv_img[0] = pn;
+            else
+            {
+                int r = i - (kHid + 1);
+                if (a.head == 1 && r < A)
+                {
+                    const float sigma = expf(pn);
+                    SIG[2 * r] = sigma * sigma;
+                    SIG[2 * r + 1] = logf(sigma);
+                }
+                else
+                {
+                    r -= a.head == 1 ? A : 0;
+                    if (r < A * kHid)
+                        wo_img[r] = pn;
+                    else
+                        bo_img[r - A * kHid] = pn;
+                }
+            }
+        }
+        __syncthreads(); // the tile region changes hands
+
+        GRU_MARK(4);
+        // ---- (4) back-propagation through time ------------------------------------------------------------------------
+        // The tape streams back through shared memory, kChunk steps at a time, one chunk ahead of the step loop.
+        // Thread (k = tid / 4, p = tid % 4).  Per step every lane of quad k forms the gate derivatives of unit k from
+        // the staged tape (dL/dh_t carried in registers), lanes 0-2 publish dgh = dL/d(W_hh h + b_hh) for the three
+        // gates; ONE barrier; then dh_{t-1}[k] = dh_t[k] z[k] + sum_g W_hh[g][k] dgh[g] with gates [48p, 48p + 48)
+        // per lane (FFMA2, two shuffles) and dW_hh[g][k] += dgh[g] h_{t-1}[k] in registers.  dgi overwrites the
+        // consumed tape rows so that dW_ih[d][g] += dgi_t[g] x_t[d] is done once per chunk by all threads.
+        {
+            float *GWIH = TILE + 2 * kChunkFloats; // [d][gate]
+            for (int i = tid; i < kGruGates * Dp; i += kGruThreads)
+                GWIH[i] = 0.f;
+            float2 wcol[24], gw[24];
+#pragma unroll
+            for (int i = 0; i < 24; ++i)
+            {
+                wcol[i].x = __ldcg(a.params + po.whh + (pp * 48 + 2 * i) * kHid + kk);
+                wcol[i].y = __ldcg(a.params + po.whh + (pp * 48 + 2 * i + 1) * kHid + kk);
+                gw[i] = make_float2(0.f, 0.f);
             }
             float gbi[3] = {0.f, 0.f, 0.f}, gbh[3] = {0.f, 0.f, 0.f};
-            // software pipeline: the tape values of step t - 1 are in flight while step t computes
-            float c_r = 0.f, c_z = 0.f, c_n = 0.f, c_g = 0.f, c_dx = 0.f, c_hp = 0.f;
-            auto load_step = [&](int t, float &r, float &z, float &n, float &g, float &dx, float &hp)
+            const int n_chunks = (T + kChunk - 1) / kChunk;
+            auto stage_chunk = [&](int c)
             {
-                const int o = t * kHid + tid;
-                r = __ldcg(TR + o), z = __ldcg(TZ + o), n = __ldcg(TN + o), g = __ldcg(TG + o), dx = __ldcg(TDX + o);
-                hp = (t == 0 || CUT[t]) ? hx0 * MSEQ[t] : __ldcg(TH + o - kHid);
-            };
-            if (tid < kHid)
-            {
-                load_step(T - 1, c_r, c_z, c_n, c_g, c_dx, c_hp);
-                DHN[tid] = 0.f; // carry into step T-1
-            }
-            __syncthreads();
-            for (int t = T - 1; t >= 0; --t)
-            {
-                float n_r = 0.f, n_z = 0.f, n_n = 0.f, n_g = 0.f, n_dx = 0.f, n_hp = 0.f;
-                if (tid < kHid)
+                const int hi = T - c * kChunk, lo = max(0, hi - kChunk);
+                float *buf = TILE + (c & 1) * kChunkFloats;
+                // buffer: {r,z,n,g} [s][64][4] | dL/dh [s][64] | h_{t-1} [s][64] (unused at t = 0)
+                for (int i = tid; i < 6 * kChunk * 16; i += kGruThreads)
                 {
-                    if (t > 0)
-                        load_step(t - 1, n_r, n_z, n_n, n_g, n_dx, n_hp);
-                    const float dh = c_dx + DHN[tid];
+                    const float *src;
+                    float *dst;
+                    int t;
+                    if (i < 4 * kChunk * 16)
+                    {
+                        const int sidx = i >> 6, c4 = i & 63;
+                        t = lo + sidx;
+                        src = TRZNG + (static_cast<size_t>(t) * kHid + c4) * 4, dst = buf + sidx * 4 * kHid + 4 * c4;
+                    }
+                    else
+                    {
+                        const int j = i - 4 * kChunk * 16, which = j >> 7, sidx = (j >> 4) & (kChunk - 1), c4 = j & 15;
+                        t = lo + sidx;
+                        src = (which ? TH + static_cast<size_t>(t > 0 ? t - 1 : 0) * kHid : TDX + static_cast<size_t>(t) * kHid) + 4 * c4;
+                        dst = buf + (4 + which) * kChunk * kHid + sidx * kHid + 4 * c4;
+                    }
+                    if (t < hi)
+                        cp_async16(dst, src);
+                }
+                cp_async_commit();
+            };
+            stage_chunk(0);
+            float carry = 0.f; // dL/dh_t arriving from step t+1 (identical in the four lanes of a quad)
+            for (int c = 0; c < n_chunks; ++c)
+            {
+                if (c + 1 < n_chunks)
+                    stage_chunk(c + 1);
+                else
+                    cp_async_commit();
+                cp_async_wait<1>();
+                __syncthreads();
+                const int hi = T - c * kChunk, lo = max(0, hi - kChunk);
+                float *buf = TILE + (c & 1) * kChunkFloats;
+                for (int t = hi - 1; t >= lo; --t)
+                {
+                    const bool first = t == 0 || CUT[t]; // step t starts a run: its state came from hxs, not from t-1
+                    float4 *rzng = reinterpret_cast<float4 *>(buf + ((t - lo) * kHid + kk) * 4);
+                    const float *row = buf + 4 * kChunk * kHid + (t - lo) * kHid + kk;
+                    float *dgh = DGH + (t & 1) * kDghStride;
+                    const float4 q4 = *rzng;
+                    const float c_r = q4.x, c_z = q4.y, c_n = q4.z, c_g = q4.w, c_dx = row[0];
+                    const float hp = first ? hx0 * MSEQ[t] : row[kChunk * kHid];
+                    const float dh = c_dx + carry;
                     const float dn = dh * (1.f - c_z);
-                    const float dz = dh * (c_hp - c_n);
+                    const float dz = dh * (hp - c_n);
                     const float dpn = dn * (1.f - c_n * c_n);
                     const float dpr = dpn * c_g * c_r * (1.f - c_r);
                     const float dpz = dz * c_z * (1.f - c_z);
-                    DGI[tid] = dpr, DGI[kHid + tid] = dpz, DGI[2 * kHid + tid] = dpn;
-                    DGH[tid] = dpr, DGH[kHid + tid] = dpz, DGH[2 * kHid + tid] = dpn * c_r;
-                    DHZ[tid] = dh * c_z;
-                    HPREV[tid] = c_hp;
                     gbi[0] += dpr, gbi[1] += dpz, gbi[2] += dpn;
                     gbh[0] += dpr, gbh[1] += dpz, gbh[2] += dpn * c_r;
-                }
-                __syncthreads();
-                {
-                    const float hp = HPREV[kk];
-                    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+                    if (pp == 0)
+                        dgh[dgh_pos(kk)] = dpr;
+                    else if (pp == 1)
+                        dgh[dgh_pos(kHid + kk)] = dpz;
+                    else if (pp == 2)
+                        dgh[dgh_pos(2 * kHid + kk)] = dpn * c_r;
+                    else
+                        *rzng = make_float4(dpr, dpz, dpn, 0.f); // dgi of the three gates, for dW_ih below
+                    __syncthreads();
+                    float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+                    const float2 hp2 = make_float2(hp, hp);
 #pragma unroll
-                    for (int i = 0; i < 48; i += 4)
+                    for (int i = 0; i < 24; i += 2)
                     {
-                        const float4 d = *reinterpret_cast<const float4 *>(DGH + pp * 48 + i);
-                        s0 = fmaf(wcol[i], d.x, s0);
-                        s1 = fmaf(wcol[i + 1], d.y, s1);
-                        s2 = fmaf(wcol[i + 2], d.z, s2);
-                        s3 = fmaf(wcol[i + 3], d.w, s3);
-                        gw[i] = fmaf(d.x, hp, gw[i]);
-                        gw[i + 1] = fmaf(d.y, hp, gw[i + 1]);
-                        gw[i + 2] = fmaf(d.z, hp, gw[i + 2]);
-                        gw[i + 3] = fmaf(d.w, hp, gw[i + 3]);
+                        const float4 d = *reinterpret_cast<const float4 *>(dgh + pp * 52 + 2 * i);
+                        const float2 lo2 = make_float2(d.x, d.y), hi2 = make_float2(d.z, d.w);
+                        s0 = __ffma2_rn(wcol[i], lo2, s0);
+                        s1 = __ffma2_rn(wcol[i + 1], hi2, s1);
+                        gw[i] = __ffma2_rn(lo2, hp2, gw[i]);
+                        gw[i + 1] = __ffma2_rn(hi2, hp2, gw[i + 1]);
                     }
-                    float s = (s0 + s1) + (s2 + s3);
-                    s += __shfl_xor_sync(0xffffffffu, s, 1);
-                    s += __shfl_xor_sync(0xffffffffu, s, 2);
-                    // a run that starts at step t takes its state from hxs, not from step t-1: no gradient crosses
-                    const float carry = (t == 0 || CUT[t]) ? 0.f : DHZ[kk] + s;
+                    float sacc = (s0.x + s0.y) + (s1.x + s1.y);
+                    sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+                    sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+                    carry = first ? 0.f : fmaf(dh, c_z, sacc);
+                }
+                __syncthreads(); // the chunk's dgi rows are complete
+                {
+                    const int ns = hi - lo;
                     for (int i = tid; i < kGruGates * Dp; i += kGruThreads)
                     {
-                        const int g = i / Dp, d = i - g * Dp;
-                        GWIH[i] = fmaf(DGI[g], XSEQ[t * Dp + d], GWIH[i]);
+                        const int d = i / kGruGates, g = i - d * kGruGates;
+                        const float *dgi = buf + (g & 63) * 4 + (g >> 6);
+                        float acc = GWIH[i];
+                        for (int sidx = 0; sidx < ns; ++sidx)
+                            acc = fmaf(dgi[sidx * 4 * kHid], XSEQ[(lo + sidx) * Dp + d], acc);
+                        GWIH[i] = acc;
                     }
-                    if (pp == 0)
-                        DHN[kk] = carry; // read by phase A of step t-1, after the barrier below
                 }
-                c_r = n_r, c_z = n_z, c_n = n_n, c_g = n_g, c_dx = n_dx, c_hp = n_hp;
-                __syncthreads();
+                __syncthreads(); // before the buffer is staged again
             }
-            // Adam on the GRU parameters
+            GRU_MARK(5);
+            // Adam on the GRU parameters (W_hh from the registers, the rest resident in shared memory)
 #pragma unroll
-            for (int i = 0; i < 48; ++i)
-                adam(po.whh + (pp * 48 + i) * kHid + kk, gw[i]);
-            if (tid < kHid)
+            for (int i0 = 0; i0 < 24; i0 += 4)
             {
+                if (!ppo)
+                {
+#pragma unroll
+                    for (int i = i0; i < i0 + 4; ++i)
+                    {
+                        atomicAdd(a.grad_out + po.whh + (pp * 48 + 2 * i) * kHid + kk, gw[i].x);
+                        atomicAdd(a.grad_out + po.whh + (pp * 48 + 2 * i + 1) * kHid + kk, gw[i].y);
+                    }
+                    continue;
+                }
+                float m[8], v[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                {
+                    const int gi = po.whh + (pp * 48 + 2 * i0 + i) * kHid + kk;
+                    m[i] = __ldcg(a.opt_m + gi), v[i] = __ldcg(a.opt_v + gi);
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                {
+                    const float2 w = wcol[i0 + (i >> 1)], g = gw[i0 + (i >> 1)];
+                    adam_core(po.whh + (pp * 48 + 2 * i0 + i) * kHid + kk, (i & 1) ? g.y : g.x, (i & 1) ? w.y : w.x, m[i], v[i]);
+                }
+            }
+            if (pp == 0)
+            {
+                float m[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, v[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                if (ppo)
+                {
+#pragma unroll
+                    for (int g = 0; g < 3; ++g)
+                    {
+                        m[g] = __ldcg(a.opt_m + po.bih + g * kHid + kk), v[g] = __ldcg(a.opt_v + po.bih + g * kHid + kk);
+                        m[3 + g] = __ldcg(a.opt_m + po.bhh + g * kHid + kk), v[3 + g] = __ldcg(a.opt_v + po.bhh + g * kHid + kk);
+                    }
+                }
 #pragma unroll
                 for (int g = 0; g < 3; ++g)
                 {
-                    adam(po.bih + g * kHid + tid, gbi[g]);
-                    adam(po.bhh + g * kHid + tid, gbh[g]);
+                    const int o = g * kHid + kk;
+                    if (ppo)
+                    {
+                        BIH[o] = adam_core(po.bih + o, gbi[g], BIH[o], m[g], v[g]);
+                        BHH[o] = adam_core(po.bhh + o, gbh[g], BHH[o], m[3 + g], v[3 + g]);
+                    }
+                    else
+                    {
+                        atomicAdd(a.grad_out + po.bih + o, gbi[g]);
+                        atomicAdd(a.grad_out + po.bhh + o, gbh[g]);
+                    }
                 }
             }
             for (int i = tid; i < kGruGates * D; i += kGruThreads)
             {
                 const int g = i / D, d = i - g * D;
-                adam(po.wih + i, GWIH[g * Dp + d]);
+                const int gi = po.wih + i, si = d * kGruGates + g;
+                if (ppo)
+                    WIHT[si] = adam_core(gi, GWIH[si], WIHT[si], __ldcg(a.opt_m + gi), __ldcg(a.opt_v + gi));
+                else
+                    atomicAdd(a.grad_out + gi, GWIH[si]);
             }
         }
         ++applied;
-        __syncthreads(); // parameter stores of this minibatch are visible to the whole CTA before the next image build
+        GRU_MARK(6);
+        __syncthreads(); // parameter stores of this minibatch are visible to the whole CTA before the next one starts
     } // minibatches
 }
 } // namespace
 
-size_t gru_update_smem_bytes(int Dp, int A, int Ap, int T) { return static_cast<size_t>(make_gru_smem(Dp, A, Ap, T).total) * sizeof(float); }
+size_t gru_update_smem_bytes(int Dp, int A, int Ap, int head, int T)
+{
+    return static_cast<size_t>(make_gru_smem(Dp, A, Ap, head, T).total) * sizeof(float);
+}
 
 int launch_gru_update(const GruUpdateArgs &args, int grid, cudaStream_t s)
 {
@@ -834,7 +998,7 @@ int launch_gru_update(const GruUpdateArgs &args, int grid, cudaStream_t s)
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(gru_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         configured = true;
     }
-    const size_t smem = gru_update_smem_bytes(args.Dp, args.A, args.Ap, args.T);
+    const size_t smem = gru_update_smem_bytes(args.Dp, args.A, args.Ap, args.head, args.T);
     gru_update_kernel<<<grid, kGruThreads, smem, s>>>(args);
     CPPRL_CUDA_TRY(cudaGetLastError());
     count_launch();

@@ -48,9 +48,11 @@ struct GruUpdateArgs
     float *tape;             // [grid][kGruTapes][T][H]
     UpdateState *state;
     float *out_value, *out_logp, *out_entropy_sum, *out_hxs;
+    long long *dbg_clocks;   // nullable: clock64() phase markers of minibatch dbg_step (profiling hook)
+    int dbg_step;
     int step_mode;           // forward: write the new hidden state to out_hxs (x rows == hxs rows)
 };
-size_t gru_update_smem_bytes(int Dp, int A, int Ap, int T);
+size_t gru_update_smem_bytes(int Dp, int A, int Ap, int head, int T);
 // grid: PPO 1 (the epoch's minibatches are a serial chain), A2C / forward one CTA per environment
 int launch_gru_update(const GruUpdateArgs &args, int grid, cudaStream_t s);
 } // namespace cpprl_b200
