@@ -65,6 +65,23 @@ def mlp_param_shapes(num_inputs: int, num_actions: int, head: str, hidden: int =
     return shapes
 
 
+def cnn_param_shapes(channels: int, num_actions: int, head: str, hidden: int = 512):
+    """CnnBase (cnn_base.cpp:9-31): three convolutions, the 1568 -> hidden linear layer, critic_linear, the head."""
+    shapes = [("base.main.0.weight", (32, channels, 8, 8)), ("base.main.0.bias", (32,)),
+              ("base.main.2.weight", (64, 32, 4, 4)), ("base.main.2.bias", (64,)),
+              ("base.main.4.weight", (32, 64, 3, 3)), ("base.main.4.bias", (32,)),
+              ("base.main.7.weight", (hidden, 32 * 7 * 7)), ("base.main.7.bias", (hidden,)),
+              ("base.critic_linear.weight", (1, hidden)), ("base.critic_linear.bias", (1,))]
+    if head == "Discrete":
+        shapes += [("output.linear.weight", (num_actions, hidden)), ("output.linear.bias", (num_actions,))]
+    elif head == "Box":
+        shapes += [("output.scale_log", (num_actions,)), ("output.linear_loc.weight", (num_actions, hidden)),
+                   ("output.linear_loc.bias", (num_actions,))]
+    else:
+        raise RuntimeError(f"Action space {head} not supported")
+    return shapes
+
+
 class RunningMeanStd:
     """Device buffers count[1], mean[D], variance[D] (running_mean_std.cpp:8-11) updated by the rms kernel."""
 
@@ -106,11 +123,12 @@ class ObservationNormalizer:
 
 
 class Policy:
-    """Flat-parameter policy (MlpBase + Categorical / Normal head).  `params` is ONE fp32 device buffer in
-    the reference's registration order; `named_parameters()` returns views into it."""
+    """Flat-parameter policy (MlpBase, GRU-fronted MlpBase or CnnBase + Categorical / Normal head).  `params` is
+    ONE fp32 device buffer in the reference's registration order; `named_parameters()` returns views into it.
+    `obs_shape` = (C, 84, 84) selects CnnBase (policy.cpp / gym_client.cpp:117-131 pick the base by observation rank)."""
 
     def __init__(self, action_space: ActionSpace, num_inputs: int, normalize_observations: bool = False,
-                 hidden: int = 64, recurrent: bool = False, device="cuda"):
+                 hidden: int = 64, recurrent: bool = False, device="cuda", obs_shape: Optional[Sequence[int]] = None):
         if action_space.type not in ("Discrete", "Box"):
             raise RuntimeError("Action space " + action_space.type + " not supported")
         self.action_space = action_space
@@ -118,7 +136,13 @@ class Policy:
         self.hidden = hidden
         self.recurrent = recurrent
         self.num_actions = int(action_space.shape[0])
-        self.shapes = mlp_param_shapes(num_inputs, self.num_actions, action_space.type, hidden, recurrent)
+        self.obs_chw = tuple(int(x) for x in obs_shape) if obs_shape is not None and len(obs_shape) == 3 else None
+        if self.obs_chw is not None:
+            if recurrent:
+                raise RuntimeError("cpprl_b200: recurrent CnnBase is not implemented")
+            self.shapes = cnn_param_shapes(self.obs_chw[0], self.num_actions, action_space.type, hidden)
+        else:
+            self.shapes = mlp_param_shapes(num_inputs, self.num_actions, action_space.type, hidden, recurrent)
         n = sum(int(torch.Size(s).numel()) for _, s in self.shapes)
         self.params = torch.zeros(n, dtype=torch.float32, device=device)
         self.observation_normalizer = ObservationNormalizer(num_inputs, device=device) if normalize_observations else None
@@ -144,6 +168,10 @@ class Policy:
     def desc(self) -> cabi.Policy:
         p = cabi.Policy()
         p.base_kind = cabi.BASE_GRU_MLP if self.recurrent else cabi.BASE_MLP
+        if self.obs_chw is not None:
+            p.base_kind = cabi.BASE_CNN
+            for i in range(3):
+                p.obs_chw[i] = self.obs_chw[i]
         p.head_kind = cabi.HEAD_CATEGORICAL if self.action_space.type == "Discrete" else cabi.HEAD_NORMAL
         p.obs_dim = self.num_inputs
         p.hidden = self.hidden

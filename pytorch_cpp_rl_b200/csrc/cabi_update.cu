@@ -2,11 +2,13 @@
 // (host-side orchestration: validation, scratch, permutation staging, launches, statistics read-back).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
 
 #include "common.cuh"
+#include "cnn_update.cuh"
 #include "gru_update.cuh"
 #include "mlp_update.cuh"
 
@@ -117,7 +119,27 @@ int validate_policy(const cpprl_b200_policy *p, const char *who)
     if (!p || !p->d_params)
         return fail(CPPRL_B200_EINVAL, std::string(who) + ": null policy / parameter buffer");
     if (p->base_kind == CPPRL_B200_BASE_CNN)
-        return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": CnnBase is not implemented on the GPU path yet");
+    {
+        // CnnBase (cnn_base.cpp:9-31): the reference hard-codes the 32*7*7 flatten, i.e. 84x84 frames
+        if (p->head_kind != CPPRL_B200_HEAD_CATEGORICAL && p->head_kind != CPPRL_B200_HEAD_NORMAL)
+            return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": only Categorical and Normal heads are implemented (Bernoulli is out of scope)");
+        if (p->obs_chw[1] != kCnnIn || p->obs_chw[2] != kCnnIn || p->obs_chw[0] < 1 || p->obs_chw[0] > 16)
+            return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": CnnBase takes [C <= 16, 84, 84] observations");
+        if (p->obs_dim != p->obs_chw[0] * kCnnIn * kCnnIn)
+            return fail(CPPRL_B200_EINVAL, std::string(who) + ": obs_dim does not match obs_chw");
+        if (p->hidden != kCnnHid)
+            return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": CnnBase hidden size must be 512 on the GPU path");
+        if (p->num_actions < 1 || p->num_actions > kMaxActions)
+            return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": num_actions must be in [1, 16]");
+        if (p->d_norm_clip || p->d_norm_count || p->d_norm_mean || p->d_norm_var)
+            return fail(CPPRL_B200_EUNSUPPORTED, std::string(who) + ": observation normalisation of image observations is not implemented on the GPU path");
+        const CnnParamOffsets cpo = cnn_param_offsets(static_cast<int>(p->obs_chw[0]), static_cast<int>(p->num_actions),
+                                                      p->head_kind == CPPRL_B200_HEAD_NORMAL ? 1 : 0);
+        if (p->n_params != cpo.P)
+            return fail(CPPRL_B200_EINVAL, std::string(who) + ": n_params does not match the policy layout (expected " +
+                                               std::to_string(cpo.P) + ", got " + std::to_string(p->n_params) + ")");
+        return 0;
+    }
     const bool gru = p->base_kind == CPPRL_B200_BASE_GRU_MLP;
     if (p->base_kind != CPPRL_B200_BASE_MLP && !gru)
         return fail(CPPRL_B200_EINVAL, std::string(who) + ": unknown base kind");
@@ -291,6 +313,27 @@ int fill_gru_policy_args(GruUpdateArgs &a, const cpprl_b200_policy &p, int64_t T
     return 0;
 }
 
+void fill_cnn_policy_args(CnnUpdateArgs &a, const cpprl_b200_policy &p)
+{
+    std::memset(&a, 0, sizeof(a));
+    a.C = static_cast<int>(p.obs_chw[0]);
+    a.A = static_cast<int>(p.num_actions);
+    a.head = p.head_kind == CPPRL_B200_HEAD_NORMAL ? 1 : 0;
+    a.po = cnn_param_offsets(a.C, a.A, a.head);
+    a.il = cnn_image_layout(a.C);
+    a.params = p.d_params;
+}
+
+// rows per pass of the CNN path: activations + their gradients take 160 KB per row
+// (CPPRL_B200_CNN_CHUNK overrides the pass size: the tests use it to exercise multi-pass accumulation on small rollouts)
+inline int cnn_chunk_rows(int64_t B)
+{
+    int64_t chunk = 4096;
+    if (const char *e = std::getenv("CPPRL_B200_CNN_CHUNK"))
+        chunk = std::max<int64_t>(1, std::atoll(e));
+    return static_cast<int>(std::min<int64_t>(B, chunk));
+}
+
 __global__ void reset_state_kernel(UpdateState *st)
 {
     const long long keep = st->opt_step;
@@ -334,6 +377,9 @@ struct cpprl_b200_ppo
     MlpUpdateArgs args;
     GruUpdateArgs gargs; // recurrent policies
     bool gru = false;
+    CnnUpdateArgs cargs; // CnnBase
+    CnnWorkspace cws;
+    bool cnn = false;
     Plan plan;
     int64_t mbs = 0, n_mb = 0;
     int epoch = 0;
@@ -540,6 +586,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         return fail(CPPRL_B200_EINVAL, "ppo_update: bad epoch / minibatch count");
     const bool sharded = h->comm != nullptr;
     h->gru = policy->base_kind == CPPRL_B200_BASE_GRU_MLP;
+    h->cnn = policy->base_kind == CPPRL_B200_BASE_CNN;
     if (h->gru)
         return ppo_begin_gru(h, policy, ro, opt, stream);
     const int64_t n_envs = sharded ? h->global_envs : ro->N; // minibatches are defined on the GLOBAL rollout
@@ -567,6 +614,56 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     h->mbs = mbs;
     h->n_mb = rows / mbs;
     h->epoch = 0;
+    if (h->cnn)
+    {
+        if (sharded)
+            return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: the CnnBase path is single-GPU in this round");
+        if (mbs > 0x7fffffffll / kCnnP1 / 4)
+            return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: minibatch too large");
+        CnnUpdateArgs &c = h->cargs;
+        fill_cnn_policy_args(c, *policy);
+        const int chunk = cnn_chunk_rows(mbs);
+        if (int rc = h->scratch.ensure(0, 0, 0))
+            return rc;
+        if (int rc = h->scratch.ensure_tape(cnn_workspace_floats(c.C, c.A, chunk, true)))
+            return rc;
+        cnn_workspace_carve(h->cws, h->scratch.tape, c.C, c.A, chunk, true);
+        c.obs = ro->d_observations;
+        c.actions = ro->d_actions;
+        c.value_preds = ro->d_value_preds;
+        c.returns = ro->d_returns;
+        c.old_logp = ro->d_action_log_probs;
+        c.rows = rows;
+        c.B = static_cast<int>(mbs);
+        c.adv_sums = h->scratch.adv_sums;
+        c.algo = kAlgoPPO;
+        c.clip_param = opt->clip_param;
+        c.clip_lo = static_cast<float>(1.0 - static_cast<double>(opt->clip_param));
+        c.clip_hi = static_cast<float>(1.0 + static_cast<double>(opt->clip_param));
+        c.c_actor = opt->actor_loss_coef;
+        c.c_value = opt->value_loss_coef;
+        c.c_entropy = opt->entropy_coef;
+        c.kl_limit = static_cast<double>(opt->kl_target) * 1.5;
+        c.opt = kOptAdam;
+        c.opt_m = h->d_m;
+        c.opt_v = h->d_v;
+        c.lr = static_cast<double>(opt->learning_rate);
+        c.beta1 = 0.9f;
+        c.beta2 = 0.999f;
+        c.eps = opt->epsilon;
+        c.state = h->scratch.state;
+        cudaStream_t cs = h->stream;
+        KernelTimer timer("prologue", cs);
+        reset_state_kernel<<<1, 1, 0, cs>>>(h->scratch.state);
+        CPPRL_LAUNCH_CHECK("reset_state_kernel");
+        CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 2 * sizeof(double), cs));
+        if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, rows, h->scratch.adv_sums, cs))
+            return rc;
+        if (int rc = cnn_build_images(c, h->cws, cs))
+            return rc;
+        h->active = true;
+        return 0;
+    }
 
     ParamOffsets po;
     mlp_param_offsets(*policy, po);
@@ -660,6 +757,21 @@ extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
 
 static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
+    if (h->cnn)
+    {
+        // one pass over the epoch's minibatches, every kernel enqueued on the stream; the KL decision stays on the
+        // device (kernels of later minibatches see state->stopped and return)
+        KernelTimer timer("update", h->stream);
+        h->cargs.perm = reinterpret_cast<const long long *>(d_perm);
+        for (int64_t mb = 0; mb < h->n_mb; ++mb)
+        {
+            h->cargs.row_base = mb * h->mbs;
+            if (int rc = cnn_minibatch(h->cargs, h->cws, h->stream))
+                return rc;
+        }
+        ++h->epoch;
+        return 0;
+    }
     if (h->gru)
     {
         h->gargs.perm = reinterpret_cast<const long long *>(d_perm);
@@ -991,6 +1103,45 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     h->stream = s;
     if (policy->base_kind == CPPRL_B200_BASE_GRU_MLP)
         return a2c_update_gru(h, policy, ro, opt, s);
+    if (policy->base_kind == CPPRL_B200_BASE_CNN)
+    {
+        if (h->comm)
+            return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: the CnnBase path is single-GPU in this round");
+        CnnUpdateArgs c;
+        fill_cnn_policy_args(c, *policy);
+        const int chunk = cnn_chunk_rows(rows);
+        if (int rc = h->scratch.ensure(0, 0, 0))
+            return rc;
+        if (int rc = h->scratch.ensure_tape(cnn_workspace_floats(c.C, c.A, chunk, true)))
+            return rc;
+        CnnWorkspace ws;
+        cnn_workspace_carve(ws, h->scratch.tape, c.C, c.A, chunk, true);
+        c.obs = ro->d_observations;
+        c.actions = ro->d_actions;
+        c.value_preds = ro->d_value_preds;
+        c.returns = ro->d_returns;
+        c.rows = rows;
+        c.B = static_cast<int>(rows);
+        c.algo = kAlgoA2C;
+        c.c_actor = 1.f;
+        c.c_value = opt->value_loss_coef;
+        c.c_entropy = opt->entropy_coef;
+        c.opt = kOptRmsprop;
+        c.opt_v = h->d_sq;
+        c.lr = static_cast<double>(opt->learning_rate);
+        c.alpha = opt->alpha;
+        c.eps = opt->epsilon;
+        c.state = h->scratch.state;
+        KernelTimer timer("update", s);
+        reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+        CPPRL_LAUNCH_CHECK("reset_state_kernel");
+        if (int rc = cnn_build_images(c, ws, s))
+            return rc;
+        if (int rc = cnn_minibatch(c, ws, s))
+            return rc;
+        CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, s));
+        return 0;
+    }
 
     ParamOffsets po;
     mlp_param_offsets(*policy, po);
@@ -1104,6 +1255,9 @@ extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
         return 0;
     ParamOffsets po;
     GruParamOffsets gpo;
+    if (policy->base_kind == CPPRL_B200_BASE_CNN)
+        return cnn_param_offsets(static_cast<int>(policy->obs_chw[0]), static_cast<int>(policy->num_actions),
+                                 policy->head_kind == CPPRL_B200_HEAD_NORMAL ? 1 : 0).P;
     if (gru_param_offsets(*policy, gpo))
         return gpo.P;
     if (!mlp_param_offsets(*policy, po))
@@ -1127,6 +1281,32 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     std::lock_guard<std::mutex> lock(g_eval_mu);
 
+    if (policy->base_kind == CPPRL_B200_BASE_CNN)
+    {
+        CnnUpdateArgs c;
+        fill_cnn_policy_args(c, *policy);
+        const int chunk = cnn_chunk_rows(B);
+        if (int rc = g_eval_scratch.ensure_tape(cnn_workspace_floats(c.C, c.A, chunk, false)))
+            return rc;
+        CnnWorkspace ws;
+        cnn_workspace_carve(ws, g_eval_scratch.tape, c.C, c.A, chunk, false);
+        c.obs = d_obs;
+        c.actions = d_actions;
+        c.rows = B;
+        c.B = static_cast<int>(B);
+        c.algo = kAlgoForward;
+        c.out_value = d_value;
+        c.out_logp = d_logp;
+        c.out_entropy_sum = d_entropy;
+        CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
+        if (int rc = cnn_build_images(c, ws, s))
+            return rc;
+        if (int rc = cnn_forward(c, ws, s))
+            return rc;
+        finish_entropy_kernel<<<1, 1, 0, s>>>(d_entropy, 1.f / static_cast<float>(B));
+        CPPRL_LAUNCH_CHECK("finish_entropy_kernel");
+        return 0;
+    }
     if (policy->base_kind == CPPRL_B200_BASE_GRU_MLP)
     {
         // NNBase::forward_gru (nn_base.cpp:47-114): n_hxs == B is the one-step mode, otherwise x is [T, n_hxs] flattened

@@ -40,7 +40,7 @@ def ref_load_rollout(sess, r):
 def make_gpu_side(w: Workload, r, params: np.ndarray, normalizer=None):
     space = api.ActionSpace("Discrete" if w.head == "categorical" else "Box", [w.num_actions])
     policy = api.Policy(space, w.obs_dim, normalize_observations=w.normalize_obs, hidden=w.hidden,
-                        recurrent=(w.base == "gru"))
+                        recurrent=(w.base == "gru"), obs_shape=w.obs_shape if w.base == "cnn" else None)
     policy.params.copy_(torch.from_numpy(params))
     if normalizer is not None and policy.observation_normalizer is not None:
         _, count, mean, var = normalizer
