@@ -138,18 +138,22 @@ def init_params(w: Workload, seed: int) -> np.ndarray:
     """Random-init flat parameters of the workload's architecture, in the reference's registration order, with
     the reference's init scheme (orthogonal weights with the gains of mlp_base.cpp:40-42 /
     output_layers.cpp:37,51, zero biases, scale_log = 0).  Used by bench.py (no checkpoints offline)."""
-    from .api import mlp_param_shapes
+    from .api import cnn_param_shapes, mlp_param_shapes
     rng = np.random.default_rng(seed)
     head = "Discrete" if w.head == "categorical" else "Box"
     out = []
-    for name, shape in mlp_param_shapes(w.obs_dim, w.num_actions, head, w.hidden, w.base == "gru"):
-        if len(shape) == 2:
+    if w.base == "cnn":
+        shapes = cnn_param_shapes(w.obs_shape[0], w.num_actions, head, w.hidden)
+    else:
+        shapes = mlp_param_shapes(w.obs_dim, w.num_actions, head, w.hidden, w.base == "gru")
+    for name, shape in shapes:
+        if len(shape) >= 2:
             gain = np.sqrt(2.0)
-            if name.startswith("output.linear_loc") or "gru" in name:
+            if name.startswith("output.linear_loc") or "gru" in name or ("critic_linear" in name and w.base == "cnn"):
                 gain = 1.0
             elif name.startswith("output.linear"):
                 gain = 0.01
-            out.append(_orthogonal(rng, shape[0], shape[1], gain).ravel())
+            out.append(_orthogonal(rng, shape[0], int(np.prod(shape[1:])), gain).ravel())
         else:
             out.append(np.zeros(shape, np.float32).ravel())
     return np.concatenate(out)
