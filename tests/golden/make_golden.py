@@ -19,7 +19,7 @@ ROOT = Path(__file__).resolve().parents[2]
 sys.path.insert(0, str(ROOT))
 
 from oracle import ref_binding as ref  # noqa: E402
-from pytorch_cpp_rl_b200.workloads import CONFIGS, synth_rollout  # noqa: E402
+from pytorch_cpp_rl_b200.workloads import CONFIGS, init_params, synth_rollout  # noqa: E402
 from tests import helpers as H  # noqa: E402
 
 HERE = Path(__file__).resolve().parent
@@ -34,6 +34,9 @@ CASES = {
     "ppo_gru_categorical_small": (CONFIGS["cfg4"].scaled(T=16, N=8, num_mini_batch=8, num_epoch=2), 3, 2),
     "a2c_gru_categorical_small": (CONFIGS["cfg4"].scaled(T=12, N=6, algo="a2c", num_epoch=1, num_mini_batch=1,
                                                          use_gae=False, learning_rate=7e-4), 4, 2),
+    # CnnBase: 866 439 parameters.  To keep the fixture small the initial parameters are regenerated from the seed
+    # (workloads.init_params) and the post-update parameters are stored at every 16th index + the whole tail
+    "ppo_cnn_categorical_small": (CONFIGS["cfg5"].scaled(T=4, N=4, num_epoch=2, num_mini_batch=2), 6, 1),
 }
 
 HYPER = ["T", "N", "num_actions", "hidden", "storage_hidden", "num_epoch", "num_mini_batch", "gamma", "tau", "clip_param",
@@ -43,11 +46,20 @@ HYPER = ["T", "N", "num_actions", "hidden", "storage_hidden", "num_epoch", "num_
 def make(name, w, seed, n_updates):
     r = synth_rollout(w, seed)
     sess = H.make_ref_session(ref, w, init_seed=seed)
+    cnn = w.base == "cnn"
+    if cnn:
+        sess.set_params(init_params(w, seed))
     H.fill_policy_outputs(sess, w, r)
     H.ref_load_rollout(sess, r)
     out = {k: r[k] for k in ("observations", "hidden_states", "rewards", "value_predictions", "action_log_probs",
                              "actions", "masks", "next_value")}
-    out["params_init"] = sess.get_params()
+    if cnn:
+        out["params_seed"] = np.array(seed)
+        n = sess.n_params
+        out["param_idx"] = np.unique(np.concatenate([np.arange(0, n, 16), np.arange(n - 4096, n)]))
+        out["observations"] = r["observations"].astype(np.uint8)  # pixels are integers 0..255
+    else:
+        out["params_init"] = sess.get_params()
     out["meta"] = np.array([w.algo, w.base, w.head, str(int(w.normalize_obs)), str(int(w.use_gae)), str(tuple(w.obs_shape))])
     out["hyper"] = np.array([float(getattr(w, k)) for k in HYPER], np.float64)
     n_perm = w.N if w.base == "gru" else w.rows
@@ -57,7 +69,7 @@ def make(name, w, seed, n_updates):
         perm_seed = 1000 + seed + u
         stats, _ = sess.update(1.0, perm_seed=perm_seed)
         out[f"stats{u}"] = stats
-        out[f"params{u}"] = sess.get_params()
+        out[f"params{u}"] = sess.get_params()[out["param_idx"]] if cnn else sess.get_params()
         if w.algo == "ppo":
             out[f"perms{u}"] = H.draw_perms(perm_seed, n_perm, w.num_epoch).numpy()
         if w.normalize_obs:
@@ -95,6 +107,9 @@ def make_kats():
 
 if __name__ == "__main__":
     assert ref.available(), "build oracle/_ref first (bash oracle/build_ref.sh)"
+    only = sys.argv[1:]
     for name, (w, seed, n) in CASES.items():
-        make(name, w, seed, n)
-    make_kats()
+        if not only or name in only:
+            make(name, w, seed, n)
+    if not only:
+        make_kats()

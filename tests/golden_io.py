@@ -24,8 +24,23 @@ def load(name: str):
     return w, d
 
 
+def initial_params(w, d):
+    """Initial flat parameters of a fixture: stored, or (CnnBase: 866k values) regenerated from the recorded seed."""
+    if "params_init" in d:
+        return d["params_init"]
+    from pytorch_cpp_rl_b200.workloads import init_params
+    return init_params(w, int(d["params_seed"]))
+
+
+def expected_params(d, u: int, flat):
+    """(got, want) for update u: the CnnBase fixture stores the post-update parameters at `param_idx` only."""
+    want = d[f"params{u}"]
+    return (flat[d["param_idx"]], want) if "param_idx" in d else (flat, want)
+
+
 def rollout_arrays(d):
     r = {k: d[k].copy() for k in ("observations", "hidden_states", "rewards", "value_predictions", "action_log_probs",
                                   "actions", "masks", "next_value")}
+    r["observations"] = r["observations"].astype(np.float32)
     r["returns"] = np.zeros_like(r["value_predictions"])
     return r

@@ -125,8 +125,9 @@ def test_kats_fixture():
 def run_oracle_case(w, d, dtype=np.float32):
     """Replays a fixture through the numpy restatement; yields (update index, stats, policy, rollout)."""
     r = G.rollout_arrays(d)
-    pol = O.Policy(w.obs_dim, w.num_actions, w.head, w.hidden, w.base == "gru", w.normalize_obs, dtype)
-    pol.set_params(d["params_init"])
+    pol = O.Policy(w.obs_dim, w.num_actions, w.head, w.hidden, w.base == "gru", w.normalize_obs, dtype,
+                   cnn_shape=w.obs_shape if w.base == "cnn" else None)
+    pol.set_params(G.initial_params(w, d))
     cast = lambda a: a.astype(dtype) if a.dtype == np.float32 else a
     ro = O.Rollout(**{k: cast(r[k]) for k in ("observations", "hidden_states", "rewards", "value_predictions", "returns",
                                               "action_log_probs", "actions", "masks")})
@@ -150,10 +151,12 @@ def test_golden_fixture(name):
         want = d[f"stats{u}"]
         assert len(stats) == len(want)
         np.testing.assert_allclose(stats, want, rtol=1e-4, atol=5e-6, equal_nan=True)
-        wp = d[f"params{u}"]
-        err = np.abs(pol.flat - wp) / np.maximum(np.abs(wp), w.learning_rate)
+        got_p, wp = G.expected_params(d, u, pol.flat)
+        err = np.abs(got_p - wp) / np.maximum(np.abs(wp), w.learning_rate)
         # two fp32 implementations of a sign-like optimiser step: 1e-4 on all but a handful of near-zero gradients
-        assert np.quantile(err, 0.99) <= 1e-4 and err.max() <= 5e-3, (u, err.max(), np.quantile(err, 0.99))
+        # (CnnBase: a fifth of the 866k weights sit behind nearly dead ReLU units, |gradient| ~ Adam's eps)
+        tail = 0.5 if w.base == "cnn" else 5e-3
+        assert np.quantile(err, 0.99) <= 1e-4 and err.max() <= tail, (u, err.max(), np.quantile(err, 0.99))
         if w.normalize_obs:
             got = np.concatenate([pol.normalizer.count, pol.normalizer.mean, pol.normalizer.variance])
             np.testing.assert_allclose(got, d[f"norm{u}"], rtol=2e-5, atol=1e-6)
