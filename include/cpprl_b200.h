@@ -294,6 +294,10 @@ int cpprl_b200_kernel_time_ms(const char *family, double *total_ms, int64_t *lau
 void cpprl_b200_kernel_time_reset(void);
 void cpprl_b200_kernel_time_enable(int on);
 
+/* Test hook for the tensor-core (tcgen05, 3xTF32) GEMM behind the CnnBase contractions: C[M][N] = A * B with plain
+ * row-major device operands A [M][K] (variant bit 0: given transposed, [K][M]) and B [K][N]; variant bits 4..: tile
+ * columns (32, 64, 128).  M, N, K multiples of 4. */
+int cpprl_b200_debug_tc_gemm(int variant, const float *d_a, const float *d_b, float *d_c, int M, int N, int K, void *stream);
 /* Profiling hook: when d_buffer (device, grid*32 int64) is non-NULL, thread 0 of every CTA of the fused PPO
  * update kernel stores clock64() at its phase boundaries during minibatch `step` of each launch. */
 void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step);

@@ -747,6 +747,16 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     return 0;
 }
 
+extern "C" int cpprl_b200_debug_tc_gemm(int variant, const float *d_a, const float *d_b, float *d_c, int M, int N, int K,
+                                        void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (!d_a || !d_b || !d_c || M <= 0 || N <= 0 || K <= 0 || N % 4 || K % 4 || M % 4)
+        return fail(CPPRL_B200_EINVAL, "debug_tc_gemm: bad arguments");
+    return cnn_debug_tc_gemm(variant, d_a, d_b, d_c, M, N, K, static_cast<cudaStream_t>(stream));
+}
+
 static long long *g_dbg_clocks = nullptr;
 static int g_dbg_step = 0;
 extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)

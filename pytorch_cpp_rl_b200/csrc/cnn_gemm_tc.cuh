@@ -1,0 +1,306 @@
+// cnn_gemm_tc.cuh — the CnnBase contractions on the 5th-generation tensor cores (tcgen05, accumulators in TMEM).
+//
+//   C[m][n] (+)= sum_k A(m, k) * B(k, n)       same loader / epilogue contract as cnn_gemm.cuh
+//
+// Parity needs fp32-grade products (post-update parameters to 1e-4 after hundreds of Adam steps), so every fp32
+// operand element x is split into hi = tf32(x) (round to nearest) and lo = x - hi, and each k-step issues THREE
+// kind::tf32 MMAs into the same fp32 TMEM accumulator: hi*hi + hi*lo + lo*hi (the dropped lo*lo term is 2^-22 of
+// the product) — "3xTF32".
+//
+// CTA = 256 threads, tile 128 (UMMA M) x BN x 32.  All threads gather the operand tile from global memory (implicit
+// im2col through the same loaders as the fp32 kernel), split it and store it into the canonical NO-SWIZZLE UMMA
+// K-major shared-memory layout with 16-byte stores (operands whose vectors run along m / n are transposed in
+// registers, 4x4 blocks; MN-major no-swizzle descriptors read back zeros for kind::tf32 on this part), then one
+// elected thread issues the MMAs (descriptors advance by k-step) and commits them to an mbarrier; two
+// shared-memory stages, the global loads of tile t+1 are in flight while tile t's MMAs run.  Epilogue: tcgen05.ld
+// (32 lanes x 8 columns per warp instruction) -> registers -> epi(m, n, float4).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cpprl_b200
+{
+namespace tc
+{
+constexpr int kThreads = 256;
+constexpr int kBM = 128;
+constexpr int kBK = 32;
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes)
+{
+    // UMMA shared-memory matrix descriptor, SWIZZLE_NONE: start address, leading / stride byte offsets (all >> 4),
+    // descriptor version 1 (Blackwell) in bits [46, 48)
+    return static_cast<uint64_t>((addr >> 4) & 0x3fffu) | (static_cast<uint64_t>((lbo_bytes >> 4) & 0x3fffu) << 16) |
+           (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3fffu) << 32) | (1ull << 46);
+}
+
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_c, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t"
+        "}\n" ::"r"(tmem_c),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+
+__device__ __forceinline__ void mbar_init(void *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(void *bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    const uint32_t addr = smem_addr(bar);
+    while (!done)
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}\n"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+}
+
+__device__ __forceinline__ void split_tf32(const float4 &x, float4 &hi, float4 &lo)
+{
+    uint32_t h0, h1, h2, h3;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h0) : "f"(x.x));
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h1) : "f"(x.y));
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h2) : "f"(x.z));
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h3) : "f"(x.w));
+    hi = make_float4(__uint_as_float(h0), __uint_as_float(h1), __uint_as_float(h2), __uint_as_float(h3));
+    lo = make_float4(x.x - hi.x, x.y - hi.y, x.z - hi.z, x.w - hi.w);
+}
+
+// Shared-memory operand layout (both operands K-major, SWIZZLE_NONE): [k chunk of 4 floats][8-row group][row % 8][4 floats]
+// with the 8-row groups 144 bytes apart (128 + 16 padding: the descriptor's stride byte offset is free, and the
+// padding makes the transposing 16-byte stores below conflict-free) and the k chunks (rows / 8) * 144 bytes apart.
+constexpr int kGroupBytes = 144;
+__host__ __device__ constexpr int operand_bytes(int rows) { return (kBK / 4) * (rows / 8) * kGroupBytes; }
+__host__ __device__ constexpr size_t smem_bytes(int BN) { return static_cast<size_t>(2) * 2 * (operand_bytes(kBM) + operand_bytes(BN)) + 64; }
+
+// A_T: A(m, k) = X[k][m] (the loader's vectors run along m: transposed on the way into shared memory); else
+// A(m, k) = X[m][k] (vectors along k).  B(k, n) = Y[k][n] always (vectors along n, transposed likewise).
+template <int BN, bool A_T, class ALoad, class BLoad, class Epi>
+__global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const BLoad bl, const Epi epi, int M, int N, int K,
+                                                           int k_slice, int z_is_k_split, const int *stop_flag)
+{
+    static_assert(BN == 32 || BN == 64 || BN == 128, "tile columns");
+    extern __shared__ __align__(128) unsigned char tc_smem[];
+    if (stop_flag && *stop_flag)
+        return;
+    constexpr int A_BYTES = operand_bytes(kBM), B_BYTES = operand_bytes(BN), STAGE_BYTES = 2 * (A_BYTES + B_BYTES);
+    constexpr uint32_t A_LBO = (kBM / 8) * kGroupBytes, B_LBO = (BN / 8) * kGroupBytes;
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(tc_smem + 2 * STAGE_BYTES);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(mbar + 2);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * BN;
+    const int k_begin = z_is_k_split ? blockIdx.z * k_slice : 0, k_end = min(K, k_begin + k_slice);
+
+    // ---- TMEM allocation (one warp), barriers ----------------------------------------------------------------------
+    constexpr uint32_t TMEM_COLS = 2 * BN; // two accumulators: see the chunked accumulation below
+    if (warp == 0)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "r"(TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (tid == 0)
+    {
+        mbar_init(&mbar[0], 1);
+        mbar_init(&mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_acc = *tmem_slot;
+
+    // instruction descriptor: D = F32 (bits 4-5), A = B = TF32 (bits 7-9, 10-12), both K-major, N >> 3, M >> 4
+    constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                               (static_cast<uint32_t>(kBM >> 4) << 24);
+
+    // byte offset of the 16-byte slot (k chunk k4, row r) inside an operand
+    auto slot = [](int k4, int r, uint32_t lbo) { return k4 * lbo + (r >> 3) * kGroupBytes + (r & 7) * 16; };
+    constexpr int B_BLOCKS = (BN / 4) * (kBK / 4); // 4x4 blocks of the B tile
+    float4 ra[4], rb[4];
+    auto fetch = [&](int k0)
+    {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+        {
+            ra[i] = rb[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (A_T)
+            {
+                const int m4 = tid & 31, k4 = tid >> 5; // one 4 (k) x 4 (m) block per thread
+                if (k0 + 4 * k4 + i < k_end)
+                    ra[i] = al(k0 + 4 * k4 + i, m0 + 4 * m4);
+            }
+            else
+            {
+                const int idx = tid + i * kThreads, mm = idx & (kBM - 1), k4 = idx >> 7;
+                if (k0 + 4 * k4 < k_end)
+                    ra[i] = al(m0 + mm, k0 + 4 * k4);
+            }
+            if (tid < B_BLOCKS)
+            {
+                const int n4 = tid % (BN / 4), k4 = tid / (BN / 4);
+                if (k0 + 4 * k4 + i < k_end)
+                    rb[i] = bl(k0 + 4 * k4 + i, n0 + 4 * n4);
+            }
+        }
+    };
+    auto store_split = [](unsigned char *hi_base, unsigned char *lo_base, int off, const float4 &x)
+    {
+        float4 hi, lo;
+        split_tf32(x, hi, lo);
+        *reinterpret_cast<float4 *>(hi_base + off) = hi;
+        *reinterpret_cast<float4 *>(lo_base + off) = lo;
+    };
+    auto stash = [&](int s)
+    {
+        unsigned char *a_hi = tc_smem + s * STAGE_BYTES, *a_lo = a_hi + A_BYTES, *b_hi = a_lo + A_BYTES, *b_lo = b_hi + B_BYTES;
+        if (A_T)
+        {
+            const int m4 = tid & 31, k4 = tid >> 5;
+            store_split(a_hi, a_lo, slot(k4, 4 * m4 + 0, A_LBO), make_float4(ra[0].x, ra[1].x, ra[2].x, ra[3].x));
+            store_split(a_hi, a_lo, slot(k4, 4 * m4 + 1, A_LBO), make_float4(ra[0].y, ra[1].y, ra[2].y, ra[3].y));
+            store_split(a_hi, a_lo, slot(k4, 4 * m4 + 2, A_LBO), make_float4(ra[0].z, ra[1].z, ra[2].z, ra[3].z));
+            store_split(a_hi, a_lo, slot(k4, 4 * m4 + 3, A_LBO), make_float4(ra[0].w, ra[1].w, ra[2].w, ra[3].w));
+        }
+        else
+        {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+            {
+                const int idx = tid + i * kThreads, mm = idx & (kBM - 1), k4 = idx >> 7;
+                store_split(a_hi, a_lo, slot(k4, mm, A_LBO), ra[i]);
+            }
+        }
+        if (tid < B_BLOCKS)
+        {
+            const int n4 = tid % (BN / 4), k4 = tid / (BN / 4);
+            store_split(b_hi, b_lo, slot(k4, 4 * n4 + 0, B_LBO), make_float4(rb[0].x, rb[1].x, rb[2].x, rb[3].x));
+            store_split(b_hi, b_lo, slot(k4, 4 * n4 + 1, B_LBO), make_float4(rb[0].y, rb[1].y, rb[2].y, rb[3].y));
+            store_split(b_hi, b_lo, slot(k4, 4 * n4 + 2, B_LBO), make_float4(rb[0].z, rb[1].z, rb[2].z, rb[3].z));
+            store_split(b_hi, b_lo, slot(k4, 4 * n4 + 3, B_LBO), make_float4(rb[0].w, rb[1].w, rb[2].w, rb[3].w));
+        }
+    };
+    auto issue = [&](int s, uint32_t acc, bool first_tile)
+    {
+        const uint32_t a_hi = smem_addr(tc_smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES, b_hi = a_lo + A_BYTES, b_lo = b_hi + B_BYTES;
+#pragma unroll
+        for (int j = 0; j < kBK / 8; ++j) // one MMA k-step = 8 tf32 = two 16-byte k chunks
+        {
+            const uint64_t dah = make_desc(a_hi + j * 2 * A_LBO, A_LBO, kGroupBytes), dal = make_desc(a_lo + j * 2 * A_LBO, A_LBO, kGroupBytes);
+            const uint64_t dbh = make_desc(b_hi + j * 2 * B_LBO, B_LBO, kGroupBytes), dbl = make_desc(b_lo + j * 2 * B_LBO, B_LBO, kGroupBytes);
+            mma_tf32(acc, dah, dbh, idesc, (first_tile && j == 0) ? 0u : 1u);
+            mma_tf32(acc, dah, dbl, idesc, 1u);
+            mma_tf32(acc, dal, dbh, idesc, 1u);
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(&mbar[s]))
+                     : "memory");
+    };
+
+    // ---- main loop ------------------------------------------------------------------------------------------------------
+    // The tensor core adds into its fp32 accumulator with truncation, an error that grows linearly with the length of
+    // the chain (measured 1e-8 * K relative).  The reduction is therefore cut into chunks of two k tiles (64 products)
+    // that alternate between two TMEM accumulators; a finished chunk is read back (tcgen05.ld) and added to fp32
+    // registers with round-to-nearest while the next chunk's MMAs run.
+    const int n_tiles = k_begin < k_end ? (k_end - k_begin + kBK - 1) / kBK : 0;
+    const int q = warp & 3, half = warp >> 2;
+    float racc[BN / 2];
+#pragma unroll
+    for (int c = 0; c < BN / 2; ++c)
+        racc[c] = 0.f;
+    auto drain_chunk = [&](int chunk)
+    {
+        const uint32_t base = tmem_acc + (chunk & 1) * BN + (static_cast<uint32_t>(32 * q) << 16) + half * (BN / 2);
+#pragma unroll
+        for (int c = 0; c < BN / 2; c += 8)
+        {
+            uint32_t r[8];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                         : "r"(base + c));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                racc[c + i] += __uint_as_float(r[i]);
+        }
+    };
+    uint32_t phase[2] = {0u, 0u};
+    if (n_tiles > 0)
+        fetch(k_begin);
+    for (int t = 0; t < n_tiles; ++t)
+    {
+        const int s = t & 1;
+        if (t >= 2)
+        {
+            mbar_wait(&mbar[s], phase[s]); // the MMAs of tile t-2 (which read this stage) are done
+            phase[s] ^= 1u;
+            if (s == 1)
+            {
+                // tile t-2 closed chunk (t-3)/2
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                drain_chunk((t - 3) >> 1);
+            }
+        }
+        stash(s);
+        if (t + 1 < n_tiles)
+            fetch(k_begin + (t + 1) * kBK); // global loads fly while this tile's MMAs run
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (tid == 0)
+        {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            issue(s, tmem_acc + ((t >> 1) & 1) * BN, s == 0);
+        }
+    }
+    // drain: chunks whose closing tile has not been waited for yet
+    if (n_tiles >= 1)
+    {
+        const int last = n_tiles - 1;
+        // tile last-1 (if any) has not been waited for either
+        if (n_tiles >= 2)
+        {
+            mbar_wait(&mbar[(last - 1) & 1], phase[(last - 1) & 1]);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (((last - 1) & 1) == 1)
+                drain_chunk((last - 1) >> 1); // it closed its chunk
+        }
+        mbar_wait(&mbar[last & 1], phase[last & 1]);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        drain_chunk(last >> 1); // the last chunk (one or two tiles)
+    }
+
+    // ---- epilogue: registers -> epi -------------------------------------------------------------------------------------------
+    if (n_tiles > 0)
+    {
+        const int m = m0 + 32 * q + lane;
+        if (m < M)
+        {
+#pragma unroll
+            for (int c = 0; c < BN / 2; c += 4)
+            {
+                const int n = n0 + half * (BN / 2) + c;
+                if (n < N)
+                    epi(m, n, make_float4(racc[c], racc[c + 1], racc[c + 2], racc[c + 3]));
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(TMEM_COLS) : "memory");
+}
+} // namespace tc
+} // namespace cpprl_b200

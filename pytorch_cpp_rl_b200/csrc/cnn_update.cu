@@ -18,6 +18,7 @@
 #include <math.h>
 
 #include "cnn_gemm.cuh"
+#include "cnn_gemm_tc.cuh"
 #include "cnn_update.cuh"
 #include "common.cuh"
 
@@ -812,6 +813,61 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     return launch_colsum(ws.dz1, static_cast<long long>(rows) * kCnnP1, kCnnC1, ws.gflat + a.po.b1, stop, s);
 }
 } // namespace
+
+namespace
+{
+struct PlainStore // C[m][n] = acc
+{
+    float *out;
+    int ld;
+    __device__ __forceinline__ void operator()(int m, int n, float4 v) const
+    {
+        *reinterpret_cast<float4 *>(out + static_cast<size_t>(m) * ld + n) = v;
+    }
+};
+
+template <int BN, bool A_T, class AL, class BL, class EP>
+int launch_gemm_tc(const AL &al, const BL &bl, const EP &ep, int M, int N, int K, int grid_z, bool z_is_k_split, const int *stop,
+                   cudaStream_t s)
+{
+    auto kernel = tc::gemm_tc_kernel<BN, A_T, AL, BL, EP>;
+    static bool configured = false;
+    if (!configured)
+    {
+        CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tc::smem_bytes(BN))));
+        configured = true;
+    }
+    int k_slice = K;
+    if (z_is_k_split)
+        k_slice = ((K + grid_z - 1) / grid_z + tc::kBK - 1) / tc::kBK * tc::kBK;
+    const dim3 grid((M + tc::kBM - 1) / tc::kBM, (N + BN - 1) / BN, grid_z);
+    kernel<<<grid, tc::kThreads, tc::smem_bytes(BN), s>>>(al, bl, ep, M, N, K, k_slice, z_is_k_split ? 1 : 0, stop);
+    CPPRL_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return 0;
+}
+} // namespace
+
+// Test hook: C[M][N] = A * B on the tensor-core path with plain row-major operands: B is [K][N];
+//   variant bit 0: A is given transposed ([K][M]); bits 4..: tile columns 32 / 64 / 128
+int cnn_debug_tc_gemm(int variant, const float *A, const float *B, float *C, int M, int N, int K, cudaStream_t s)
+{
+    const bool a_t = variant & 1;
+    const int bn = (variant >> 4) & 0xff;
+    const MatLoad al{A, a_t ? K : M, a_t ? M : K}, bl{B, K, N};
+    const PlainStore ep{C, N};
+#define CPPRL_TC_CASE(BN_, A_) \
+    if (bn == BN_ && a_t == A_) \
+        return launch_gemm_tc<BN_, A_>(al, bl, ep, M, N, K, 1, false, nullptr, s);
+    CPPRL_TC_CASE(32, false)
+    CPPRL_TC_CASE(32, true)
+    CPPRL_TC_CASE(64, false)
+    CPPRL_TC_CASE(64, true)
+    CPPRL_TC_CASE(128, false)
+    CPPRL_TC_CASE(128, true)
+#undef CPPRL_TC_CASE
+    return fail(CPPRL_B200_EINVAL, "debug_tc_gemm: unknown variant");
+}
 
 int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s)
 {

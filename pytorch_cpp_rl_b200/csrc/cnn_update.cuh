@@ -75,4 +75,5 @@ void cnn_workspace_carve(CnnWorkspace &ws, float *base, int C, int A, int chunk,
 int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s);
 int cnn_minibatch(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s); // forward + backward + decide + optimiser
 int cnn_forward(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s);   // evaluate_actions
+int cnn_debug_tc_gemm(int variant, const float *A, const float *B, float *C, int M, int N, int K, cudaStream_t s);
 } // namespace cpprl_b200
