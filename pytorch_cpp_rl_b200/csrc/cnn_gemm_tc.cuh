@@ -130,8 +130,11 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
     // byte offset of the 16-byte slot (k chunk k4, row r) inside an operand
     auto slot = [](int k4, int r, uint32_t lbo) { return k4 * lbo + (r >> 3) * kGroupBytes + (r & 7) * 16; };
     constexpr int B_BLOCKS = (BN / 4) * (kBK / 4); // 4x4 blocks of the B tile
-    float4 ra[4], rb[4];
-    auto fetch = [&](int k0)
+    // two tiles of operands in flight per thread (the loads of tiles t+1 and t+2 overlap tile t's MMAs)
+    float4 ra2[2][4], rb2[2][4];
+    // K-major A: every vector of this thread belongs to the SAME row m0 + (tid & 127): its context is formed once
+    const auto a_row = al.row(A_T ? 0 : m0 + (tid & (kBM - 1)));
+    auto fetch = [&](int k0, float4 (&ra)[4], float4 (&rb)[4])
     {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
@@ -141,13 +144,13 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
             {
                 const int m4 = tid & 31, k4 = tid >> 5; // one 4 (k) x 4 (m) block per thread
                 if (k0 + 4 * k4 + i < k_end)
-                    ra[i] = al(k0 + 4 * k4 + i, m0 + 4 * m4);
+                    ra[i] = al.load(al.row(k0 + 4 * k4 + i), m0 + 4 * m4);
             }
             else
             {
-                const int idx = tid + i * kThreads, mm = idx & (kBM - 1), k4 = idx >> 7;
+                const int k4 = (tid >> 7) + 2 * i;
                 if (k0 + 4 * k4 < k_end)
-                    ra[i] = al(m0 + mm, k0 + 4 * k4);
+                    ra[i] = al.load(a_row, k0 + 4 * k4);
             }
             if (tid < B_BLOCKS)
             {
@@ -164,7 +167,7 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
         *reinterpret_cast<float4 *>(hi_base + off) = hi;
         *reinterpret_cast<float4 *>(lo_base + off) = lo;
     };
-    auto stash = [&](int s)
+    auto stash = [&](int s, const float4 (&ra)[4], const float4 (&rb)[4])
     {
         unsigned char *a_hi = tc_smem + s * STAGE_BYTES, *a_lo = a_hi + A_BYTES, *b_hi = a_lo + A_BYTES, *b_lo = b_hi + B_BYTES;
         if (A_T)
@@ -238,8 +241,10 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
     };
     uint32_t phase[2] = {0u, 0u};
     if (n_tiles > 0)
-        fetch(k_begin);
-    for (int t = 0; t < n_tiles; ++t)
+        fetch(k_begin, ra2[0], rb2[0]);
+    if (n_tiles > 1)
+        fetch(k_begin + kBK, ra2[1], rb2[1]);
+    auto tile_step = [&](int t, float4 (&ra)[4], float4 (&rb)[4])
     {
         const int s = t & 1;
         if (t >= 2)
@@ -253,9 +258,9 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
                 drain_chunk((t - 3) >> 1);
             }
         }
-        stash(s);
-        if (t + 1 < n_tiles)
-            fetch(k_begin + (t + 1) * kBK); // global loads fly while this tile's MMAs run
+        stash(s, ra, rb);
+        if (t + 2 < n_tiles)
+            fetch(k_begin + (t + 2) * kBK, ra, rb); // two tiles of global loads stay in flight
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
@@ -264,6 +269,12 @@ __global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             issue(s, tmem_acc + ((t >> 1) & 1) * BN, s == 0);
         }
+    };
+    for (int t = 0; t < n_tiles; t += 2)
+    {
+        tile_step(t, ra2[0], rb2[0]);
+        if (t + 1 < n_tiles)
+            tile_step(t + 1, ra2[1], rb2[1]);
     }
     // drain: chunks whose closing tile has not been waited for yet
     if (n_tiles >= 1)

@@ -17,6 +17,8 @@
 // decision (ppo.cpp:100-104) is taken on the device before the optimiser kernel runs.
 #include <math.h>
 
+#include <cstdlib>
+
 #include "cnn_gemm.cuh"
 #include "cnn_gemm_tc.cuh"
 #include "cnn_update.cuh"
@@ -105,25 +107,40 @@ void cnn_workspace_carve(CnnWorkspace &ws, float *base, int C, int A, int chunk,
 namespace
 {
 // ---- operand loaders (see cnn_gemm.cuh: X(r, c) = X[r][c .. c+3]) -----------------------------------------------------
-// im2col of the raw observations for conv1: X[(i, oy, ox)][(c, ky, kx)], pixels divided by 255 (cnn_base.cpp:37).
-// Rows come straight out of the rollout through the minibatch permutation.
+// Every loader splits into row(r) -> RowCtx (the divisions, the permutation look-up, the validity of the row) and
+// load(ctx, c): the tensor-core kernel's K-major A operand keeps ONE row per thread for the whole kernel, so the
+// context is formed once and the k loop only adds offsets.
+struct RowCtx
+{
+    const float *p; // base pointer of the row (null: outside the matrix)
+    int a, b;       // loader specific (pixel coordinates for the data-gradient gathers)
+};
+
+// im2col of the raw observations for conv1: X[(i, oy, ox)][(c, ky, kx)].  Rows come straight out of the rollout through
+// the minibatch permutation; pixels stay raw 0..255 here, the division by 255 (cnn_base.cpp:37) is applied to the
+// accumulated sums in the epilogues (conv is linear in its input; raw integer pixels are exact in TF32).
 struct ObsIm2col
 {
     const float *obs;
     const long long *perm;
     long long row_base;
     int rows, C;
-    __device__ __forceinline__ float4 operator()(int r, int k) const
+    __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * kCnnP1 || k >= C * 64)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r >= rows * kCnnP1)
+            return RowCtx{nullptr, 0, 0};
         const int i = r / kCnnP1, p = r - i * kCnnP1, oy = p / kCnnO1, ox = p - oy * kCnnO1;
-        const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
         const long long row = perm ? __ldg(perm + row_base + i) : row_base + i;
-        const float4 v = __ldg(reinterpret_cast<const float4 *>(obs + (row * C + c) * (kCnnIn * kCnnIn) +
-                                                                 (4 * oy + ky) * kCnnIn + 4 * ox + kx));
-        return make_float4(v.x / 255.f, v.y / 255.f, v.z / 255.f, v.w / 255.f);
+        return RowCtx{obs + row * C * (kCnnIn * kCnnIn) + (4 * oy) * kCnnIn + 4 * ox, 0, 0};
     }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    {
+        if (!ctx.p || k >= C * 64)
+            return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
+        return __ldg(reinterpret_cast<const float4 *>(ctx.p + c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx));
+    }
+    __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
 // im2col of an NHWC activation: X[(i, oy, ox)][(ky, kx, c)]
@@ -132,15 +149,21 @@ struct ActIm2col
 {
     const float *act;
     int rows;
-    __device__ __forceinline__ float4 operator()(int r, int k) const
+    __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * OH * OH || k >= KW * KW * CIN)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r >= rows * OH * OH)
+            return RowCtx{nullptr, 0, 0};
         const int i = r / (OH * OH), p = r - i * (OH * OH), oy = p / OH, ox = p - oy * OH;
-        const int tap = k / CIN, c = k - tap * CIN, ky = tap / KW, kx = tap - ky * KW;
-        return __ldg(reinterpret_cast<const float4 *>(
-            act + (static_cast<size_t>(i) * IH * IH + (S * oy + ky) * IH + S * ox + kx) * CIN + c));
+        return RowCtx{act + (static_cast<size_t>(i) * IH * IH + (S * oy) * IH + S * ox) * CIN, 0, 0};
     }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    {
+        if (!ctx.p || k >= KW * KW * CIN)
+            return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int tap = k / CIN, c = k - tap * CIN, ky = tap / KW, kx = tap - ky * KW;
+        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (ky * IH + kx) * CIN + c));
+    }
+    __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
 // plain row-major matrix [rows][cols]
@@ -148,12 +171,17 @@ struct MatLoad
 {
     const float *p;
     int rows, cols;
-    __device__ __forceinline__ float4 operator()(int r, int c) const
+    __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows || c >= cols)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(p + static_cast<size_t>(r) * cols + c));
+        return RowCtx{r < rows ? p + static_cast<size_t>(r) * cols : nullptr, 0, 0};
     }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int c) const
+    {
+        if (!ctx.p || c >= cols)
+            return make_float4(0.f, 0.f, 0.f, 0.f);
+        return __ldg(reinterpret_cast<const float4 *>(ctx.p + c));
+    }
+    __device__ __forceinline__ float4 operator()(int r, int c) const { return load(row(r), c); }
 };
 
 // one matrix per blockIdx.z (conv2 data gradient: one weight slice per input-pixel parity class)
@@ -174,17 +202,22 @@ struct Dgrad3Load
 {
     const float *dz;
     int rows;
-    __device__ __forceinline__ float4 operator()(int r, int k) const
+    __device__ __forceinline__ RowCtx row(int r) const
     {
         if (r >= rows * kCnnP2)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
+            return RowCtx{nullptr, 0, 0};
         const int i = r / kCnnP2, p = r - i * kCnnP2, y = p / kCnnO2, x = p - y * kCnnO2;
-        const int tap = k >> 5, n = k & 31, ky = tap / 3, kx = tap - 3 * ky;
-        const int oy = y - ky, ox = x - kx;
-        if (oy < 0 || oy >= kCnnO3 || ox < 0 || ox >= kCnnO3)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(dz + (static_cast<size_t>(i) * kCnnP3 + oy * kCnnO3 + ox) * kCnnC3 + n));
+        return RowCtx{dz + static_cast<size_t>(i) * kCnnP3 * kCnnC3, y, x};
     }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    {
+        const int tap = k >> 5, n = k & 31, ky = tap / 3, kx = tap - 3 * ky;
+        const int oy = ctx.a - ky, ox = ctx.b - kx;
+        if (!ctx.p || oy < 0 || oy >= kCnnO3 || ox < 0 || ox >= kCnnO3)
+            return make_float4(0.f, 0.f, 0.f, 0.f);
+        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (oy * kCnnO3 + ox) * kCnnC3 + n));
+    }
+    __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
 // conv2 data gradient for the input pixels (y, x) = (2 py + cy, 2 px + cx) of parity class blockIdx.z = 2 cy + cx:
@@ -193,39 +226,50 @@ struct Dgrad2Load
 {
     const float *dz;
     int rows;
-    __device__ __forceinline__ float4 operator()(int r, int k) const
+    __device__ __forceinline__ RowCtx row(int r) const
     {
         if (r >= rows * 100)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
+            return RowCtx{nullptr, 0, 0};
         const int i = r / 100, p = r - i * 100, py = p / 10, px = p - py * 10;
-        const int tap = k >> 6, n = k & 63, oy = py - (tap >> 1), ox = px - (tap & 1);
-        if (oy < 0 || oy >= kCnnO2 || ox < 0 || ox >= kCnnO2)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(dz + (static_cast<size_t>(i) * kCnnP2 + oy * kCnnO2 + ox) * kCnnC2 + n));
+        return RowCtx{dz + static_cast<size_t>(i) * kCnnP2 * kCnnC2, py, px};
     }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    {
+        const int tap = k >> 6, n = k & 63, oy = ctx.a - (tap >> 1), ox = ctx.b - (tap & 1);
+        if (!ctx.p || oy < 0 || oy >= kCnnO2 || ox < 0 || ox >= kCnnO2)
+            return make_float4(0.f, 0.f, 0.f, 0.f);
+        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (oy * kCnnO2 + ox) * kCnnC2 + n));
+    }
+    __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
 // ---- epilogues ------------------------------------------------------------------------------------------------------------
-struct BiasReluStore // out[m][n] = relu(acc + bias[n])
+struct BiasReluStore // out[m][n] = relu(acc / div + bias[n])   (div = 255 for conv1: raw pixels in, see ObsIm2col)
 {
     float *out;
     const float *bias;
     int ld;
+    float div;
     __device__ __forceinline__ void operator()(int m, int n, float4 v) const
     {
         const float4 b = __ldg(reinterpret_cast<const float4 *>(bias + n));
+        if (div != 1.f)
+            v.x = v.x / div, v.y = v.y / div, v.z = v.z / div, v.w = v.w / div;
         v.x = fmaxf(v.x + b.x, 0.f), v.y = fmaxf(v.y + b.y, 0.f), v.z = fmaxf(v.z + b.z, 0.f), v.w = fmaxf(v.w + b.w, 0.f);
         *reinterpret_cast<float4 *>(out + static_cast<size_t>(m) * ld + n) = v;
     }
 };
 
-struct AtomicAddStore // gradient image, reduction split across the grid
+struct AtomicAddStore // gradient image, reduction split across the grid (div as above)
 {
     float *out;
     int ld;
+    float div;
     __device__ __forceinline__ void operator()(int m, int n, float4 v) const
     {
         float *o = out + static_cast<size_t>(m) * ld + n;
+        if (div != 1.f)
+            v.x = v.x / div, v.y = v.y / div, v.z = v.z / div, v.w = v.w / div;
         atomicAdd(o, v.x), atomicAdd(o + 1, v.y), atomicAdd(o + 2, v.z), atomicAdd(o + 3, v.w);
     }
 };
@@ -686,10 +730,54 @@ __global__ void __launch_bounds__(256) cnn_optimizer_kernel(const CnnUpdateArgs 
 // ---- host orchestration -------------------------------------------------------------------------------------------------
 namespace
 {
+struct PlainStore // C[m][n] = acc
+{
+    float *out;
+    int ld;
+    __device__ __forceinline__ void operator()(int m, int n, float4 v) const
+    {
+        *reinterpret_cast<float4 *>(out + static_cast<size_t>(m) * ld + n) = v;
+    }
+};
+
+template <int BN, bool A_T, class AL, class BL, class EP>
+int launch_gemm_tc(const AL &al, const BL &bl, const EP &ep, int M, int N, int K, int grid_z, bool z_is_k_split, const int *stop,
+                   cudaStream_t s)
+{
+    auto kernel = tc::gemm_tc_kernel<BN, A_T, AL, BL, EP>;
+    static bool configured = false;
+    if (!configured)
+    {
+        CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tc::smem_bytes(BN))));
+        configured = true;
+    }
+    int k_slice = K;
+    if (z_is_k_split)
+        k_slice = ((K + grid_z - 1) / grid_z + tc::kBK - 1) / tc::kBK * tc::kBK;
+    const dim3 grid((M + tc::kBM - 1) / tc::kBM, (N + BN - 1) / BN, grid_z);
+    kernel<<<grid, tc::kThreads, tc::smem_bytes(BN), s>>>(al, bl, ep, M, N, K, k_slice, z_is_k_split ? 1 : 0, stop);
+    CPPRL_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return 0;
+}
+
+// Tensor cores (tcgen05, 3xTF32) by default; CPPRL_B200_CNN_FP32=1 selects the fp32 FFMA kernels (same loaders and
+// epilogues), kept for A/B measurements.
+inline bool use_tensor_cores()
+{
+    static const bool on = [] {
+        const char *e = std::getenv("CPPRL_B200_CNN_FP32");
+        return !(e && e[0] == '1');
+    }();
+    return on;
+}
+
 template <int BM, int BN, int TM, int TN, bool A_T, class AL, class BL, class EP>
 int launch_gemm(const AL &al, const BL &bl, const EP &ep, int M, int N, int K, int grid_z, bool z_is_k_split, const int *stop,
                 cudaStream_t s)
 {
+    if (use_tensor_cores())
+        return launch_gemm_tc<BN, A_T>(al, bl, ep, M, N, K, grid_z, z_is_k_split, stop, s);
     int k_slice = K;
     if (z_is_k_split)
         k_slice = ((K + grid_z - 1) / grid_z + kGemmBK - 1) / kGemmBK * kGemmBK;
@@ -719,21 +807,21 @@ int cnn_forward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, i
     const float *img = ws.img;
     if (int rc = launch_gemm<256, 32, 8, 4, false>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C},
                                                    MatLoad{img + a.il.w1, K1, kCnnC1},
-                                                   BiasReluStore{ws.act1, a.params + a.po.b1, kCnnC1}, rows * kCnnP1, kCnnC1,
+                                                   BiasReluStore{ws.act1, a.params + a.po.b1, kCnnC1, 255.f}, rows * kCnnP1, kCnnC1,
                                                    K1, 1, false, stop, s))
         return rc;
     if (int rc = launch_gemm<128, 64, 8, 4, false>(ActIm2col<kCnnO1, kCnnO2, 4, 2, kCnnC1>{ws.act1, rows},
                                                    MatLoad{img + a.il.w2, kCnnK2, kCnnC2},
-                                                   BiasReluStore{ws.act2, a.params + a.po.b2, kCnnC2}, rows * kCnnP2, kCnnC2,
+                                                   BiasReluStore{ws.act2, a.params + a.po.b2, kCnnC2, 1.f}, rows * kCnnP2, kCnnC2,
                                                    kCnnK2, 1, false, stop, s))
         return rc;
     if (int rc = launch_gemm<256, 32, 8, 4, false>(ActIm2col<kCnnO2, kCnnO3, 3, 1, kCnnC2>{ws.act2, rows},
                                                    MatLoad{img + a.il.w3, kCnnK3, kCnnC3},
-                                                   BiasReluStore{ws.act3, a.params + a.po.b3, kCnnC3}, rows * kCnnP3, kCnnC3,
+                                                   BiasReluStore{ws.act3, a.params + a.po.b3, kCnnC3, 1.f}, rows * kCnnP3, kCnnC3,
                                                    kCnnK3, 1, false, stop, s))
         return rc;
     return launch_gemm<128, 128, 8, 8, false>(MatLoad{ws.act3, rows, kCnnFlat}, MatLoad{img + a.il.wfc, kCnnFlat, kCnnHid},
-                                              BiasReluStore{ws.h, a.params + a.po.bfc, kCnnHid}, rows, kCnnHid, kCnnFlat, 1,
+                                              BiasReluStore{ws.h, a.params + a.po.bfc, kCnnHid, 1.f}, rows, kCnnHid, kCnnFlat, 1,
                                               false, stop, s);
 }
 
@@ -770,7 +858,7 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     const float *img = ws.img;
     // linear 1568 -> 512: weight gradient (reduction over rows), bias, data gradient masked by conv3's ReLU
     if (int rc = launch_gemm<128, 128, 8, 8, true>(MatLoad{ws.act3, rows, kCnnFlat}, MatLoad{ws.dh, rows, kCnnHid},
-                                                   AtomicAddStore{ws.gimg + a.il.wfc, kCnnHid}, kCnnFlat, kCnnHid, rows,
+                                                   AtomicAddStore{ws.gimg + a.il.wfc, kCnnHid, 1.f}, kCnnFlat, kCnnHid, rows,
                                                    splits_for(13 * 4, rows), true, stop, s))
         return rc;
     if (int rc = launch_colsum(ws.dh, rows, kCnnHid, ws.gflat + a.po.bfc, stop, s))
@@ -782,8 +870,8 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     // conv3
     if (int rc = launch_gemm<256, 32, 8, 4, true>(ActIm2col<kCnnO2, kCnnO3, 3, 1, kCnnC2>{ws.act2, rows},
                                                   MatLoad{ws.dz3, rows * kCnnP3, kCnnC3},
-                                                  AtomicAddStore{ws.gimg + a.il.w3, kCnnC3}, kCnnK3, kCnnC3, rows * kCnnP3,
-                                                  splits_for(3, static_cast<long long>(rows) * kCnnP3), true, stop, s))
+                                                  AtomicAddStore{ws.gimg + a.il.w3, kCnnC3, 1.f}, kCnnK3, kCnnC3, rows * kCnnP3,
+                                                  splits_for(use_tensor_cores() ? 5 : 3, static_cast<long long>(rows) * kCnnP3), true, stop, s))
         return rc;
     if (int rc = launch_colsum(ws.dz3, static_cast<long long>(rows) * kCnnP3, kCnnC3, ws.gflat + a.po.b3, stop, s))
         return rc;
@@ -794,7 +882,7 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     // conv2
     if (int rc = launch_gemm<128, 64, 8, 4, true>(ActIm2col<kCnnO1, kCnnO2, 4, 2, kCnnC1>{ws.act1, rows},
                                                   MatLoad{ws.dz2, rows * kCnnP2, kCnnC2},
-                                                  AtomicAddStore{ws.gimg + a.il.w2, kCnnC2}, kCnnK2, kCnnC2, rows * kCnnP2,
+                                                  AtomicAddStore{ws.gimg + a.il.w2, kCnnC2, 1.f}, kCnnK2, kCnnC2, rows * kCnnP2,
                                                   splits_for(4, static_cast<long long>(rows) * kCnnP2), true, stop, s))
         return rc;
     if (int rc = launch_colsum(ws.dz2, static_cast<long long>(rows) * kCnnP2, kCnnC2, ws.gflat + a.po.b2, stop, s))
@@ -806,45 +894,11 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     // conv1 (its input needs no gradient)
     if (int rc = launch_gemm<256, 32, 8, 4, true>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C},
                                                   MatLoad{ws.dz1, rows * kCnnP1, kCnnC1},
-                                                  AtomicAddStore{ws.gimg + a.il.w1, kCnnC1}, K1, kCnnC1, rows * kCnnP1,
-                                                  splits_for((K1 + 255) / 256, static_cast<long long>(rows) * kCnnP1), true,
+                                                  AtomicAddStore{ws.gimg + a.il.w1, kCnnC1, 255.f}, K1, kCnnC1, rows * kCnnP1,
+                                                  splits_for((K1 + 255) / 256 * (use_tensor_cores() ? 2 : 1), static_cast<long long>(rows) * kCnnP1), true,
                                                   stop, s))
         return rc;
     return launch_colsum(ws.dz1, static_cast<long long>(rows) * kCnnP1, kCnnC1, ws.gflat + a.po.b1, stop, s);
-}
-} // namespace
-
-namespace
-{
-struct PlainStore // C[m][n] = acc
-{
-    float *out;
-    int ld;
-    __device__ __forceinline__ void operator()(int m, int n, float4 v) const
-    {
-        *reinterpret_cast<float4 *>(out + static_cast<size_t>(m) * ld + n) = v;
-    }
-};
-
-template <int BN, bool A_T, class AL, class BL, class EP>
-int launch_gemm_tc(const AL &al, const BL &bl, const EP &ep, int M, int N, int K, int grid_z, bool z_is_k_split, const int *stop,
-                   cudaStream_t s)
-{
-    auto kernel = tc::gemm_tc_kernel<BN, A_T, AL, BL, EP>;
-    static bool configured = false;
-    if (!configured)
-    {
-        CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tc::smem_bytes(BN))));
-        configured = true;
-    }
-    int k_slice = K;
-    if (z_is_k_split)
-        k_slice = ((K + grid_z - 1) / grid_z + tc::kBK - 1) / tc::kBK * tc::kBK;
-    const dim3 grid((M + tc::kBM - 1) / tc::kBM, (N + BN - 1) / BN, grid_z);
-    kernel<<<grid, tc::kThreads, tc::smem_bytes(BN), s>>>(al, bl, ep, M, N, K, k_slice, z_is_k_split ? 1 : 0, stop);
-    CPPRL_CUDA_TRY(cudaGetLastError());
-    count_launch();
-    return 0;
 }
 } // namespace
 

@@ -179,7 +179,7 @@ def test_ppo_update_cnn_float64_tiebreak(ref, seed):
             if name.startswith(upstream_of_flip) and upstream_of_flip:
                 assert a <= 2e-2, (upd, name, a)
             else:
-                assert a <= 3.0 * b + 2e-6, (upd, name, a, b)
+                assert a <= 3.0 * b + 1e-5, (upd, name, a, b)  # 1e-5: a tenth of the 1e-4 parity budget
         for i in range(4):
             d_ref, d_gpu = abs(want[i] - s64[i]), abs(got[i] - s64[i])
             slack = 1e-3 if seed == 0 and upd > 0 else 1e-4
