@@ -68,14 +68,13 @@ __device__ __forceinline__ void mbar_wait(void *bar, uint32_t parity)
             : "memory");
 }
 
+// x = hi + lo with hi on the TF32 grid (round to nearest, ties away: what cvt.rna.tf32.f32 does, written as integer
+// arithmetic because the cvt expands to a four-instruction sequence with an Inf/NaN guard this path has no use for;
+// Inf stays Inf, values within half a TF32 ulp of FLT_MAX round to Inf) and lo = x - hi exact in fp32.
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
 __device__ __forceinline__ void split_tf32(const float4 &x, float4 &hi, float4 &lo)
 {
-    uint32_t h0, h1, h2, h3;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h0) : "f"(x.x));
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h1) : "f"(x.y));
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h2) : "f"(x.z));
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h3) : "f"(x.w));
-    hi = make_float4(__uint_as_float(h0), __uint_as_float(h1), __uint_as_float(h2), __uint_as_float(h3));
+    hi = make_float4(tf32_hi(x.x), tf32_hi(x.y), tf32_hi(x.z), tf32_hi(x.w));
     lo = make_float4(x.x - hi.x, x.y - hi.y, x.z - hi.z, x.w - hi.w);
 }
 
@@ -89,7 +88,7 @@ __host__ __device__ constexpr size_t smem_bytes(int BN) { return static_cast<siz
 // A_T: A(m, k) = X[k][m] (the loader's vectors run along m: transposed on the way into shared memory); else
 // A(m, k) = X[m][k] (vectors along k).  B(k, n) = Y[k][n] always (vectors along n, transposed likewise).
 template <int BN, bool A_T, class ALoad, class BLoad, class Epi>
-__global__ void __launch_bounds__(kThreads) gemm_tc_kernel(const ALoad al, const BLoad bl, const Epi epi, int M, int N, int K,
+__global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(const ALoad al, const BLoad bl, const Epi epi, int M, int N, int K,
                                                            int k_slice, int z_is_k_split, const int *stop_flag)
 {
     static_assert(BN == 32 || BN == 64 || BN == 128, "tile columns");

@@ -749,6 +749,8 @@ int launch_gemm_tc(const AL &al, const BL &bl, const EP &ep, int M, int N, int K
     if (!configured)
     {
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tc::smem_bytes(BN))));
+        // two CTAs per SM (BN <= 64) need the whole 228 KB carve-out; the driver's default sizes it for one
+        CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         configured = true;
     }
     int k_slice = K;
