@@ -322,6 +322,7 @@ void fill_cnn_policy_args(CnnUpdateArgs &a, const cpprl_b200_policy &p)
     a.po = cnn_param_offsets(a.C, a.A, a.head);
     a.il = cnn_image_layout(a.C);
     a.params = p.d_params;
+    a.comm.world = 1;
 }
 
 // rows per pass of the CNN path: activations + their gradients take 160 KB per row
@@ -616,12 +617,16 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     h->epoch = 0;
     if (h->cnn)
     {
-        if (sharded)
-            return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: the CnnBase path is single-GPU in this round");
         if (mbs > 0x7fffffffll / kCnnP1 / 4)
             return fail(CPPRL_B200_EUNSUPPORTED, "ppo_update: minibatch too large");
         CnnUpdateArgs &c = h->cargs;
         fill_cnn_policy_args(c, *policy);
+        if (sharded)
+        {
+            c.comm = comm_view(h->comm);
+            if (cnn_exchange_floats(c.C, c.A) > 2ll * c.comm.x_stride)
+                return fail(CPPRL_B200_EINVAL, "ppo_update: the communicator was created for fewer parameters than this policy has");
+        }
         const int chunk = cnn_chunk_rows(mbs);
         if (int rc = h->scratch.ensure(0, 0, 0))
             return rc;
@@ -633,8 +638,9 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         c.value_preds = ro->d_value_preds;
         c.returns = ro->d_returns;
         c.old_logp = ro->d_action_log_probs;
-        c.rows = rows;
+        c.rows = rows; // box-wide: the advantage moments and every mean are over the GLOBAL rollout / minibatch
         c.B = static_cast<int>(mbs);
+        c.B_norm = static_cast<int>(mbs);
         c.adv_sums = h->scratch.adv_sums;
         c.algo = kAlgoPPO;
         c.clip_param = opt->clip_param;
@@ -656,9 +662,13 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         KernelTimer timer("prologue", cs);
         reset_state_kernel<<<1, 1, 0, cs>>>(h->scratch.state);
         CPPRL_LAUNCH_CHECK("reset_state_kernel");
-        CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 2 * sizeof(double), cs));
-        if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, rows, h->scratch.adv_sums, cs))
+        double *moments = sharded ? comm_local_adv(h->comm) : h->scratch.adv_sums;
+        CPPRL_CUDA_TRY(cudaMemsetAsync(moments, 0, 2 * sizeof(double), cs));
+        if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, moments, cs))
             return rc;
+        if (sharded)
+            if (int rc = cnn_adv_exchange(c.comm, ++*comm_update_seq(h->comm), h->scratch.adv_sums, h->scratch.state, cs))
+                return rc;
         if (int rc = cnn_build_images(c, h->cws, cs))
             return rc;
         h->active = true;
@@ -765,17 +775,57 @@ extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
     g_dbg_step = step;
 }
 
+static int ppo_shard_permutation(cpprl_b200_ppo *h, const int64_t *d_perm)
+{
+    const size_t need = static_cast<size_t>(h->mbs * h->n_mb);
+    if (need > h->lperm_cap)
+    {
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_lperm);
+        h->d_lperm = nullptr;
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_lperm, need * sizeof(int64_t)));
+        h->lperm_cap = need;
+    }
+    if (static_cast<size_t>(h->n_mb) > h->counts_cap)
+    {
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+        cudaFree(h->d_counts);
+        h->d_counts = nullptr;
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_counts, h->n_mb * sizeof(int)));
+        h->counts_cap = h->n_mb;
+    }
+    return launch_shard_permutation(d_perm, h->n_mb, h->mbs, h->global_envs, h->env_offset, h->rollout.N, h->d_lperm,
+                                    h->d_counts, h->stream);
+}
+
 static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
     if (h->cnn)
     {
         // one pass over the epoch's minibatches, every kernel enqueued on the stream; the KL decision stays on the
         // device (kernels of later minibatches see state->stopped and return)
+        std::vector<int> counts;
+        if (h->comm)
+        {
+            // this rank's rows of every minibatch (stable compaction of the global permutation, comm.cu); the row
+            // counts size the grids, so they come back to the host: one small synchronising copy per epoch
+            if (int rc = ppo_shard_permutation(h, d_perm))
+                return rc;
+            counts.resize(h->n_mb);
+            CPPRL_CUDA_TRY(cudaMemcpyAsync(counts.data(), h->d_counts, h->n_mb * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
+            d_perm = h->d_lperm;
+        }
         KernelTimer timer("update", h->stream);
         h->cargs.perm = reinterpret_cast<const long long *>(d_perm);
         for (int64_t mb = 0; mb < h->n_mb; ++mb)
         {
             h->cargs.row_base = mb * h->mbs;
+            if (h->comm)
+            {
+                h->cargs.B = counts[mb];
+                h->cargs.xseq = ++*comm_step_seq(h->comm);
+            }
             if (int rc = cnn_minibatch(h->cargs, h->cws, h->stream))
                 return rc;
         }
@@ -796,25 +846,7 @@ static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
     if (h->comm)
     {
         // compact the global permutation to the rows this rank owns (stable, one CTA per minibatch)
-        const size_t need = static_cast<size_t>(h->mbs * h->n_mb);
-        if (need > h->lperm_cap)
-        {
-            CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
-            cudaFree(h->d_lperm);
-            h->d_lperm = nullptr;
-            CPPRL_CUDA_TRY(cudaMalloc(&h->d_lperm, need * sizeof(int64_t)));
-            h->lperm_cap = need;
-        }
-        if (static_cast<size_t>(h->n_mb) > h->counts_cap)
-        {
-            CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
-            cudaFree(h->d_counts);
-            h->d_counts = nullptr;
-            CPPRL_CUDA_TRY(cudaMalloc(&h->d_counts, h->n_mb * sizeof(int)));
-            h->counts_cap = h->n_mb;
-        }
-        if (int rc = launch_shard_permutation(d_perm, h->n_mb, h->mbs, h->global_envs, h->env_offset, h->rollout.N,
-                                              h->d_lperm, h->d_counts, h->stream))
+        if (int rc = ppo_shard_permutation(h, d_perm))
             return rc;
         d_perm = h->d_lperm;
         h->args.step_rows = h->d_counts;
@@ -1115,10 +1147,16 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
         return a2c_update_gru(h, policy, ro, opt, s);
     if (policy->base_kind == CPPRL_B200_BASE_CNN)
     {
-        if (h->comm)
-            return fail(CPPRL_B200_EUNSUPPORTED, "a2c_update: the CnnBase path is single-GPU in this round");
         CnnUpdateArgs c;
         fill_cnn_policy_args(c, *policy);
+        if (sharded)
+        {
+            // every rank holds the same number of environments; the loss means are over the box-wide T * global_envs rows
+            c.comm = comm_view(h->comm);
+            if (cnn_exchange_floats(c.C, c.A) > 2ll * c.comm.x_stride)
+                return fail(CPPRL_B200_EINVAL, "a2c_update: the communicator was created for fewer parameters than this policy has");
+            c.xseq = ++*comm_step_seq(h->comm);
+        }
         const int chunk = cnn_chunk_rows(rows);
         if (int rc = h->scratch.ensure(0, 0, 0))
             return rc;
@@ -1130,8 +1168,9 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
         c.actions = ro->d_actions;
         c.value_preds = ro->d_value_preds;
         c.returns = ro->d_returns;
-        c.rows = rows;
+        c.rows = rows_global;
         c.B = static_cast<int>(rows);
+        c.B_norm = static_cast<int>(rows_global);
         c.algo = kAlgoA2C;
         c.c_actor = 1.f;
         c.c_value = opt->value_loss_coef;

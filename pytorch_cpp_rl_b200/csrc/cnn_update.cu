@@ -925,6 +925,91 @@ int cnn_debug_tc_gemm(int variant, const float *A, const float *B, float *C, int
     return fail(CPPRL_B200_EINVAL, "debug_tc_gemm: unknown variant");
 }
 
+namespace
+{
+// ---- env-sharded update: sum of the gradient vector over the GPUs of the box (NVLink peer memory, comm.cuh) ---------------
+// Pull protocol with one flag per CTA: CTA b copies slice b of {grad[0, n), sums[0, 8)} into this rank's exchange buffer
+// (parity = sequence & 1), publishes step_flag[b] = seq (system fence + release store), then for every rank IN RANK
+// ORDER waits for that rank's flag b and adds its slice (peer reads over NVLink; the own slice from local memory) —
+// every rank forms the same sum in the same order, so the optimiser steps stay bit-identical box-wide.  A buffer is
+// rewritten two exchanges later, which no peer can still be reading: finishing exchange s+1 needs every peer's
+// record s+1, published only after that peer finished reading s.
+__global__ void __launch_bounds__(256) cnn_allreduce_kernel(const CommView comm, unsigned int seq, float *__restrict__ grad,
+                                                            long long n, float *__restrict__ sums, UpdateState *st)
+{
+    if (st->stopped)
+        return;
+    const int world = comm.world, me = comm.rank, b = blockIdx.x, G = gridDim.x;
+    const long long total = n + 8; // n is a multiple of 4 (workspace carve), the sums ride at the end
+    const long long per = ((total / 4 + G - 1) / G) * 4;
+    const long long lo = static_cast<long long>(b) * per, hi = lo + per < total ? lo + per : total;
+    float *mine = exchange_fbuf(comm.area[me], seq & 1u, world, comm.x_stride);
+    auto src = [&](long long i) -> const float * { return i < n ? grad + i : sums + (i - n); };
+    for (long long i = lo + 4ll * threadIdx.x; i < hi; i += 4ll * blockDim.x)
+        *reinterpret_cast<float4 *>(mine + i) = *reinterpret_cast<const float4 *>(src(i));
+    __syncthreads();
+    __shared__ int ok;
+    if (threadIdx.x == 0)
+    {
+        flag_publish(&comm.area[me]->step_flag[b], seq);
+        int good = 1;
+        for (int r = 0; r < world; ++r)
+            if (r != me && !flag_wait(&comm.area[r]->step_flag[b], seq))
+                good = 0;
+        ok = good;
+        if (!good)
+            st->comm_error = 1;
+    }
+    __syncthreads();
+    if (!ok)
+        return;
+    for (long long i = lo + 4ll * threadIdx.x; i < hi; i += 4ll * blockDim.x)
+    {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < world; ++r)
+        {
+            const float4 v = r == me ? *reinterpret_cast<const float4 *>(mine + i)
+                                     : peer_load4(exchange_fbuf(comm.area[r], seq & 1u, world, comm.x_stride) + i);
+            acc.x += v.x, acc.y += v.y, acc.z += v.z, acc.w += v.w;
+        }
+        *reinterpret_cast<float4 *>(const_cast<float *>(src(i))) = acc;
+    }
+}
+
+// box-wide advantage moments (ppo.cpp:57 over the GLOBAL rollout): the local {sum, sum of squares} sit in this rank's
+// exchange area; read every rank's in rank order
+__global__ void cnn_adv_exchange_kernel(const CommView comm, unsigned int seq, double *out, UpdateState *st)
+{
+    flag_publish(&comm.area[comm.rank]->adv_flag, seq);
+    double s1 = 0.0, s2 = 0.0;
+    for (int r = 0; r < comm.world; ++r)
+    {
+        if (r != comm.rank && !flag_wait(&comm.area[r]->adv_flag, seq))
+            st->comm_error = 1;
+        s1 += peer_load(comm.area[r]->adv);
+        s2 += peer_load(comm.area[r]->adv + 1);
+    }
+    out[0] = s1;
+    out[1] = s2;
+}
+} // namespace
+
+int cnn_adv_exchange(const CommView &comm, unsigned int seq, double *out, UpdateState *st, cudaStream_t s)
+{
+    cnn_adv_exchange_kernel<<<1, 1, 0, s>>>(comm, seq, out, st);
+    CPPRL_CUDA_TRY(cudaGetLastError());
+    count_launch();
+    return 0;
+}
+
+// floats one exchange record of the CnnBase update takes (checked against the communicator's capacity)
+long long cnn_exchange_floats(int C, int A)
+{
+    const CnnImageLayout il = cnn_image_layout(C);
+    const CnnParamOffsets po = cnn_param_offsets(C, A, 1);
+    return static_cast<long long>((il.grad_total + 15) & ~15ll) + ((po.P + 15) & ~15ll) + 8;
+}
+
 int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s)
 {
     cnn_build_images_kernel<<<std::min(4 * sm_count(), (a.po.P + 255) / 256), 256, 0, s>>>(a.params, a.po, a.il, a.C, ws.img);
@@ -936,9 +1021,11 @@ int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_
 int cnn_minibatch(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s)
 {
     const int *stop = &a.state->stopped;
-    const float inv_b = 1.f / static_cast<float>(a.B);
+    const bool sharded = a.comm.world > 1;
+    const float inv_b = 1.f / static_cast<float>(sharded ? a.B_norm : a.B); // every mean divides by the box-wide row count
     // gradient image and flat gradients are adjacent in the workspace: one clear; then the five partial sums
-    CPPRL_CUDA_TRY(cudaMemsetAsync(ws.gimg, 0, (reinterpret_cast<char *>(ws.gflat + a.po.P) - reinterpret_cast<char *>(ws.gimg)), s));
+    const long long grad_floats = (ws.gflat - ws.gimg) + ((a.po.P + 15) & ~15ll);
+    CPPRL_CUDA_TRY(cudaMemsetAsync(ws.gimg, 0, grad_floats * sizeof(float), s));
     CPPRL_CUDA_TRY(cudaMemsetAsync(ws.sums, 0, 8 * sizeof(float), s));
     for (int base = 0; base < a.B; base += ws.chunk)
     {
@@ -949,6 +1036,13 @@ int cnn_minibatch(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s
             return rc;
         if (int rc = cnn_backward_pass(a, ws, base, rows, stop, s))
             return rc;
+    }
+    if (sharded)
+    {
+        // (a rank without rows in this minibatch contributes zeros)
+        cnn_allreduce_kernel<<<std::min(sm_count(), kMaxCtas), 256, 0, s>>>(a.comm, a.xseq, ws.gimg, grad_floats, ws.sums, a.state);
+        CPPRL_CUDA_TRY(cudaGetLastError());
+        count_launch();
     }
     cnn_decide_kernel<<<1, 1, 0, s>>>(a.state, ws.sums, ws.consts, a.algo, inv_b, a.kl_limit, a.lr, a.beta1, a.beta2);
     CPPRL_CUDA_TRY(cudaGetLastError());

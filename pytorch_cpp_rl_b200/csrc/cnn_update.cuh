@@ -55,7 +55,7 @@ struct CnnUpdateArgs
     long long rows;
     const long long *perm; // row ids of THIS minibatch (device), nullable = identity from row_base
     long long row_base;
-    int B;                 // rows of the minibatch
+    int B;                 // rows of the minibatch (held by this rank)
     const double *adv_sums;
     int algo;
     float clip_param, clip_lo, clip_hi, c_actor, c_value, c_entropy;
@@ -66,6 +66,11 @@ struct CnnUpdateArgs
     float beta1, beta2, eps, alpha;
     UpdateState *state;
     float *out_value, *out_logp, *out_entropy_sum; // forward evaluation
+    // env-sharded update (world > 1): B rows of this rank out of a minibatch of B_norm rows box-wide; gradients and
+    // partial sums are added over the ranks (exchange sequence number xseq) before the optimiser step
+    int B_norm;
+    CommView comm;
+    unsigned int xseq;
 };
 
 CnnParamOffsets cnn_param_offsets(int C, int A, int head);
@@ -75,5 +80,7 @@ void cnn_workspace_carve(CnnWorkspace &ws, float *base, int C, int A, int chunk,
 int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s);
 int cnn_minibatch(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s); // forward + backward + decide + optimiser
 int cnn_forward(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s);   // evaluate_actions
+int cnn_adv_exchange(const CommView &comm, unsigned int seq, double *out, UpdateState *st, cudaStream_t s);
+long long cnn_exchange_floats(int C, int A);
 int cnn_debug_tc_gemm(int variant, const float *A, const float *B, float *C, int M, int N, int K, cudaStream_t s);
 } // namespace cpprl_b200

@@ -93,6 +93,18 @@ __device__ __forceinline__ float peer_load(const float *p)
     asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
     return v;
 }
+__device__ __forceinline__ float4 peer_load4(const float *p)
+{
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+// The gradient exchange seen as plain floats (bulk records published under the per-CTA step flags: the CnnBase
+// all-reduce): buffer `parity` of area `a` holds 2 * x_stride floats per sender slot; a rank uses slot 0 of its own area.
+__device__ __forceinline__ float *exchange_fbuf(ExchangeArea *a, int parity, int world, int x_stride)
+{
+    return reinterpret_cast<float *>(exchange_xbuf(a)) + static_cast<size_t>(parity) * world * 2 * x_stride;
+}
 __device__ __forceinline__ double peer_load(const double *p)
 {
     double v;

@@ -59,11 +59,15 @@ def run_case(w, seed, rank, world, n_updates=2):
         else:
             got = algo.update(st, 1.0)
         got = np.array([d.value for d in got], np.float32)
-        np.testing.assert_allclose(got[:4] if w.algo == "ppo" else got, want[:4] if w.algo == "ppo" else want, rtol=2e-4,
-                                   atol=5e-6)
+        np.testing.assert_allclose(got[:4] if w.algo == "ppo" else got, want[:4] if w.algo == "ppo" else want,
+                                   rtol=2e-4 if upd == 0 or w.base != "cnn" else 1e-3, atol=5e-6)
         want_p, got_p = sess.get_params(), policy.params.cpu().numpy()
         err = np.abs(got_p - want_p) / np.maximum(np.abs(want_p), w.learning_rate)
         budget = 1e-4 * max(1, w.optimizer_steps) ** 0.5 + 2e-4
+        if w.base == "cnn":
+            # CnnBase: the bulk within 1e-4, the near-dead-ReLU tail as in tests/test_cnn_gpu.py
+            bulk_ok = np.quantile(err, 0.99) <= 1e-4 and np.quantile(err, 0.999) <= 2e-3
+            budget = 0.5 if bulk_ok else 0.0
         # all ranks bit-identical
         gathered = [torch.empty_like(policy.params) for _ in range(world)]
         dist.all_gather(gathered, policy.params)
@@ -91,6 +95,11 @@ def main():
     ok &= run_case(CONFIGS["cfg3"].scaled(T=16, N=1536, num_epoch=2, num_mini_batch=2), 2, rank, world, n_updates=1)
     ok &= run_case(CONFIGS["cfg1"].scaled(N=10, kl_target=0.01, learning_rate=3e-2), 5, rank, world, n_updates=3)
     ok &= run_case(CONFIGS["cfg2"].scaled(N=512), 3, rank, world)
+    cnn = CONFIGS["cfg5"].scaled(T=8, N=8, num_epoch=2, num_mini_batch=2)
+    ok &= run_case(cnn, 0, rank, world, n_updates=1)
+    ok &= run_case(cnn.scaled(T=6, N=6, num_mini_batch=3, kl_target=0.003, learning_rate=3e-3, num_epoch=3), 4, rank, world)
+    ok &= run_case(cnn.scaled(T=5, N=16, algo="a2c", num_epoch=1, num_mini_batch=1, use_gae=False, learning_rate=7e-4), 7,
+                   rank, world, n_updates=1)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
