@@ -278,17 +278,25 @@ static void test_learning()
 }
 
 // ---- parity with the compiled reference on identical rollouts and identical torch::manual_seed permutations ----------------
-static void test_parity(bool ppo_algo, bool box)
+// base: REF_BASE_MLP, REF_BASE_GRU_MLP (nn_base.cpp:47-114 through recurrent_generator.cpp) or REF_BASE_CNN (cnn_base.cpp)
+static void test_parity(bool ppo_algo, bool box, int base = REF_BASE_MLP)
 {
-    std::printf("parity vs compiled reference: %s %s\n", ppo_algo ? "PPO" : "A2C", box ? "Box/Normal" : "Discrete/Categorical");
-    const int T = ppo_algo ? 32 : 5, N = ppo_algo ? 8 : 64, D = box ? 17 : 8, A = box ? 6 : 4;
+    const bool gru = base == REF_BASE_GRU_MLP, cnn = base == REF_BASE_CNN;
+    std::printf("parity vs compiled reference: %s %s %s\n", ppo_algo ? "PPO" : "A2C", box ? "Box/Normal" : "Discrete/Categorical",
+                gru ? "GRU + MlpBase" : (cnn ? "CnnBase" : "MlpBase"));
+    const int T = cnn ? 8 : (gru ? 16 : (ppo_algo ? 32 : 5)), N = cnn || gru ? 8 : (ppo_algo ? 8 : 64);
+    const int C = 4, D = cnn ? C * 84 * 84 : (box ? 17 : 8), A = box ? 6 : 4, Hs = gru ? 64 : 1;
     RefConfig cfg{};
     cfg.algo = ppo_algo ? REF_ALGO_PPO : REF_ALGO_A2C;
-    cfg.base = REF_BASE_MLP;
+    cfg.base = base;
     cfg.head = box ? REF_HEAD_NORMAL : REF_HEAD_CATEGORICAL;
-    cfg.T = T, cfg.N = N, cfg.obs_ndim = 1, cfg.obs_shape[0] = D, cfg.num_actions = A;
-    cfg.hidden = 64, cfg.storage_hidden = 1, cfg.normalize_obs = 1;
-    cfg.num_epoch = 3, cfg.num_mini_batch = 4;
+    cfg.T = T, cfg.N = N, cfg.num_actions = A;
+    if (cnn)
+        cfg.obs_ndim = 3, cfg.obs_shape[0] = C, cfg.obs_shape[1] = 84, cfg.obs_shape[2] = 84;
+    else
+        cfg.obs_ndim = 1, cfg.obs_shape[0] = D;
+    cfg.hidden = cnn ? 512 : 64, cfg.storage_hidden = Hs, cfg.normalize_obs = cnn ? 0 : 1;
+    cfg.num_epoch = cnn ? 2 : 3, cfg.num_mini_batch = gru ? N : (cnn ? 2 : 4); // recurrent: one environment per minibatch
     cfg.clip_param = 0.2f, cfg.actor_loss_coef = 1.f, cfg.value_loss_coef = 0.5f, cfg.entropy_coef = 0.01f;
     cfg.learning_rate = ppo_algo ? 3e-4f : 7e-4f, cfg.epsilon = 1e-8f, cfg.alpha = 0.99f, cfg.max_grad_norm = 0.5f;
     cfg.kl_target = 1e9f;
@@ -304,37 +312,47 @@ static void test_parity(bool ppo_algo, bool box)
     ref_get_params(ref, params.data());
 
     ActionSpace space{box ? "Box" : "Discrete", {A}};
-    Policy policy(space, std::make_shared<MlpBase>(D, false, 64), true);
+    std::shared_ptr<NNBase> nn_base;
+    if (cnn)
+        nn_base = std::make_shared<CnnBase>(C, false, 512);
+    else
+        nn_base = std::make_shared<MlpBase>(D, gru, 64);
+    Policy policy(space, nn_base, !cnn);
     policy->to(kDev);
     CHECK(policy->flat_parameters().numel() == P);
     policy->flat_parameters().copy_(torch::from_blob(params.data(), {P}).clone());
 
     torch::manual_seed(11);
-    auto obs = torch::randn({T + 1, N, D}), rewards = torch::randn({T, N, 1});
+    auto obs = cnn ? torch::floor(torch::rand({T + 1, N, C, 84, 84}) * 256) : torch::randn({T + 1, N, D});
+    auto rewards = torch::randn({T, N, 1});
     auto masks = (torch::rand({T + 1, N, 1}) < 0.95).to(torch::kFloat);
     masks[0].fill_(1);
-    auto hidden = torch::zeros({T + 1, N, 1}), returns = torch::zeros({T + 1, N, 1}), next_value = torch::randn({N, 1});
+    auto hidden = torch::zeros({T + 1, N, Hs}), returns = torch::zeros({T + 1, N, 1}), next_value = torch::randn({N, 1});
     torch::Tensor actions = box ? torch::randn({T, N, A}) : torch::randint(A, {T, N, 1}, torch::kLong);
     auto values = torch::zeros({T + 1, N, 1}), logp = torch::zeros({T, N, 1});
     {
         auto flat_obs = obs.narrow(0, 0, T).reshape({T * N, D}).contiguous();
-        auto hxs = torch::zeros({T * N, 1}), ones = torch::ones({T * N, 1});
+        (void)D;
+        // recurrent: sequence mode, N initial states and the rollout's masks (nn_base.cpp:57-112)
+        auto hxs = gru ? torch::zeros({N, Hs}) : torch::zeros({T * N, 1});
+        auto ones = gru ? masks.narrow(0, 0, T).reshape({T * N, 1}).contiguous() : torch::ones({T * N, 1});
         auto v = torch::zeros({T * N, 1}), lp = torch::zeros({T * N, 1});
         float ent = 0;
         auto act_flat = actions.reshape({T * N, -1}).contiguous();
-        CHECK(ref_evaluate_actions(ref, flat_obs.data_ptr<float>(), hxs.data_ptr<float>(), T * N, ones.data_ptr<float>(),
+        CHECK(ref_evaluate_actions(ref, flat_obs.data_ptr<float>(), hxs.data_ptr<float>(), hxs.size(0), ones.data_ptr<float>(),
                                    act_flat.data_ptr(), T * N, v.data_ptr<float>(), lp.data_ptr<float>(), &ent) == 0);
         values.narrow(0, 0, T).copy_(v.view({T, N, 1}));
         logp.copy_(lp.view({T, N, 1}));
         // the drop-in's own forward agrees with the reference's on the same weights
-        auto mine = policy->evaluate_actions(flat_obs.to(kDev), torch::Tensor(), torch::Tensor(), act_flat.to(kDev));
-        CHECK(torch::allclose(mine[0].cpu(), v, 1e-4, 1e-5));
-        CHECK(torch::allclose(mine[1].cpu(), lp, 1e-4, 1e-5));
+        auto mine = gru ? policy->evaluate_actions(flat_obs.to(kDev), hxs.to(kDev), ones.to(kDev), act_flat.to(kDev))
+                        : policy->evaluate_actions(flat_obs.to(kDev), torch::Tensor(), torch::Tensor(), act_flat.to(kDev));
+        CHECK(torch::allclose(mine[0].cpu(), v, 1e-4, 2e-5));
+        CHECK(torch::allclose(mine[1].cpu(), lp, 1e-4, 2e-5));
         CHECK(std::fabs(mine[2].item().toFloat() - ent) <= 1e-4 * std::fabs(ent));
     }
     ref_set_rollout(ref, obs.data_ptr<float>(), hidden.data_ptr<float>(), rewards.data_ptr<float>(), values.data_ptr<float>(),
                     returns.data_ptr<float>(), logp.data_ptr<float>(), actions.data_ptr(), masks.data_ptr<float>());
-    RolloutStorage storage(T, N, {D}, space, 1, kDev);
+    RolloutStorage storage(T, N, cnn ? std::vector<int64_t>{C, 84, 84} : std::vector<int64_t>{D}, space, Hs, kDev);
     storage.set_observations(obs.to(kDev));
     storage.set_rewards(rewards.to(kDev));
     storage.set_masks(masks.to(kDev));
@@ -361,7 +379,8 @@ static void test_parity(bool ppo_algo, bool box)
         CHECK(static_cast<int>(got.size()) == n_want);
         for (int i = 0; i < n_want && i < static_cast<int>(got.size()); ++i)
         {
-            const float tol = 1e-4f * std::fabs(want[i]) + 5e-6f;
+            // (CnnBase / GRU: later updates inherit the near-zero-gradient parameter tail of the first, tests/test_cnn_gpu.py)
+            const float tol = ((cnn || gru) && upd > 0 ? 1e-3f : 1e-4f) * std::fabs(want[i]) * (i == 4 && (cnn || gru) ? 10.f : 1.f) + 5e-6f;
             if (std::fabs(got[i].value - want[i]) > tol)
                 std::printf("  stat %s: got %.8g want %.8g\n", got[i].name.c_str(), got[i].value, want[i]);
             CHECK(std::fabs(got[i].value - want[i]) <= tol);
@@ -369,9 +388,14 @@ static void test_parity(bool ppo_algo, bool box)
         ref_get_params(ref, params.data());
         auto mine = policy->flat_parameters().cpu();
         auto want_p = torch::from_blob(params.data(), {P});
-        auto err = ((mine - want_p).abs() / torch::max(want_p.abs(), torch::full({P}, cfg.learning_rate))).max().item().toFloat();
-        std::printf("  update %d: max parameter error relative to max(|ref|, lr) = %.3e\n", upd, err);
-        CHECK(err <= 1e-3f);
+        auto rel = (mine - want_p).abs() / torch::max(want_p.abs(), torch::full({P}, cfg.learning_rate));
+        const float err = rel.max().item().toFloat();
+        const float q99 = std::get<0>(rel.kthvalue(static_cast<int64_t>(0.99 * (P - 1)) + 1)).item().toFloat();
+        std::printf("  update %d: parameter error relative to max(|ref|, lr): max %.3e, 99th percentile %.3e\n", upd, err, q99);
+        // MlpBase: every parameter; CnnBase / GRU: the bulk to 1e-4, the sign-like Adam steps of near-zero gradients bounded
+        CHECK(cnn || gru ? (q99 <= 1e-4f && err <= 0.5f) : err <= 1e-3f);
+        if (cnn)
+            continue; // no observation normaliser on image observations
         float clip, count;
         std::vector<float> mean(D), var(D);
         ref_get_normalizer(ref, &clip, &count, mean.data(), var.data());
@@ -398,6 +422,8 @@ int main()
     test_parity(true, false);
     test_parity(true, true);
     test_parity(false, false);
+    test_parity(true, false, REF_BASE_GRU_MLP);
+    test_parity(true, false, REF_BASE_CNN);
     std::printf("%d checks, %d failed\n", g_checks, g_failed);
     return g_failed == 0 ? 0 : 1;
 }
