@@ -131,31 +131,32 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     constexpr int B_BLOCKS = (BN / 4) * (kBK / 4); // 4x4 blocks of the B tile
     // two tiles of operands in flight per thread (the loads of tiles t+1 and t+2 overlap tile t's MMAs)
     float4 ra2[2][4], rb2[2][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        ra2[0][i] = ra2[1][i] = rb2[0][i] = rb2[1][i] = make_float4(0.f, 0.f, 0.f, 0.f);
     // K-major A: every vector of this thread belongs to the SAME row m0 + (tid & 127): its context is formed once
     const auto a_row = al.row(A_T ? 0 : m0 + (tid & (kBM - 1)));
+    // every load is unconditional (out-of-range elements come from the loaders' zero page): no branches, no zeroing
     auto fetch = [&](int k0, float4 (&ra)[4], float4 (&rb)[4])
     {
 #pragma unroll
         for (int i = 0; i < 4; ++i)
         {
-            ra[i] = rb[i] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (A_T)
             {
                 const int m4 = tid & 31, k4 = tid >> 5; // one 4 (k) x 4 (m) block per thread
-                if (k0 + 4 * k4 + i < k_end)
-                    ra[i] = al.load(al.row(k0 + 4 * k4 + i), m0 + 4 * m4);
+                const int r = k0 + 4 * k4 + i;
+                ra[i] = al.load(al.row(r < k_end ? r : 0x7fffffff), m0 + 4 * m4, r < k_end);
             }
             else
             {
                 const int k4 = (tid >> 7) + 2 * i;
-                if (k0 + 4 * k4 < k_end)
-                    ra[i] = al.load(a_row, k0 + 4 * k4);
+                ra[i] = al.load(a_row, k0 + 4 * k4, k0 + 4 * k4 < k_end);
             }
             if (tid < B_BLOCKS)
             {
                 const int n4 = tid % (BN / 4), k4 = tid / (BN / 4);
-                if (k0 + 4 * k4 + i < k_end)
-                    rb[i] = bl(k0 + 4 * k4 + i, n0 + 4 * n4);
+                rb[i] = bl.at(k0 + 4 * k4 + i, n0 + 4 * n4, k0 + 4 * k4 + i < k_end);
             }
         }
     };

@@ -116,6 +116,14 @@ struct RowCtx
     int a, b;       // loader specific (pixel coordinates for the data-gradient gathers)
 };
 
+// Out-of-range operand elements are read from this zero page: every load is UNCONDITIONAL with a selected address
+// (no branch, no zero-initialised destination registers in the GEMM main loops).
+__device__ __align__(16) float g_zero_page[4];
+__device__ __forceinline__ float4 ld_or_zero(const float *p, bool ok)
+{
+    return __ldg(reinterpret_cast<const float4 *>(ok ? p : g_zero_page));
+}
+
 // im2col of the raw observations for conv1: X[(i, oy, ox)][(c, ky, kx)].  Rows come straight out of the rollout through
 // the minibatch permutation; pixels stay raw 0..255 here, the division by 255 (cnn_base.cpp:37) is applied to the
 // accumulated sums in the epilogues (conv is linear in its input; raw integer pixels are exact in TF32).
@@ -127,18 +135,16 @@ struct ObsIm2col
     int rows, C;
     __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * kCnnP1)
-            return RowCtx{nullptr, 0, 0};
+        const bool ok = r < rows * kCnnP1;
+        r = ok ? r : 0;
         const int i = r / kCnnP1, p = r - i * kCnnP1, oy = p / kCnnO1, ox = p - oy * kCnnO1;
         const long long row = perm ? __ldg(perm + row_base + i) : row_base + i;
-        return RowCtx{obs + row * C * (kCnnIn * kCnnIn) + (4 * oy) * kCnnIn + 4 * ox, 0, 0};
+        return RowCtx{ok ? obs + row * C * (kCnnIn * kCnnIn) + (4 * oy) * kCnnIn + 4 * ox : nullptr, 0, 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
     {
-        if (!ctx.p || k >= C * 64)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
         const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
-        return __ldg(reinterpret_cast<const float4 *>(ctx.p + c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx));
+        return ld_or_zero(ctx.p + c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx, ok && ctx.p && k < C * 64);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -151,17 +157,15 @@ struct ActIm2col
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * OH * OH)
-            return RowCtx{nullptr, 0, 0};
+        const bool ok = r < rows * OH * OH;
+        r = ok ? r : 0;
         const int i = r / (OH * OH), p = r - i * (OH * OH), oy = p / OH, ox = p - oy * OH;
-        return RowCtx{act + (static_cast<size_t>(i) * IH * IH + (S * oy) * IH + S * ox) * CIN, 0, 0};
+        return RowCtx{ok ? act + (static_cast<size_t>(i) * IH * IH + (S * oy) * IH + S * ox) * CIN : nullptr, 0, 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
     {
-        if (!ctx.p || k >= KW * KW * CIN)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
         const int tap = k / CIN, c = k - tap * CIN, ky = tap / KW, kx = tap - ky * KW;
-        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (ky * IH + kx) * CIN + c));
+        return ld_or_zero(ctx.p + (ky * IH + kx) * CIN + c, ok && ctx.p && k < KW * KW * CIN);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -175,13 +179,15 @@ struct MatLoad
     {
         return RowCtx{r < rows ? p + static_cast<size_t>(r) * cols : nullptr, 0, 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int c) const
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int c, bool ok = true) const
     {
-        if (!ctx.p || c >= cols)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(ctx.p + c));
+        return ld_or_zero(ctx.p + c, ok && ctx.p && c < cols);
     }
     __device__ __forceinline__ float4 operator()(int r, int c) const { return load(row(r), c); }
+    __device__ __forceinline__ float4 at(int r, int c, bool ok) const
+    {
+        return ld_or_zero(p + static_cast<size_t>(r) * cols + c, ok && r < rows && c < cols);
+    }
 };
 
 // one matrix per blockIdx.z (conv2 data gradient: one weight slice per input-pixel parity class)
@@ -189,12 +195,11 @@ struct ClassMatLoad
 {
     const float *p;
     int rows, cols;
-    __device__ __forceinline__ float4 operator()(int r, int c) const
+    __device__ __forceinline__ float4 at(int r, int c, bool ok) const
     {
-        if (r >= rows || c >= cols)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(p + (static_cast<size_t>(blockIdx.z) * rows + r) * cols + c));
+        return ld_or_zero(p + (static_cast<size_t>(blockIdx.z) * rows + r) * cols + c, ok && r < rows && c < cols);
     }
+    __device__ __forceinline__ float4 operator()(int r, int c) const { return at(r, c, true); }
 };
 
 // conv3 data gradient: X[(i, y, x) on the 9x9 input][(tap, n)] = dz3[i][y - ky][x - kx][n]
@@ -204,18 +209,19 @@ struct Dgrad3Load
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * kCnnP2)
-            return RowCtx{nullptr, 0, 0};
+        const bool ok = r < rows * kCnnP2;
+        r = ok ? r : 0;
         const int i = r / kCnnP2, p = r - i * kCnnP2, y = p / kCnnO2, x = p - y * kCnnO2;
-        return RowCtx{dz + static_cast<size_t>(i) * kCnnP3 * kCnnC3, y, x};
+        return RowCtx{ok ? dz + static_cast<size_t>(i) * kCnnP3 * kCnnC3 : nullptr, y, x};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
     {
         const int tap = k >> 5, n = k & 31, ky = tap / 3, kx = tap - 3 * ky;
         const int oy = ctx.a - ky, ox = ctx.b - kx;
-        if (!ctx.p || oy < 0 || oy >= kCnnO3 || ox < 0 || ox >= kCnnO3)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (oy * kCnnO3 + ox) * kCnnC3 + n));
+        // (unsigned compare: 0 <= o < 7)
+        ok = ok && ctx.p && static_cast<unsigned>(oy) < static_cast<unsigned>(kCnnO3) &&
+             static_cast<unsigned>(ox) < static_cast<unsigned>(kCnnO3) && tap < 9;
+        return ld_or_zero(ctx.p + (oy * kCnnO3 + ox) * kCnnC3 + n, ok);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -228,17 +234,17 @@ struct Dgrad2Load
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
     {
-        if (r >= rows * 100)
-            return RowCtx{nullptr, 0, 0};
+        const bool ok = r < rows * 100;
+        r = ok ? r : 0;
         const int i = r / 100, p = r - i * 100, py = p / 10, px = p - py * 10;
-        return RowCtx{dz + static_cast<size_t>(i) * kCnnP2 * kCnnC2, py, px};
+        return RowCtx{ok ? dz + static_cast<size_t>(i) * kCnnP2 * kCnnC2 : nullptr, py, px};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
     {
         const int tap = k >> 6, n = k & 63, oy = ctx.a - (tap >> 1), ox = ctx.b - (tap & 1);
-        if (!ctx.p || oy < 0 || oy >= kCnnO2 || ox < 0 || ox >= kCnnO2)
-            return make_float4(0.f, 0.f, 0.f, 0.f);
-        return __ldg(reinterpret_cast<const float4 *>(ctx.p + (oy * kCnnO2 + ox) * kCnnC2 + n));
+        ok = ok && ctx.p && static_cast<unsigned>(oy) < static_cast<unsigned>(kCnnO2) &&
+             static_cast<unsigned>(ox) < static_cast<unsigned>(kCnnO2) && tap < 4;
+        return ld_or_zero(ctx.p + (oy * kCnnO2 + ox) * kCnnC2 + n, ok);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
