@@ -135,8 +135,10 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     for (int i = 0; i < 4; ++i)
         ra2[0][i] = ra2[1][i] = rb2[0][i] = rb2[1][i] = make_float4(0.f, 0.f, 0.f, 0.f);
     // K-major A: every vector of this thread belongs to the SAME row m0 + (tid & 127): its context is formed once
-    const auto a_row = al.row(A_T ? 0 : m0 + (tid & (kBM - 1)));
+    auto a_row = al.row(A_T ? 0 : m0 + (tid & (kBM - 1)));
+    al.clip(a_row, k_end);
     // every load is unconditional (out-of-range elements come from the loaders' zero page): no branches, no zeroing
+    const int b_row_lim = bl.row_limit(n0 + 4 * (tid % (BN / 4)), k_end);
     auto fetch = [&](int k0, float4 (&ra)[4], float4 (&rb)[4])
     {
 #pragma unroll
@@ -146,17 +148,19 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
             {
                 const int m4 = tid & 31, k4 = tid >> 5; // one 4 (k) x 4 (m) block per thread
                 const int r = k0 + 4 * k4 + i;
-                ra[i] = al.load(al.row(r < k_end ? r : 0x7fffffff), m0 + 4 * m4, r < k_end);
+                auto ctx = al.row(r);
+                ctx.lim = r < k_end ? ctx.lim : 0;
+                ra[i] = al.load(ctx, m0 + 4 * m4);
             }
             else
             {
                 const int k4 = (tid >> 7) + 2 * i;
-                ra[i] = al.load(a_row, k0 + 4 * k4, k0 + 4 * k4 < k_end);
+                ra[i] = al.load(a_row, k0 + 4 * k4);
             }
             if (tid < B_BLOCKS)
             {
                 const int n4 = tid % (BN / 4), k4 = tid / (BN / 4);
-                rb[i] = bl.at(k0 + 4 * k4 + i, n0 + 4 * n4, k0 + 4 * k4 + i < k_end);
+                rb[i] = bl.at(k0 + 4 * k4 + i, n0 + 4 * n4, b_row_lim);
             }
         }
     };

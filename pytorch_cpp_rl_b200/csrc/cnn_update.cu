@@ -112,16 +112,20 @@ namespace
 // context is formed once and the k loop only adds offsets.
 struct RowCtx
 {
-    const float *p; // base pointer of the row (null: outside the matrix)
+    const float *p; // base pointer of the row
     int a, b;       // loader specific (pixel coordinates for the data-gradient gathers)
+    int lim;        // columns of this row that exist (0: the row lies outside the matrix); a tap bit mask for the
+                    // data-gradient gathers.  ONE compare per load decides between the element and the zero page.
 };
 
 // Out-of-range operand elements are read from this zero page: every load is UNCONDITIONAL with a selected address
 // (no branch, no zero-initialised destination registers in the GEMM main loops).
 __device__ __align__(16) float g_zero_page[4];
-__device__ __forceinline__ float4 ld_or_zero(const float *p, bool ok)
+// base + unsigned 32-bit element offset (one IMAD.WIDE.U32), one predicate, one pointer select
+__device__ __forceinline__ float4 ld_or_zero(const float *base, int off, bool ok)
 {
-    return __ldg(reinterpret_cast<const float4 *>(ok ? p : g_zero_page));
+    const float *q = base + static_cast<unsigned>(off);
+    return __ldg(reinterpret_cast<const float4 *>(ok ? q : g_zero_page));
 }
 
 // im2col of the raw observations for conv1: X[(i, oy, ox)][(c, ky, kx)].  Rows come straight out of the rollout through
@@ -139,12 +143,13 @@ struct ObsIm2col
         r = ok ? r : 0;
         const int i = r / kCnnP1, p = r - i * kCnnP1, oy = p / kCnnO1, ox = p - oy * kCnnO1;
         const long long row = perm ? __ldg(perm + row_base + i) : row_base + i;
-        return RowCtx{ok ? obs + row * C * (kCnnIn * kCnnIn) + (4 * oy) * kCnnIn + 4 * ox : nullptr, 0, 0};
+        return RowCtx{obs + row * C * (kCnnIn * kCnnIn) + (4 * oy) * kCnnIn + 4 * ox, 0, 0, ok ? C * 64 : 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
+    __device__ __forceinline__ void clip(RowCtx &ctx, int k_end) const { ctx.lim = min(ctx.lim, k_end); }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
     {
         const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
-        return ld_or_zero(ctx.p + c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx, ok && ctx.p && k < C * 64);
+        return ld_or_zero(ctx.p, c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx, k < ctx.lim);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -160,12 +165,13 @@ struct ActIm2col
         const bool ok = r < rows * OH * OH;
         r = ok ? r : 0;
         const int i = r / (OH * OH), p = r - i * (OH * OH), oy = p / OH, ox = p - oy * OH;
-        return RowCtx{ok ? act + (static_cast<size_t>(i) * IH * IH + (S * oy) * IH + S * ox) * CIN : nullptr, 0, 0};
+        return RowCtx{act + (static_cast<size_t>(i) * IH * IH + (S * oy) * IH + S * ox) * CIN, 0, 0, ok ? KW * KW * CIN : 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
+    __device__ __forceinline__ void clip(RowCtx &ctx, int k_end) const { ctx.lim = min(ctx.lim, k_end); }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
     {
         const int tap = k / CIN, c = k - tap * CIN, ky = tap / KW, kx = tap - ky * KW;
-        return ld_or_zero(ctx.p + (ky * IH + kx) * CIN + c, ok && ctx.p && k < KW * KW * CIN);
+        return ld_or_zero(ctx.p, (ky * IH + kx) * CIN + c, k < ctx.lim);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -177,17 +183,15 @@ struct MatLoad
     int rows, cols;
     __device__ __forceinline__ RowCtx row(int r) const
     {
-        return RowCtx{r < rows ? p + static_cast<size_t>(r) * cols : nullptr, 0, 0};
+        const bool ok = r < rows;
+        return RowCtx{p + static_cast<size_t>(ok ? r : 0) * cols, 0, 0, ok ? cols : 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int c, bool ok = true) const
-    {
-        return ld_or_zero(ctx.p + c, ok && ctx.p && c < cols);
-    }
+    __device__ __forceinline__ void clip(RowCtx &ctx, int k_end) const { ctx.lim = min(ctx.lim, k_end); }
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int c) const { return ld_or_zero(ctx.p, c, c < ctx.lim); }
     __device__ __forceinline__ float4 operator()(int r, int c) const { return load(row(r), c); }
-    __device__ __forceinline__ float4 at(int r, int c, bool ok) const
-    {
-        return ld_or_zero(p + static_cast<size_t>(r) * cols + c, ok && r < rows && c < cols);
-    }
+    // B operand: element (r, c) for r < row_lim (the caller folds the column check and the k range into row_lim)
+    __device__ __forceinline__ int row_limit(int c, int k_end) const { return c < cols ? min(rows, k_end) : 0; }
+    __device__ __forceinline__ float4 at(int r, int c, int row_lim) const { return ld_or_zero(p, r * cols + c, r < row_lim); }
 };
 
 // one matrix per blockIdx.z (conv2 data gradient: one weight slice per input-pixel parity class)
@@ -195,14 +199,16 @@ struct ClassMatLoad
 {
     const float *p;
     int rows, cols;
-    __device__ __forceinline__ float4 at(int r, int c, bool ok) const
+    __device__ __forceinline__ int row_limit(int c, int k_end) const { return c < cols ? min(rows, k_end) : 0; }
+    __device__ __forceinline__ float4 at(int r, int c, int row_lim) const
     {
-        return ld_or_zero(p + (static_cast<size_t>(blockIdx.z) * rows + r) * cols + c, ok && r < rows && c < cols);
+        return ld_or_zero(p, (static_cast<int>(blockIdx.z) * rows + r) * cols + c, r < row_lim);
     }
-    __device__ __forceinline__ float4 operator()(int r, int c) const { return at(r, c, true); }
+    __device__ __forceinline__ float4 operator()(int r, int c) const { return at(r, c, row_limit(c, rows)); }
 };
 
-// conv3 data gradient: X[(i, y, x) on the 9x9 input][(tap, n)] = dz3[i][y - ky][x - kx][n]
+// conv3 data gradient: X[(i, y, x) on the 9x9 input][(tap, n)] = dz3[i][y - ky][x - kx][n]; ctx.lim = mask of the taps
+// (ky, kx) whose output pixel (y - ky, x - kx) exists.  (No k split with the mask loaders: K = taps * channels.)
 struct Dgrad3Load
 {
     const float *dz;
@@ -212,16 +218,20 @@ struct Dgrad3Load
         const bool ok = r < rows * kCnnP2;
         r = ok ? r : 0;
         const int i = r / kCnnP2, p = r - i * kCnnP2, y = p / kCnnO2, x = p - y * kCnnO2;
-        return RowCtx{ok ? dz + static_cast<size_t>(i) * kCnnP3 * kCnnC3 : nullptr, y, x};
+        int mask = 0;
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap)
+        {
+            const int oy = y - tap / 3, ox = x - tap % 3;
+            mask |= (oy >= 0 && oy < kCnnO3 && ox >= 0 && ox < kCnnO3) ? (1 << tap) : 0;
+        }
+        return RowCtx{dz + static_cast<size_t>(i) * kCnnP3 * kCnnC3, y, x, ok ? mask : 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
+    __device__ __forceinline__ void clip(RowCtx &, int) const {}
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
     {
         const int tap = k >> 5, n = k & 31, ky = tap / 3, kx = tap - 3 * ky;
-        const int oy = ctx.a - ky, ox = ctx.b - kx;
-        // (unsigned compare: 0 <= o < 7)
-        ok = ok && ctx.p && static_cast<unsigned>(oy) < static_cast<unsigned>(kCnnO3) &&
-             static_cast<unsigned>(ox) < static_cast<unsigned>(kCnnO3) && tap < 9;
-        return ld_or_zero(ctx.p + (oy * kCnnO3 + ox) * kCnnC3 + n, ok);
+        return ld_or_zero(ctx.p, ((ctx.a - ky) * kCnnO3 + (ctx.b - kx)) * kCnnC3 + n, (ctx.lim >> tap) & 1);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
@@ -237,14 +247,20 @@ struct Dgrad2Load
         const bool ok = r < rows * 100;
         r = ok ? r : 0;
         const int i = r / 100, p = r - i * 100, py = p / 10, px = p - py * 10;
-        return RowCtx{ok ? dz + static_cast<size_t>(i) * kCnnP2 * kCnnC2 : nullptr, py, px};
+        int mask = 0;
+#pragma unroll
+        for (int tap = 0; tap < 4; ++tap)
+        {
+            const int oy = py - (tap >> 1), ox = px - (tap & 1);
+            mask |= (oy >= 0 && oy < kCnnO2 && ox >= 0 && ox < kCnnO2) ? (1 << tap) : 0;
+        }
+        return RowCtx{dz + static_cast<size_t>(i) * kCnnP2 * kCnnC2, py, px, ok ? mask : 0};
     }
-    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k, bool ok = true) const
+    __device__ __forceinline__ void clip(RowCtx &, int) const {}
+    __device__ __forceinline__ float4 load(const RowCtx &ctx, int k) const
     {
-        const int tap = k >> 6, n = k & 63, oy = ctx.a - (tap >> 1), ox = ctx.b - (tap & 1);
-        ok = ok && ctx.p && static_cast<unsigned>(oy) < static_cast<unsigned>(kCnnO2) &&
-             static_cast<unsigned>(ox) < static_cast<unsigned>(kCnnO2) && tap < 4;
-        return ld_or_zero(ctx.p + (oy * kCnnO2 + ox) * kCnnC2 + n, ok);
+        const int tap = k >> 6, n = k & 63;
+        return ld_or_zero(ctx.p, ((ctx.a - (tap >> 1)) * kCnnO2 + (ctx.b - (tap & 1))) * kCnnC2 + n, (ctx.lim >> tap) & 1);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
