@@ -82,8 +82,12 @@ __device__ __forceinline__ void split_tf32(const float4 &x, float4 &hi, float4 &
 // with the 8-row groups 144 bytes apart (128 + 16 padding: the descriptor's stride byte offset is free, and the
 // padding makes the transposing 16-byte stores below conflict-free) and the k chunks (rows / 8) * 144 bytes apart.
 constexpr int kGroupBytes = 144;
+// The A operand's k chunks are a further 16 bytes apart (leading byte offset 16 * 144 + 16): eight lanes that store the
+// eight k chunks of ONE row (the lanes-along-k gather below) then fall into eight different 16-byte bank groups.
 __host__ __device__ constexpr int operand_bytes(int rows) { return (kBK / 4) * (rows / 8) * kGroupBytes; }
-__host__ __device__ constexpr size_t smem_bytes(int BN) { return static_cast<size_t>(2) * 2 * (operand_bytes(kBM) + operand_bytes(BN)) + 64; }
+__host__ __device__ constexpr int a_lbo_bytes() { return (kBM / 8) * kGroupBytes + 16; }
+__host__ __device__ constexpr int a_operand_bytes() { return (kBK / 4) * a_lbo_bytes(); }
+__host__ __device__ constexpr size_t smem_bytes(int BN) { return static_cast<size_t>(2) * 2 * (a_operand_bytes() + operand_bytes(BN)) + 64; }
 
 // A_T: A(m, k) = X[k][m] (the loader's vectors run along m: transposed on the way into shared memory); else
 // A(m, k) = X[m][k] (vectors along k).  B(k, n) = Y[k][n] always (vectors along n, transposed likewise).
@@ -95,8 +99,13 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     extern __shared__ __align__(128) unsigned char tc_smem[];
     if (stop_flag && *stop_flag)
         return;
-    constexpr int A_BYTES = operand_bytes(kBM), B_BYTES = operand_bytes(BN), STAGE_BYTES = 2 * (A_BYTES + B_BYTES);
-    constexpr uint32_t A_LBO = (kBM / 8) * kGroupBytes, B_LBO = (BN / 8) * kGroupBytes;
+    constexpr int A_BYTES = a_operand_bytes(), B_BYTES = operand_bytes(BN), STAGE_BYTES = 2 * (A_BYTES + B_BYTES);
+    constexpr uint32_t A_LBO = a_lbo_bytes(), B_LBO = (BN / 8) * kGroupBytes;
+    // K-major sources whose rows are contiguous in memory (activations, plain matrices) are gathered with the LANES
+    // ALONG K: eight lanes read the 128 contiguous bytes one row contributes to a k tile, a warp request touches 4
+    // lines instead of 32 (the L1 wavefront count had been the limiter of those kernels).  The thread then owns the
+    // same k chunk of four rows (four row contexts).  conv1's NCHW gather keeps lanes along the output pixels.
+    constexpr bool ALONG_K = !A_T && ALoad::kLanesAlongK;
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tc_smem + 2 * STAGE_BYTES);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(mbar + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -137,6 +146,13 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     // K-major A: every vector of this thread belongs to the SAME row m0 + (tid & 127): its context is formed once
     auto a_row = al.row(A_T ? 0 : m0 + (tid & (kBM - 1)));
     al.clip(a_row, k_end);
+    decltype(a_row) a_rows[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+        a_rows[i] = al.row(ALONG_K ? m0 + (tid >> 3) + 32 * i : 0);
+        al.clip(a_rows[i], k_end);
+    }
     // every load is unconditional (out-of-range elements come from the loaders' zero page): no branches, no zeroing
     const int b_row_lim = bl.row_limit(n0 + 4 * (tid % (BN / 4)), k_end);
     auto fetch = [&](int k0, float4 (&ra)[4], float4 (&rb)[4])
@@ -152,6 +168,8 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
                 ctx.lim = r < k_end ? ctx.lim : 0;
                 ra[i] = al.load(ctx, m0 + 4 * m4);
             }
+            else if (ALONG_K)
+                ra[i] = al.load(a_rows[i], k0 + 4 * (tid & 7));
             else
             {
                 const int k4 = (tid >> 7) + 2 * i;
@@ -187,7 +205,8 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
 #pragma unroll
             for (int i = 0; i < 4; ++i)
             {
-                const int idx = tid + i * kThreads, mm = idx & (kBM - 1), k4 = idx >> 7;
+                const int idx = tid + i * kThreads;
+                const int mm = ALONG_K ? idx >> 3 : idx & (kBM - 1), k4 = ALONG_K ? idx & 7 : idx >> 7;
                 store_split(a_hi, a_lo, slot(k4, mm, A_LBO), ra[i]);
             }
         }

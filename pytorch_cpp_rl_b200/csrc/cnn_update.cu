@@ -133,6 +133,8 @@ __device__ __forceinline__ float4 ld_or_zero(const float *base, int off, bool ok
 // accumulated sums in the epilogues (conv is linear in its input; raw integer pixels are exact in TF32).
 struct ObsIm2col
 {
+    static constexpr bool kLanesAlongK = false; // see cnn_gemm_tc.cuh
+
     const float *obs;
     const long long *perm;
     long long row_base;
@@ -158,6 +160,8 @@ struct ObsIm2col
 template <int IH, int OH, int KW, int S, int CIN>
 struct ActIm2col
 {
+    static constexpr bool kLanesAlongK = true; // see cnn_gemm_tc.cuh
+
     const float *act;
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
@@ -179,6 +183,8 @@ struct ActIm2col
 // plain row-major matrix [rows][cols]
 struct MatLoad
 {
+    static constexpr bool kLanesAlongK = true; // see cnn_gemm_tc.cuh
+
     const float *p;
     int rows, cols;
     __device__ __forceinline__ RowCtx row(int r) const
@@ -211,6 +217,8 @@ struct ClassMatLoad
 // (ky, kx) whose output pixel (y - ky, x - kx) exists.  (No k split with the mask loaders: K = taps * channels.)
 struct Dgrad3Load
 {
+    static constexpr bool kLanesAlongK = true; // see cnn_gemm_tc.cuh
+
     const float *dz;
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
@@ -240,6 +248,8 @@ struct Dgrad3Load
 // only the taps ky = cy + 2a, kx = cx + 2b reach them: X[(i, py, px)][(a, b, n)] = dz2[i][py - a][px - b][n]
 struct Dgrad2Load
 {
+    static constexpr bool kLanesAlongK = true; // see cnn_gemm_tc.cuh
+
     const float *dz;
     int rows;
     __device__ __forceinline__ RowCtx row(int r) const
