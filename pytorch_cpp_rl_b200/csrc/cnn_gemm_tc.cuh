@@ -316,19 +316,26 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         drain_chunk(last >> 1); // the last chunk (one or two tiles)
     }
 
-    // ---- epilogue: registers -> epi -------------------------------------------------------------------------------------------
+    // ---- epilogue: registers -> shared memory (transpose) -> epi ------------------------------------------------------------
+    // TMEM hands every thread ONE ROW of the tile; stored from there a warp request would touch 32 lines (16 bytes of
+    // each).  The tile goes through the (now idle: every MMA has completed) stage memory instead and is read back with
+    // the lanes along n, so that the epilogue's global loads / stores / atomics cover whole lines.
     if (n_tiles > 0)
     {
-        const int m = m0 + 32 * q + lane;
-        if (m < M)
-        {
+        float *tile = reinterpret_cast<float *>(tc_smem);
+        constexpr int LD = BN + 4; // row stride 16 bytes off a multiple of 128: conflict-free 16-byte stores per row
+        const int row = 32 * q + lane;
 #pragma unroll
-            for (int c = 0; c < BN / 2; c += 4)
-            {
-                const int n = n0 + half * (BN / 2) + c;
-                if (n < N)
-                    epi(m, n, make_float4(racc[c], racc[c + 1], racc[c + 2], racc[c + 3]));
-            }
+        for (int c = 0; c < BN / 2; c += 4)
+            *reinterpret_cast<float4 *>(tile + row * LD + half * (BN / 2) + c) = make_float4(racc[c], racc[c + 1], racc[c + 2], racc[c + 3]);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < BN / 8; ++j)
+        {
+            const int v = tid + j * kThreads, r = v / (BN / 4), c4 = v % (BN / 4);
+            const int m = m0 + r, n = n0 + 4 * c4;
+            if (m < M && n < N)
+                epi(m, n, *reinterpret_cast<const float4 *>(tile + r * LD + 4 * c4));
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
