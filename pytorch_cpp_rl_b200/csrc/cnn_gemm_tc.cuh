@@ -100,7 +100,11 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     if (stop_flag && *stop_flag)
         return;
     constexpr int A_BYTES = a_operand_bytes(), B_BYTES = operand_bytes(BN), STAGE_BYTES = 2 * (A_BYTES + B_BYTES);
-    constexpr uint32_t A_LBO = a_lbo_bytes(), B_LBO = (BN / 8) * kGroupBytes;
+    // B holds its hi and lo planes as ONE operand of 2 BN rows (hi rows [0, BN), lo rows [BN, 2 BN)): A_hi x [B_hi; B_lo]
+    // is a single N = 2 BN instruction whose two column halves are hi*hi and hi*lo, so a k-step is TWO instructions
+    // (the second, A_lo x B_hi with N = BN, adds into the first half) and A — the 4 KB operand whose shared-memory
+    // reads bound these small-N MMAs — is read twice instead of three times.
+    constexpr uint32_t A_LBO = a_lbo_bytes(), B_LBO = (2 * BN / 8) * kGroupBytes;
     // K-major sources whose rows are contiguous in memory (activations, plain matrices) are gathered with the LANES
     // ALONG K: eight lanes read the 128 contiguous bytes one row contributes to a k tile, a warp request touches 4
     // lines instead of 32 (the L1 wavefront count had been the limiter of those kernels).  The thread then owns the
@@ -113,7 +117,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     const int k_begin = z_is_k_split ? blockIdx.z * k_slice : 0, k_end = min(K, k_begin + k_slice);
 
     // ---- TMEM allocation (one warp), barriers ----------------------------------------------------------------------
-    constexpr uint32_t TMEM_COLS = 2 * BN; // two accumulators: see the chunked accumulation below
+    constexpr uint32_t TMEM_COLS = 4 * BN; // two accumulators of 2 BN columns: see the chunked accumulation below
     if (warp == 0)
     {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "r"(TMEM_COLS)
@@ -134,6 +138,8 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     // instruction descriptor: D = F32 (bits 4-5), A = B = TF32 (bits 7-9, 10-12), both K-major, N >> 3, M >> 4
     constexpr uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
                                (static_cast<uint32_t>(kBM >> 4) << 24);
+    constexpr uint32_t idesc2 = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>((2 * BN) >> 3) << 17) |
+                                (static_cast<uint32_t>(kBM >> 4) << 24);
 
     // byte offset of the 16-byte slot (k chunk k4, row r) inside an operand
     auto slot = [](int k4, int r, uint32_t lbo) { return k4 * lbo + (r >> 3) * kGroupBytes + (r & 7) * 16; };
@@ -191,7 +197,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     };
     auto stash = [&](int s, const float4 (&ra)[4], const float4 (&rb)[4])
     {
-        unsigned char *a_hi = tc_smem + s * STAGE_BYTES, *a_lo = a_hi + A_BYTES, *b_hi = a_lo + A_BYTES, *b_lo = b_hi + B_BYTES;
+        unsigned char *a_hi = tc_smem + s * STAGE_BYTES, *a_lo = a_hi + A_BYTES, *b_hi = a_lo + A_BYTES, *b_lo = b_hi + (BN / 8) * kGroupBytes;
         if (A_T)
         {
             const int m4 = tid & 31, k4 = tid >> 5;
@@ -221,15 +227,14 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     };
     auto issue = [&](int s, uint32_t acc, bool first_tile)
     {
-        const uint32_t a_hi = smem_addr(tc_smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES, b_hi = a_lo + A_BYTES, b_lo = b_hi + B_BYTES;
+        const uint32_t a_hi = smem_addr(tc_smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES, b_all = a_lo + A_BYTES;
 #pragma unroll
         for (int j = 0; j < kBK / 8; ++j) // one MMA k-step = 8 tf32 = two 16-byte k chunks
         {
             const uint64_t dah = make_desc(a_hi + j * 2 * A_LBO, A_LBO, kGroupBytes), dal = make_desc(a_lo + j * 2 * A_LBO, A_LBO, kGroupBytes);
-            const uint64_t dbh = make_desc(b_hi + j * 2 * B_LBO, B_LBO, kGroupBytes), dbl = make_desc(b_lo + j * 2 * B_LBO, B_LBO, kGroupBytes);
-            mma_tf32(acc, dah, dbh, idesc, (first_tile && j == 0) ? 0u : 1u);
-            mma_tf32(acc, dah, dbl, idesc, 1u);
-            mma_tf32(acc, dal, dbh, idesc, 1u);
+            const uint64_t db = make_desc(b_all + j * 2 * B_LBO, B_LBO, kGroupBytes);
+            mma_tf32(acc, dah, db, idesc2, (first_tile && j == 0) ? 0u : 1u); // [hi*hi | hi*lo]
+            mma_tf32(acc, dal, db, idesc, 1u);                                // lo*hi into the first half
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(&mbar[s]))
                      : "memory");
@@ -248,18 +253,21 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         racc[c] = 0.f;
     auto drain_chunk = [&](int chunk)
     {
-        const uint32_t base = tmem_acc + (chunk & 1) * BN + (static_cast<uint32_t>(32 * q) << 16) + half * (BN / 2);
+        const uint32_t base = tmem_acc + (chunk & 1) * 2 * BN + (static_cast<uint32_t>(32 * q) << 16) + half * (BN / 2);
 #pragma unroll
         for (int c = 0; c < BN / 2; c += 8)
         {
-            uint32_t r[8];
+            uint32_t r[8], r2[8];
             asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
                          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
                          : "r"(base + c));
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                         : "=r"(r2[0]), "=r"(r2[1]), "=r"(r2[2]), "=r"(r2[3]), "=r"(r2[4]), "=r"(r2[5]), "=r"(r2[6]), "=r"(r2[7])
+                         : "r"(base + BN + c));
             asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
             for (int i = 0; i < 8; ++i)
-                racc[c + i] += __uint_as_float(r[i]);
+                racc[c + i] += __uint_as_float(r[i]) + __uint_as_float(r2[i]); // (hi*hi + lo*hi) + hi*lo
         }
     };
     uint32_t phase[2] = {0u, 0u};
@@ -290,7 +298,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         if (tid == 0)
         {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            issue(s, tmem_acc + ((t >> 1) & 1) * BN, s == 0);
+            issue(s, tmem_acc + ((t >> 1) & 1) * 2 * BN, s == 0);
         }
     };
     for (int t = 0; t < n_tiles; t += 2)
