@@ -48,6 +48,24 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_c, uint64_t desc_a, uint6
         : "memory");
 }
 
+// the same MMA with the descriptors given as 32-bit halves: the high word {stride byte offset, version} is common to
+// all operands, the low word {start address >> 4, leading byte offset} is a loop-invariant base plus a constant
+__device__ __forceinline__ void mma_tf32_halves(uint32_t tmem_c, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                                uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        ".reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, {%6, %6, %6, %6}, p;\n\t"
+        "}\n" ::"r"(tmem_c),
+        "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+
 __device__ __forceinline__ void mbar_init(void *bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
@@ -225,16 +243,19 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
             store_split(b_hi, b_lo, slot(k4, 4 * n4 + 3, B_LBO), make_float4(rb[0].w, rb[1].w, rb[2].w, rb[3].w));
         }
     };
+    // descriptor halves (make_desc): smem addresses stay below 2^18, so base + constant never carries out of the
+    // 14-bit start-address field; s is a literal at both call sites, every offset below folds into one add
+    const uint32_t smem0 = smem_addr(tc_smem) >> 4;
+    const uint32_t a_desc_lo = smem0 | ((A_LBO >> 4) << 16), b_desc_lo = smem0 | ((B_LBO >> 4) << 16);
+    constexpr uint32_t desc_hi = (kGroupBytes >> 4) | (1u << 14);
     auto issue = [&](int s, uint32_t acc, bool first_tile)
     {
-        const uint32_t a_hi = smem_addr(tc_smem + s * STAGE_BYTES), a_lo = a_hi + A_BYTES, b_all = a_lo + A_BYTES;
 #pragma unroll
         for (int j = 0; j < kBK / 8; ++j) // one MMA k-step = 8 tf32 = two 16-byte k chunks
         {
-            const uint64_t dah = make_desc(a_hi + j * 2 * A_LBO, A_LBO, kGroupBytes), dal = make_desc(a_lo + j * 2 * A_LBO, A_LBO, kGroupBytes);
-            const uint64_t db = make_desc(b_all + j * 2 * B_LBO, B_LBO, kGroupBytes);
-            mma_tf32(acc, dah, db, idesc2, (first_tile && j == 0) ? 0u : 1u); // [hi*hi | hi*lo]
-            mma_tf32(acc, dal, db, idesc, 1u);                                // lo*hi into the first half
+            const uint32_t a_off = (s * STAGE_BYTES + j * 2 * A_LBO) >> 4, b_off = (s * STAGE_BYTES + 2 * A_BYTES + j * 2 * B_LBO) >> 4;
+            mma_tf32_halves(acc, a_desc_lo + a_off, b_desc_lo + b_off, desc_hi, idesc2, (first_tile && j == 0) ? 0u : 1u); // [hi*hi | hi*lo]
+            mma_tf32_halves(acc, a_desc_lo + a_off + (A_BYTES >> 4), b_desc_lo + b_off, desc_hi, idesc, 1u); // lo*hi into the first half
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(&mbar[s]))
                      : "memory");
@@ -275,9 +296,8 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         fetch(k_begin, ra2[0], rb2[0]);
     if (n_tiles > 1)
         fetch(k_begin + kBK, ra2[1], rb2[1]);
-    auto tile_step = [&](int t, float4 (&ra)[4], float4 (&rb)[4])
+    auto tile_step = [&](int t, const int s, float4 (&ra)[4], float4 (&rb)[4]) // s = t & 1, a literal at the call sites
     {
-        const int s = t & 1;
         if (t >= 2)
         {
             mbar_wait(&mbar[s], phase[s]); // the MMAs of tile t-2 (which read this stage) are done
@@ -303,9 +323,9 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     };
     for (int t = 0; t < n_tiles; t += 2)
     {
-        tile_step(t, ra2[0], rb2[0]);
+        tile_step(t, 0, ra2[0], rb2[0]);
         if (t + 1 < n_tiles)
-            tile_step(t + 1, ra2[1], rb2[1]);
+            tile_step(t + 1, 1, ra2[1], rb2[1]);
     }
     // drain: chunks whose closing tile has not been waited for yet
     if (n_tiles >= 1)
