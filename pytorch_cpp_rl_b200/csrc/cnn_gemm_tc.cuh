@@ -179,8 +179,15 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     }
     // every load is unconditional (out-of-range elements come from the loaders' zero page): no branches, no zeroing
     const int b_row_lim = bl.row_limit(n0 + 4 * (tid % (BN / 4)), k_end);
+    // element offsets = per-thread column part (formed once) + per-tile part (uniform over the CTA)
+    int a_col[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        a_col[i] = al.col_part(ALONG_K ? 4 * (tid & 7) : 4 * ((tid >> 7) + 2 * i));
     auto fetch = [&](int k0, float4 (&ra)[4], float4 (&rb)[4])
     {
+        const int a_tile = al.tile_part(k0);
+        (void)a_tile;
 #pragma unroll
         for (int i = 0; i < 4; ++i)
         {
@@ -193,12 +200,9 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
                 ra[i] = al.load(ctx, m0 + 4 * m4);
             }
             else if (ALONG_K)
-                ra[i] = al.load(a_rows[i], k0 + 4 * (tid & 7));
+                ra[i] = al.load_parts(a_rows[i], a_col[0] + a_tile, k0 + 4 * (tid & 7));
             else
-            {
-                const int k4 = (tid >> 7) + 2 * i;
-                ra[i] = al.load(a_row, k0 + 4 * k4);
-            }
+                ra[i] = al.load_parts(a_row, a_col[i] + a_tile, k0 + 4 * ((tid >> 7) + 2 * i));
             if (tid < B_BLOCKS)
             {
                 const int n4 = tid % (BN / 4), k4 = tid / (BN / 4);

@@ -153,6 +153,11 @@ struct ObsIm2col
         const int c = k >> 6, ky = (k >> 3) & 7, kx = k & 7;
         return ld_or_zero(ctx.p, c * (kCnnIn * kCnnIn) + ky * kCnnIn + kx, k < ctx.lim);
     }
+    // the same offset split into a per-thread constant (column kc of a 32-column k tile) and a per-tile part (tile
+    // base k0, a multiple of 32: uniform over the CTA): 64 columns per channel, so no carry between the two
+    __device__ __forceinline__ int col_part(int kc) const { return (kc >> 3) * kCnnIn + (kc & 7); }
+    __device__ __forceinline__ int tile_part(int k0) const { return (k0 >> 6) * (kCnnIn * kCnnIn) + ((k0 & 32) >> 3) * kCnnIn; }
+    __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const { return ld_or_zero(ctx.p, part, k < ctx.lim); }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
@@ -177,6 +182,14 @@ struct ActIm2col
         const int tap = k / CIN, c = k - tap * CIN, ky = tap / KW, kx = tap - ky * KW;
         return ld_or_zero(ctx.p, (ky * IH + kx) * CIN + c, k < ctx.lim);
     }
+    static_assert(CIN == 32 || CIN == 64, "a 32-column k tile lies inside one tap");
+    __device__ __forceinline__ int col_part(int kc) const { return kc; }
+    __device__ __forceinline__ int tile_part(int k0) const
+    {
+        const int tap = k0 / CIN, ky = tap / KW, kx = tap - ky * KW;
+        return (ky * IH + kx) * CIN + (k0 - tap * CIN);
+    }
+    __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const { return ld_or_zero(ctx.p, part, k < ctx.lim); }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
@@ -194,6 +207,9 @@ struct MatLoad
     }
     __device__ __forceinline__ void clip(RowCtx &ctx, int k_end) const { ctx.lim = min(ctx.lim, k_end); }
     __device__ __forceinline__ float4 load(const RowCtx &ctx, int c) const { return ld_or_zero(ctx.p, c, c < ctx.lim); }
+    __device__ __forceinline__ int col_part(int kc) const { return kc; }
+    __device__ __forceinline__ int tile_part(int k0) const { return k0; }
+    __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const { return ld_or_zero(ctx.p, part, k < ctx.lim); }
     __device__ __forceinline__ float4 operator()(int r, int c) const { return load(row(r), c); }
     // B operand: element (r, c) for r < row_lim (the caller folds the column check and the k range into row_lim)
     __device__ __forceinline__ int row_limit(int c, int k_end) const { return c < cols ? min(rows, k_end) : 0; }
@@ -241,6 +257,17 @@ struct Dgrad3Load
         const int tap = k >> 5, n = k & 31, ky = tap / 3, kx = tap - 3 * ky;
         return ld_or_zero(ctx.p, ((ctx.a - ky) * kCnnO3 + (ctx.b - kx)) * kCnnC3 + n, (ctx.lim >> tap) & 1);
     }
+    // parts: the row's own pixel offset (y * 7 + x) * 32 is added on the fly (two's complement: the sum is exact)
+    __device__ __forceinline__ int col_part(int kc) const { return kc; }
+    __device__ __forceinline__ int tile_part(int k0) const
+    {
+        const int tap = k0 >> 5, ky = tap / 3, kx = tap - 3 * ky;
+        return -(ky * kCnnO3 + kx) * kCnnC3;
+    }
+    __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const
+    {
+        return ld_or_zero(ctx.p, (ctx.a * kCnnO3 + ctx.b) * kCnnC3 + part, (ctx.lim >> (k >> 5)) & 1);
+    }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
 
@@ -271,6 +298,16 @@ struct Dgrad2Load
     {
         const int tap = k >> 6, n = k & 63;
         return ld_or_zero(ctx.p, ((ctx.a - (tap >> 1)) * kCnnO2 + (ctx.b - (tap & 1))) * kCnnC2 + n, (ctx.lim >> tap) & 1);
+    }
+    __device__ __forceinline__ int col_part(int kc) const { return kc; }
+    __device__ __forceinline__ int tile_part(int k0) const
+    {
+        const int tap = k0 >> 6;
+        return -((tap >> 1) * kCnnO2 + (tap & 1)) * kCnnC2 + (k0 & 32);
+    }
+    __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const
+    {
+        return ld_or_zero(ctx.p, (ctx.a * kCnnO2 + ctx.b) * kCnnC2 + part, (ctx.lim >> (k >> 6)) & 1);
     }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
 };
