@@ -431,6 +431,10 @@ def main():
         run_reference(args, w, rank, world)
     else:
         run_ours(args, w, rank, local_rank, world)
+        if world > 1:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -786,13 +786,14 @@ static int ppo_shard_permutation(cpprl_b200_ppo *h, const int64_t *d_perm)
         CPPRL_CUDA_TRY(cudaMalloc(&h->d_lperm, need * sizeof(int64_t)));
         h->lperm_cap = need;
     }
-    if (static_cast<size_t>(h->n_mb) > h->counts_cap)
+    // n_mb totals + up to 64 piece counts per minibatch (comm.cu)
+    if (static_cast<size_t>(h->n_mb) * 65 > h->counts_cap)
     {
         CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
         cudaFree(h->d_counts);
         h->d_counts = nullptr;
-        CPPRL_CUDA_TRY(cudaMalloc(&h->d_counts, h->n_mb * sizeof(int)));
-        h->counts_cap = h->n_mb;
+        CPPRL_CUDA_TRY(cudaMalloc(&h->d_counts, h->n_mb * 65 * sizeof(int)));
+        h->counts_cap = h->n_mb * 65;
     }
     return launch_shard_permutation(d_perm, h->n_mb, h->mbs, h->global_envs, h->env_offset, h->rollout.N, h->d_lperm,
                                     h->d_counts, h->stream);

@@ -32,6 +32,10 @@ def shard(r, lo, hi):
 
 def run_case(w, seed, rank, world, n_updates=2):
     from oracle import ref_binding as ref
+    if w.N < world:  # every rank needs at least one environment
+        if rank == 0:
+            print(f"[dist] {w.name} {w.algo}: skipped, {w.N} environments < world={world}", flush=True)
+        return True
     r = synth_rollout(w, seed)
     sess = H.make_ref_session(ref, w, init_seed=seed)          # every rank computes the same reference (CPU)
     H.fill_policy_outputs(sess, w, r)
