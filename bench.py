@@ -210,7 +210,7 @@ class GpuSide:
                 self.algo.set_communicator(self.comm, world * w.N)
         self.e2e_calls = 0
         self.h2d_bytes = sum(t.numel() * t.element_size() for t in self.pinned.values()) + self.pinned_nv.numel() * 4
-        if w.algo == "ppo":
+        if w.algo == "ppo" and world == 1:  # (sharded updates draw the global permutations on the device)
             self.h2d_bytes += w.num_epoch * self.perm_len * 8
         self.d2h_bytes = 64
 

@@ -439,6 +439,7 @@ class PPO:
         else:
             n = N if self.policy.is_recurrent() else T * (getattr(self, "_global_envs", 0) or N)
             can_stop = self.kl_target * 1.5 < 1e3  # a mean log-prob difference cannot reach this: no stop possible
+            keep = []
             check(lib.cpprl_b200_ppo_begin(self._h, C.byref(pd), C.byref(rd), C.byref(od), _stream()))
             for epoch in range(self.num_epoch):
                 if can_stop and epoch > 0:
@@ -446,9 +447,20 @@ class PPO:
                     check(lib.cpprl_b200_ppo_stopped(self._h, C.byref(stopped)))
                     if stopped.value:
                         break
-                perm = torch.randperm(n, dtype=torch.int64)
-                check(lib.cpprl_b200_ppo_epoch(self._h, C.c_void_p(perm.data_ptr()), n))
+                if getattr(self, "_comm", None) is not None:
+                    # env-sharded: the permutation is over the GLOBAL rollout (T * global_envs ids, identical on every
+                    # rank).  Drawing it on the host costs every rank tens of ms per epoch and does not shrink with
+                    # the number of GPUs, so it comes from the CUDA generator instead: identically seeded ranks
+                    # (torch.manual_seed) on identical GPUs draw identical permutations.  (The reference has no
+                    # distributed path whose CPU random stream this could be compared with.)
+                    perm = torch.randperm(n, dtype=torch.int64, device=self.policy.params.device)
+                    keep.append(perm)
+                    check(lib.cpprl_b200_ppo_epoch_device(self._h, _ptr(perm), n))
+                else:
+                    perm = torch.randperm(n, dtype=torch.int64)
+                    check(lib.cpprl_b200_ppo_epoch(self._h, C.c_void_p(perm.data_ptr()), n))
             check(lib.cpprl_b200_ppo_end(self._h, C.byref(stats)))
+            keep.clear()
         if return_stats:
             return stats
         data = [UpdateDatum("Value loss", stats.value_loss), UpdateDatum("Action loss", stats.action_loss),
