@@ -201,7 +201,7 @@ class GpuSide:
         else:
             self.algo = api.A2C(self.policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
         self.comm = None
-        if world > 1:
+        if world > 1 and not gru:  # recurrent path: replicas only (one environment per minibatch: nothing to shard)
             # environments sharded over the GPUs of the box; gradient all-reduce inside the fused kernel (NVLink)
             self.comm = api.Communicator(self.policy.params.numel())
             if w.algo == "ppo":
@@ -402,6 +402,7 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "config": {"workload": f"{w.name}: {w.description}", "rows_per_step": w.rows, "optimizer_steps": w.optimizer_steps,
                    "l2": "flushed between timed iterations (256 MiB write)",
                    "parallelism": "single GPU" if world == 1 else
+                   f"{world} independent replicas (the recurrent path does not shard: SURVEY 8e)" if w.base == "gru" else
                    f"dp{world}: {world * w.N} envs sharded by environment over {world} GPUs ({w.N} per GPU), global "
                    f"minibatch {world * w.rows // max(1, w.num_mini_batch)} rows, gradient all-reduce "
                    + ("kernel between backward and optimiser" if w.base == "cnn" else "inside the fused kernel") +
