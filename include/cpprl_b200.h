@@ -171,6 +171,17 @@ int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_
                                 float *d_value, float *d_logp, float *d_entropy, float *d_hxs_out,
                                 void *stream);
 
+/* replaces PolicyImpl::act, src/model/policy.cpp:52-81: forward + Distribution::sample + log_prob on B rows (arguments
+ * as evaluate_actions).  Categorical::sample (src/distributions/categorical.cpp:63-80, torch::multinomial) becomes
+ * the inverse CDF of one Philox uniform per row, Normal::sample (src/distributions/normal.cpp:39-44) loc + scale * z;
+ * the generator is Philox4x32-10 keyed by (seed, row) at `offset`, so (seed, offset) reproduces the actions.
+ * Outputs: value [B], actions int64 [B] or fp32 [B,A], logp [B] (summed over A for Normal), hxs_out (recurrent).
+ * Parity with the reference is distributional (it consumes the CPU mt19937 stream); value and logp agree with
+ * evaluate_actions on the sampled actions. */
+int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                   const float *d_masks, int64_t B, uint64_t seed, uint64_t offset, float *d_value, void *d_actions,
+                   float *d_logp, float *d_hxs_out, void *stream);
+
 /* ---- (c)+(d) PPO update -----------------------------------------------------------------------
  * replaces PPO::update, src/algorithms/ppo.cpp:44-178, including the generator's gathers
  * (feed_forward_generator.cpp:42-80 / recurrent_generator.cpp:47-98), Policy::evaluate_actions,

@@ -186,6 +186,31 @@ class Policy:
             p.d_norm_var = n.rms.variance.data_ptr()
         return p
 
+    def act(self, inputs, rnn_hxs, masks, seed: Optional[int] = None, offset: int = 0) -> List[torch.Tensor]:
+        """PolicyImpl::act (policy.cpp:52-81): {value [B,1], action [B,1] int64 or [B,A], log-prob [B,1], hxs}.
+        The sample comes from a Philox stream keyed by (seed, row); without a seed one is drawn from torch's CPU
+        generator (so torch.manual_seed makes a run reproducible, as it does for the reference)."""
+        _need_cuda(inputs)
+        B = inputs.shape[0]
+        obs = inputs.reshape(B, -1).float().contiguous()
+        if seed is None:
+            seed = int(torch.randint(0, 2 ** 62, (1,)).item())
+        discrete = self.action_space.type == "Discrete"
+        A = self.action_space.shape[0]
+        value = torch.empty(B, 1, device=obs.device)
+        logp = torch.empty(B, 1, device=obs.device)
+        action = torch.empty((B, 1), dtype=torch.int64, device=obs.device) if discrete else torch.empty(B, A, device=obs.device)
+        hxs = msk = hxs_out = None
+        if self.is_recurrent():
+            hxs = rnn_hxs.float().contiguous()
+            msk = masks.float().reshape(-1).contiguous()
+            hxs_out = torch.empty_like(hxs)
+        pd = self.desc()
+        check(cabi.load().cpprl_b200_act(C.byref(pd), _ptr(obs), _ptr(hxs), 0 if hxs is None else hxs.shape[0], _ptr(msk), B,
+                                         C.c_uint64(seed), C.c_uint64(offset), _ptr(value), _ptr(action), _ptr(logp),
+                                         _ptr(hxs_out), _stream()))
+        return [value, action, logp, hxs_out if hxs_out is not None else rnn_hxs]
+
     def evaluate_actions(self, inputs, rnn_hxs, masks, actions) -> List[torch.Tensor]:
         """{value [B,1], action_log_probs [B,1], entropy [], rnn_hxs} — policy.cpp:83-115 (forward only)."""
         _need_cuda(inputs, actions)

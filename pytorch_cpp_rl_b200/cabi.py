@@ -81,6 +81,8 @@ SIGNATURES = {
     "cpprl_b200_rmsprop_step": (C.c_int, [C.c_void_p] * 3 + [C.c_int64, C.c_float, C.c_float, C.c_float, C.c_void_p]),
     "cpprl_b200_policy_num_params": (C.c_int64, [C.POINTER(Policy)]),
     "cpprl_b200_evaluate_actions": (C.c_int, [C.POINTER(Policy), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64] + [C.c_void_p] * 5),
+    "cpprl_b200_act": (C.c_int, [C.POINTER(Policy), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_uint64, C.c_uint64]
+                       + [C.c_void_p] * 5),
     "cpprl_b200_ppo_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int64]),
     "cpprl_b200_ppo_destroy": (None, [C.c_void_p]),
     "cpprl_b200_ppo_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),

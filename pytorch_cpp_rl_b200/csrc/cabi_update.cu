@@ -7,6 +7,8 @@
 #include <mutex>
 #include <vector>
 
+#include <curand_kernel.h>
+
 #include "common.cuh"
 #include "cnn_update.cuh"
 #include "gru_update.cuh"
@@ -1315,21 +1317,11 @@ extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
     return po.P;
 }
 
-extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs,
-                                           int64_t n_hxs, const float *d_masks, const void *d_actions, int64_t B,
-                                           float *d_value, float *d_logp, float *d_entropy, float *d_hxs_out,
-                                           void *stream)
+// forward of any base on B explicit rows; d_dist (nullable, [B][A]) receives what act() samples from.  Caller holds g_eval_mu.
+static int evaluate_impl(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                         const float *d_masks, const void *d_actions, int64_t B, float *d_value, float *d_logp,
+                         float *d_entropy, float *d_hxs_out, float *d_dist, cudaStream_t s)
 {
-    if (int rc = require_device())
-        return rc;
-    if (int rc = validate_policy(policy, "evaluate_actions"))
-        return rc;
-    if (!d_obs || !d_actions || !d_value || !d_logp || !d_entropy)
-        return fail(CPPRL_B200_EINVAL, "evaluate_actions: null pointer");
-    if (B <= 0 || B > 0x7fffffffll)
-        return fail(CPPRL_B200_EINVAL, "evaluate_actions: bad batch size");
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    std::lock_guard<std::mutex> lock(g_eval_mu);
 
     if (policy->base_kind == CPPRL_B200_BASE_CNN)
     {
@@ -1348,6 +1340,7 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
         c.out_value = d_value;
         c.out_logp = d_logp;
         c.out_entropy_sum = d_entropy;
+        c.out_dist = d_dist;
         CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
         if (int rc = cnn_build_images(c, ws, s))
             return rc;
@@ -1386,6 +1379,7 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
         a.out_logp = d_logp;
         a.out_entropy_sum = d_entropy;
         a.out_hxs = d_hxs_out;
+        a.out_dist = d_dist;
         a.step_mode = T == 1;
         CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
         if (int rc = launch_gru_update(a, static_cast<int>(n_hxs), s))
@@ -1428,11 +1422,151 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     a.out_value = d_value;
     a.out_logp = d_logp;
     a.out_entropy_sum = d_entropy;
+    a.out_dist = d_dist;
     CPPRL_CUDA_TRY(cudaMemsetAsync(g_eval_scratch.image, 0, il.floats * sizeof(float), s));
     CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
     if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
         return rc;
     finish_entropy_kernel<<<1, 1, 0, s>>>(d_entropy, 1.f / static_cast<float>(B)); // entropy().mean() (policy.cpp:109)
     CPPRL_LAUNCH_CHECK("finish_entropy_kernel");
+    return 0;
+}
+
+extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs,
+                                           int64_t n_hxs, const float *d_masks, const void *d_actions, int64_t B,
+                                           float *d_value, float *d_logp, float *d_entropy, float *d_hxs_out,
+                                           void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "evaluate_actions"))
+        return rc;
+    if (!d_obs || !d_actions || !d_value || !d_logp || !d_entropy)
+        return fail(CPPRL_B200_EINVAL, "evaluate_actions: null pointer");
+    if (B <= 0 || B > 0x7fffffffll)
+        return fail(CPPRL_B200_EINVAL, "evaluate_actions: bad batch size");
+    std::lock_guard<std::mutex> lock(g_eval_mu);
+    return evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, d_actions, B, d_value, d_logp, d_entropy, d_hxs_out, nullptr,
+                         static_cast<cudaStream_t>(stream));
+}
+
+// ---- PolicyImpl::act (policy.cpp:52-81): forward + sample + log-prob ----------------------------------------------------
+// Categorical::sample is torch::multinomial(probs, 1) (categorical.cpp:63-80): inverse CDF of one uniform here;
+// Normal::sample is loc + scale * N(0, 1) (normal.cpp:39-44).  Philox4x32-10 keyed by (seed, row), so a given
+// (seed, offset) reproduces the same actions whatever the launch shape.  Parity with the reference is distributional
+// (it draws from the CPU mt19937 stream); the log-probabilities are those evaluate_actions returns for the same actions.
+__global__ void __launch_bounds__(256)
+    act_sample_kernel(const float *__restrict__ dist, const float *__restrict__ params, int slog_offset, int head, int A,
+                      long long B, unsigned long long seed, unsigned long long offset, void *__restrict__ actions,
+                      float *__restrict__ logp)
+{
+    const long long row = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (row >= B)
+        return;
+    curandStatePhilox4_32_10_t rng;
+    curand_init(seed, static_cast<unsigned long long>(row), offset, &rng);
+    const float *d = dist + row * A;
+    if (head == 0)
+    {
+        const float u = curand_uniform(&rng); // (0, 1]
+        float cdf = 0.f;
+        int pick = A - 1;
+        for (int i = 0; i < A; ++i)
+        {
+            cdf += expf(d[i]);
+            if (u <= cdf)
+            {
+                pick = i;
+                break;
+            }
+        }
+        static_cast<long long *>(actions)[row] = pick;
+        logp[row] = d[pick];
+    }
+    else
+    {
+        float lp = 0.f;
+        for (int i = 0; i < A; i += 4)
+        {
+            const float4 z = curand_normal4(&rng);
+            const float zz[4] = {z.x, z.y, z.z, z.w};
+            for (int j = 0; j < 4 && i + j < A; ++j)
+            {
+                const float log_sigma = params[slog_offset + i + j], sigma = expf(log_sigma);
+                const float x = d[i + j] + sigma * zz[j];
+                const float diff = x - d[i + j];
+                static_cast<float *>(actions)[row * A + i + j] = x;
+                lp += -(diff * diff) / (2.f * sigma * sigma) - log_sigma - 0.91893853320467274178f; // normal.cpp:24-37
+            }
+        }
+        logp[row] = lp; // summed over the action dimensions (policy.cpp:72-75)
+    }
+}
+
+static float *g_act_dist = nullptr;
+static void *g_act_zero = nullptr;
+static size_t g_act_dist_cap = 0, g_act_zero_cap = 0;
+
+extern "C" int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                              const float *d_masks, int64_t B, uint64_t seed, uint64_t offset, float *d_value,
+                              void *d_actions, float *d_logp, float *d_hxs_out, void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "act"))
+        return rc;
+    if (!d_obs || !d_actions || !d_value || !d_logp)
+        return fail(CPPRL_B200_EINVAL, "act: null pointer");
+    if (B <= 0 || B > 0x7fffffffll)
+        return fail(CPPRL_B200_EINVAL, "act: bad batch size");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int A = static_cast<int>(policy->num_actions);
+    const bool normal = policy->head_kind == CPPRL_B200_HEAD_NORMAL;
+    std::lock_guard<std::mutex> lock(g_eval_mu);
+    // scratch: the distribution parameters [B][A] + one float of entropy, and placeholder actions (zeros)
+    const size_t need_dist = static_cast<size_t>(B) * A + 4, need_zero = static_cast<size_t>(B) * (normal ? A * sizeof(float) : sizeof(int64_t));
+    if (need_dist > g_act_dist_cap)
+    {
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(s));
+        cudaFree(g_act_dist);
+        g_act_dist = nullptr;
+        CPPRL_CUDA_TRY(cudaMalloc(&g_act_dist, need_dist * sizeof(float)));
+        g_act_dist_cap = need_dist;
+    }
+    if (need_zero > g_act_zero_cap)
+    {
+        CPPRL_CUDA_TRY(cudaStreamSynchronize(s));
+        cudaFree(g_act_zero);
+        g_act_zero = nullptr;
+        CPPRL_CUDA_TRY(cudaMalloc(&g_act_zero, need_zero));
+        CPPRL_CUDA_TRY(cudaMemset(g_act_zero, 0, need_zero));
+        g_act_zero_cap = need_zero;
+    }
+    float *d_entropy = g_act_dist + static_cast<size_t>(B) * A;
+    if (int rc = evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, g_act_zero, B, d_value, d_logp, d_entropy, d_hxs_out,
+                               g_act_dist, s))
+        return rc;
+    int slog = 0;
+    if (normal)
+    {
+        if (policy->base_kind == CPPRL_B200_BASE_CNN)
+            slog = cnn_param_offsets(static_cast<int>(policy->obs_chw[0]), A, 1).slog;
+        else if (policy->base_kind == CPPRL_B200_BASE_GRU_MLP)
+        {
+            GruUpdateArgs g;
+            if (int rc = fill_gru_policy_args(g, *policy, 1, "act"))
+                return rc;
+            slog = g.po.slog;
+        }
+        else
+        {
+            ParamOffsets po;
+            mlp_param_offsets(*policy, po);
+            slog = po.slog;
+        }
+    }
+    act_sample_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, s>>>(g_act_dist, policy->d_params, slog, normal ? 1 : 0, A,
+                                                                            B, seed, offset, d_actions, d_logp);
+    CPPRL_LAUNCH_CHECK("act_sample_kernel");
     return 0;
 }

@@ -644,6 +644,14 @@ __global__ void __launch_bounds__(256, 1) cnn_heads_kernel(const CnnUpdateArgs a
                 a.out_value[chunk_base + r] = value;
                 if (a.out_logp)
                     a.out_logp[chunk_base + r] = newlp;
+                if (a.out_dist)
+                {
+                    // Categorical: logit[] already holds the normalised log-probabilities; Normal: the means
+#pragma unroll
+                    for (int o = 0; o < kMaxActions; ++o)
+                        if (o < A)
+                            a.out_dist[static_cast<size_t>(chunk_base + r) * A + o] = logit[o];
+                }
             }
             ent_sum += ent;
             continue;

@@ -66,6 +66,7 @@ struct CnnUpdateArgs
     float beta1, beta2, eps, alpha;
     UpdateState *state;
     float *out_value, *out_logp, *out_entropy_sum; // forward evaluation
+    float *out_dist;       // nullable [B][A]: normalised log-probabilities / means (see mlp_update.cuh)
     // env-sharded update (world > 1): B rows of this rank out of a minibatch of B_norm rows box-wide; gradients and
     // partial sums are added over the ranks (exchange sequence number xseq) before the optimiser step
     int B_norm;

@@ -454,6 +454,8 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const __grid
                         newlp += i == act ? l : 0.f;
                         LOGIT[i * GLD + r] = l;
                         DLOGIT[i * GLD + r] = pr;
+                        if (!training && a.out_dist && valid)
+                            a.out_dist[(static_cast<size_t>(t0 + r) * N + agent) * A + i] = l;
                     }
                 }
                 else
@@ -462,6 +464,8 @@ __global__ void __launch_bounds__(kGruThreads, 1) gru_update_kernel(const __grid
                     {
                         const float var = SIG[2 * i], log_sigma = SIG[2 * i + 1];
                         const float diff = ACT[i * GLD + r] - LOGIT[i * GLD + r];
+                        if (!training && a.out_dist && valid)
+                            a.out_dist[(static_cast<size_t>(t0 + r) * N + agent) * A + i] = LOGIT[i * GLD + r];
                         newlp += -(diff * diff) / (2.f * var) - log_sigma - 0.91893853320467274178f;
                         ent += 0.5f + 0.5f * 1.8378770664093454836f + log_sigma;
                         LOGIT[i * GLD + r] = diff / var;

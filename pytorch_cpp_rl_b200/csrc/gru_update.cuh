@@ -48,6 +48,7 @@ struct GruUpdateArgs
     float *tape;             // [grid][kGruTapes][T][H]
     UpdateState *state;
     float *out_value, *out_logp, *out_entropy_sum, *out_hxs;
+    float *out_dist; // nullable [rows][A]: normalised log-probabilities / means (see mlp_update.cuh)
     long long *dbg_clocks;   // nullable: clock64() phase markers of minibatch dbg_step (profiling hook)
     int dbg_step;
     int step_mode;           // forward: write the new hidden state to out_hxs (x rows == hxs rows)

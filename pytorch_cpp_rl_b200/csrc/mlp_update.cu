@@ -571,6 +571,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         newlp += i == act ? l : 0.f;             // log_prob = gather(l, action)  (categorical.cpp:54-61)
                         LOGIT[i * LD + r] = l;
                         DLOGIT[i * LD + r] = pr;
+                        if (!training && a.out_dist && valid)
+                            a.out_dist[static_cast<size_t>(row0 + r) * A + i] = l;
                     }
                 }
                 else
@@ -580,6 +582,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     {
                         const float var = SIG[2 * i], log_sigma = SIG[2 * i + 1];
                         const float diff = ACT[i * LD + r] - LOGIT[i * LD + r];
+                        if (!training && a.out_dist && valid)
+                            a.out_dist[static_cast<size_t>(row0 + r) * A + i] = LOGIT[i * LD + r];
                         newlp += -(diff * diff) / (2.f * var) - log_sigma - 0.91893853320467274178f;
                         ent += 0.5f + 0.5f * 1.8378770664093454836f + log_sigma;
                         LOGIT[i * LD + r] = diff / var;                   // d logp / d loc

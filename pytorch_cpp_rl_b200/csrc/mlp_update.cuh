@@ -101,5 +101,6 @@ struct MlpUpdateArgs
     int dbg_step;
     // forward-only outputs (kAlgoForward)
     float *out_value, *out_logp, *out_entropy_sum;
+    float *out_dist; // nullable [B][A]: normalised log-probabilities (Categorical) / means (Normal): what act() samples from
 };
 } // namespace cpprl_b200

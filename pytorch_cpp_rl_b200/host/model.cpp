@@ -265,20 +265,28 @@ void PolicyImpl::describe(cpprl_b200_policy &out) const
 
 std::vector<torch::Tensor> PolicyImpl::act(torch::Tensor inputs, torch::Tensor rnn_hxs, torch::Tensor masks) const
 {
-    if (!observation_normalizer.is_empty())
-        inputs = observation_normalizer->process_observation(inputs);
-    auto out = base->forward(inputs, rnn_hxs, masks);
-    auto dist = output_layer->forward(out[1]);
-    auto action = dist->sample();
-    auto logp = dist->log_prob(action);
-    if (action_space.type == "Discrete")
+    // policy.cpp:52-81 as ONE C-ABI call (fused forward + Philox sample + log-prob).  The Philox seed is drawn from
+    // torch's CPU generator, so torch::manual_seed makes a run reproducible as it does for the reference.
+    cpprl_b200_policy desc;
+    describe(desc);
+    const int64_t B = inputs.size(0);
+    auto obs = detail::dense(inputs.reshape({B, -1}).to(torch::kFloat), "act: inputs");
+    const bool discrete = action_space.type == "Discrete";
+    auto opts = obs.options();
+    auto value = torch::empty({B, 1}, opts), logp = torch::empty({B, 1}, opts);
+    auto action = discrete ? torch::empty({B, 1}, opts.dtype(torch::kLong)) : torch::empty({B, action_space.shape.at(0)}, opts);
+    torch::Tensor hxs, msk, hxs_out;
+    if (base->is_recurrent())
     {
-        action = action.unsqueeze(-1);
-        logp = logp.unsqueeze(-1);
+        hxs = detail::dense(rnn_hxs.to(torch::kFloat), "act: rnn_hxs");
+        msk = detail::dense(masks.to(torch::kFloat).reshape({-1}), "act: masks");
+        hxs_out = torch::empty_like(hxs);
     }
-    else
-        logp = logp.sum(-1, true);
-    return {out[0], action, logp, out[2]};
+    const uint64_t seed = static_cast<uint64_t>(torch::randint(0, static_cast<int64_t>(1) << 62, {1}, torch::kLong).item<int64_t>());
+    check(cpprl_b200_act(&desc, fptr(obs), hxs.defined() ? fptr(hxs) : nullptr, hxs.defined() ? hxs.size(0) : 0,
+                         msk.defined() ? fptr(msk) : nullptr, B, seed, 0, fptr(value), action.data_ptr(), fptr(logp),
+                         hxs_out.defined() ? fptr(hxs_out) : nullptr, current_stream(obs)));
+    return {value, action, logp, hxs_out.defined() ? hxs_out : rnn_hxs};
 }
 
 std::vector<torch::Tensor> PolicyImpl::evaluate_actions(torch::Tensor inputs, torch::Tensor rnn_hxs, torch::Tensor masks,

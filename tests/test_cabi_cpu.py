@@ -22,7 +22,7 @@ def test_header_declares_the_path():
     names = declared_functions()
     for must in ("cpprl_b200_compute_returns", "cpprl_b200_advantages", "cpprl_b200_gather_rows", "cpprl_b200_rms_update",
                  "cpprl_b200_normalize_observations", "cpprl_b200_adam_step", "cpprl_b200_rmsprop_step",
-                 "cpprl_b200_evaluate_actions", "cpprl_b200_ppo_update", "cpprl_b200_a2c_update", "cpprl_b200_last_error"):
+                 "cpprl_b200_evaluate_actions", "cpprl_b200_act", "cpprl_b200_ppo_update", "cpprl_b200_a2c_update", "cpprl_b200_last_error"):
         assert must in names
 
 
