@@ -334,6 +334,20 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     barrier()
     e2e_s = (time.perf_counter() - t0) / args.steps
 
+    # the same end-to-end call with the opt-in device-drawn permutations (api.PPO.device_permutations): what is left of
+    # the gap between `value` and `e2e` once the host randperm (the reference's own CPU random stream) is out of the way
+    e2e_dev_s = None
+    if world == 1 and w.algo == "ppo" and w.base != "gru":
+        side.algo.device_permutations = True
+        side.step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            side.step_e2e()
+        barrier()
+        e2e_dev_s = (time.perf_counter() - t0) / args.steps
+        side.algo.device_permutations = False
+
     if world > 1:
         t = torch.tensor([total_ms, e2e_s], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -408,7 +422,11 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
                    + ("kernel between backward and optimiser" if w.base == "cnn" else "inside the fused kernel") +
                    " over NVLink peer memory"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": side.h2d_bytes, "d2h_bytes_per_step": side.d2h_bytes,
-                "ms_per_step": e2e_s * 1e3},
+                "ms_per_step": e2e_s * 1e3,
+                "permutations": "device (sharded update)" if world > 1 and w.base != "gru" else "host torch.randperm, the reference's CPU random stream",
+                "with_device_permutations": None if e2e_dev_s is None else
+                {"value": world * w.rows / e2e_dev_s, "ms_per_step": e2e_dev_s * 1e3,
+                 "h2d_bytes_per_step": side.h2d_bytes - w.num_epoch * side.perm_len * 8}},
         "gpu_launches": int(launches), "roofline": roofline, "stages": stages, "kernel_time_share": shares,
         "cpu_baseline": cpu, "clocks": clocks.summary(), "wall_ms_per_step_incl_flush": t_wall * 1e3 / args.steps,
     }

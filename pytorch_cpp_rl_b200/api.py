@@ -416,6 +416,7 @@ class PPO:
         self.actor_loss_coef, self.value_loss_coef, self.entropy_coef = actor_loss_coef, value_loss_coef, entropy_coef
         self.original_learning_rate = learning_rate
         self.epsilon, self.max_grad_norm, self.kl_target = epsilon, max_grad_norm, kl_target
+        self.device_permutations = False  # opt-in: draw the per-epoch permutations with the CUDA generator (see update)
         self._h = C.c_void_p()
         check(cabi.load().cpprl_b200_ppo_create(C.byref(self._h), policy.params.numel()))
 
@@ -472,12 +473,14 @@ class PPO:
                     check(lib.cpprl_b200_ppo_stopped(self._h, C.byref(stopped)))
                     if stopped.value:
                         break
-                if getattr(self, "_comm", None) is not None:
+                if getattr(self, "_comm", None) is not None or self.device_permutations:
                     # env-sharded: the permutation is over the GLOBAL rollout (T * global_envs ids, identical on every
                     # rank).  Drawing it on the host costs every rank tens of ms per epoch and does not shrink with
                     # the number of GPUs, so it comes from the CUDA generator instead: identically seeded ranks
                     # (torch.manual_seed) on identical GPUs draw identical permutations.  (The reference has no
-                    # distributed path whose CPU random stream this could be compared with.)
+                    # distributed path whose CPU random stream this could be compared with.)  On one GPU the same
+                    # path is the opt-in `device_permutations`: statistically equivalent minibatches, but no longer
+                    # the reference's CPU random stream (the default keeps torch.randperm on the CPU generator).
                     perm = torch.randperm(n, dtype=torch.int64, device=self.policy.params.device)
                     keep.append(perm)
                     check(lib.cpprl_b200_ppo_epoch_device(self._h, _ptr(perm), n))
