@@ -372,6 +372,11 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "peak_source": f"nominal 148 SM x 128 FMA/clk x 2 x {sm_max:.0f} MHz; fp32 CUDA-core bound, neither hbm nor tensor "
                        "(see DESIGN.md); share of step = " + f"{upd_ms / total_ms:.2f}",
     }
+    if w.name == "cfg3" and world == 1:
+        # dram__bytes_read.sum + dram__bytes_write.sum of one launch (= one epoch) from the committed ncu --set full capture;
+        # the algorithmic bytes of an epoch are the gathered rollout rows, 262144 x 112 B = 29.4 MB: no wasted re-reads
+        roofline["traffic"] = 29616128 + 353792
+        roofline["traffic_source"] = "profiles/r1b_mlp_update_cfg3_raw.csv"
     if w.base == "cnn" and os.environ.get("CPPRL_B200_CNN_FP32") != "1":
         # the ten CnnBase contractions run on tcgen05 as 3xTF32 (hi*hi + hi*lo + lo*hi): three TF32 MMAs per
         # algorithmic product at half the bf16 rate, so this path's own ceiling is the measured bf16 peak / 6
