@@ -269,6 +269,34 @@ def gae_sweep(torch, api, hbm_peak, T=256, N=1 << 20, iters=5):
             "ms_per_launch": ms, "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak}
 
 
+def insert_sweep(torch, api, hbm_peak, T=8, N=1024, iters=8):
+    """RolloutStorage::insert HBM GB/s with Atari frames (cpprl_b200_storage_insert, one launch for all seven
+    fields): N x 4x84x84 fp32 = 115.6 MB read + written per launch (> L2 together with the rotating time rows)."""
+    space = api.ActionSpace("Discrete", [6])
+    st = api.RolloutStorage(T, N, (4, 84, 84), space, 1)
+    rows = [torch.rand(N, 4, 84, 84, device="cuda") for _ in range(2)]
+    small = [torch.zeros(N, 1, device="cuda") for _ in range(5)]
+    act = torch.zeros(N, 1, dtype=torch.int64, device="cuda")
+
+    def one(i):
+        st.insert(rows[i % 2], small[0], act, small[1], small[2], small[3], small[4])
+    for i in range(3):
+        one(i)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for i, (a, b) in enumerate(ev):
+        a.record()
+        one(i)
+        b.record()
+    torch.cuda.synchronize()
+    ms = float(np.mean([a.elapsed_time(b) for a, b in ev]))
+    row_bytes = 4 * (4 * 84 * 84 + 1 + 1 + 1 + 1 + 1) + 8  # observation, hidden, log-prob, value, reward, mask, int64 action
+    nbytes = 2 * N * row_bytes
+    gbs = nbytes / (ms * 1e-3) / 1e9
+    return {"kernel": "storage_copy_kernel", "bound": "hbm", "workload": f"insert N={N} frames 4x84x84 (SURVEY 8f row 2)",
+            "bytes_per_launch": nbytes, "ms_per_launch": ms, "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+            "frac": gbs / hbm_peak}
+
+
 def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     import torch
     import torch.distributed as dist
@@ -392,8 +420,9 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
                            "; achieved counts ALGORITHMIC fp32 flops (2 x MACs of forward + both backward contractions); "
                            "fp32-accurate results need 3 TF32 MMAs per product at bf16/2 rate -> ceiling = peak / 6; "
                            f"share of step = {upd_ms / total_ms:.2f}"})
-    stages = [gae_sweep(torch, api, hbm_peak)]
-    stages[0]["peak_source"] = peak_src
+    stages = [gae_sweep(torch, api, hbm_peak), insert_sweep(torch, api, hbm_peak)]
+    for st in stages:
+        st["peak_source"] = peak_src
     shares = {"update": upd_ms / total_ms, "returns": ret_ms / total_ms, "prologue": pro_ms / total_ms,
               "rms": rms_ms / total_ms}
 

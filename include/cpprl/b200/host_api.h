@@ -27,6 +27,7 @@ struct cpprl_b200_ppo;
 struct cpprl_b200_a2c;
 struct cpprl_b200_policy;
 struct cpprl_b200_rollout;
+struct cpprl_b200_storage;
 
 namespace cpprl
 {
@@ -250,6 +251,9 @@ class RolloutStorage
 
     // C-ABI view of the buffers (re-read on every call: the handles above may have been rebound)
     void describe(cpprl_b200_rollout &out) const;
+    // writable view for the write-side entry points (insert / after_update / concatenation); makes rebound,
+    // non-contiguous buffers dense first
+    void describe_storage(cpprl_b200_storage &out);
 
   private:
     torch::Tensor observations, hidden_states, rewards, value_predictions, returns, action_log_probs, actions, masks;

@@ -297,6 +297,45 @@ int cpprl_b200_a2c_set_comm(cpprl_b200_a2c *h, cpprl_b200_comm *comm, int64_t gl
 int cpprl_b200_rms_update_sharded(cpprl_b200_comm *comm, const float *d_x, int64_t M, int64_t D, float *d_count,
                                   float *d_mean, float *d_var, void *d_workspace, void *stream);
 
+/* ---- (f2) the write side of the rollout buffer ------------------------------------------------------
+ * Writable description of a RolloutStorage (src/storage.cpp:15-49), every buffer time-major contiguous. */
+typedef struct cpprl_b200_storage
+{
+    int64_t T, N;
+    int64_t obs_dim;            /* product of the observation shape */
+    int64_t hidden_dim;         /* Hs */
+    int64_t action_cols;        /* 1 for Discrete, A for Box */
+    int32_t action_elem_bytes;  /* 8 (int64, Discrete) or 4 (fp32, Box) */
+    float *d_observations;      /* [T+1,N,obs_dim] */
+    float *d_hidden_states;     /* [T+1,N,Hs] */
+    float *d_rewards;           /* [T,N] */
+    float *d_value_preds;       /* [T+1,N] */
+    float *d_returns;           /* [T+1,N] */
+    float *d_action_log_probs;  /* [T,N] */
+    void *d_actions;            /* [T,N,action_cols] */
+    float *d_masks;             /* [T+1,N] */
+} cpprl_b200_storage;
+
+/* replaces RolloutStorage::insert, src/storage.cpp:176-193 (seven copy_ calls) with ONE launch: observation [N,obs_dim],
+ * hidden_state [N,Hs] and mask [N] go to time row step+1; action [N,action_cols], action_log_prob [N],
+ * value_prediction [N] and reward [N] to time row step.  The caller advances step = (step + 1) % T as the
+ * reference does (storage.cpp:192).  Inputs must already have the storage's dtypes (the reference's copy_ converts;
+ * the host mirrors convert before calling). */
+int cpprl_b200_storage_insert(const cpprl_b200_storage *st, int64_t step, const float *d_observation,
+                              const float *d_hidden_state, const void *d_action, const float *d_action_log_prob,
+                              const float *d_value_prediction, const float *d_reward, const float *d_mask,
+                              void *stream);
+/* replaces RolloutStorage::after_update, src/storage.cpp:106-111: time row 0 <- time row T of observations,
+ * hidden states and masks, one launch. */
+int cpprl_b200_storage_after_update(const cpprl_b200_storage *st, void *stream);
+/* replaces RolloutStorage::set_first_observation, src/storage.cpp:220-223. */
+int cpprl_b200_storage_set_first_observation(const cpprl_b200_storage *st, const float *d_observation, void *stream);
+/* replaces the body of the concatenating constructor, src/storage.cpp:51-104 (torch::cat(parts, 1) of the eight
+ * fields): writes `part` into environments [env_offset, env_offset + part->N) of `dst`, all eight fields in one
+ * launch; call once per part.  Also the scatter of a global rollout into per-GPU shards, read the other way. */
+int cpprl_b200_storage_concat(const cpprl_b200_storage *dst, const cpprl_b200_storage *part, int64_t env_offset,
+                              void *stream);
+
 /* ---- timing hooks ---------------------------------------------------------------------------------
  * The fused kernels record CUDA events on the caller's stream around each launch; these return the
  * accumulated device time and launch count of the named kernel family since the last reset

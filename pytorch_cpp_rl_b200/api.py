@@ -262,10 +262,72 @@ class RolloutStorage:
                                                      _ptr(next_value), _ptr(self.returns), self.num_steps,
                                                      self.num_processes, int(use_gae), gamma, tau, _stream()))
 
-    def after_update(self) -> None:  # storage.cpp:106-111
-        self.observations[0].copy_(self.observations[-1])
-        self.hidden_states[0].copy_(self.hidden_states[-1])
-        self.masks[0].copy_(self.masks[-1])
+    def storage_desc(self) -> cabi.Storage:
+        """Writable description of the eight buffers for the write-side entry points (cpprl_b200_storage_*)."""
+        bufs = (self.observations, self.hidden_states, self.rewards, self.value_predictions, self.returns,
+                self.action_log_probs, self.actions, self.masks)
+        _need_cuda(*bufs)
+        s = cabi.Storage()
+        s.T, s.N = self.num_steps, self.num_processes
+        s.obs_dim = self.observations[0, 0].numel()
+        s.hidden_dim = self.hidden_states.shape[-1]
+        s.action_cols = self.actions.shape[-1]
+        s.action_elem_bytes = self.actions.element_size()
+        (s.d_observations, s.d_hidden_states, s.d_rewards, s.d_value_preds, s.d_returns, s.d_action_log_probs,
+         s.d_actions, s.d_masks) = (t.data_ptr() for t in bufs)
+        return s
+
+    def _row(self, value: torch.Tensor, like: torch.Tensor, what: str) -> torch.Tensor:
+        # Tensor::copy_ converts dtype / device and broadcasts (storage.cpp:183-189); the kernel takes dense rows
+        # of the storage's own dtype, so anything else is converted here first
+        if not value.is_cuda:
+            raise RuntimeError(f"cpprl_b200: RolloutStorage.insert: {what} must live on a CUDA device "
+                               "(there is no CPU fallback)")
+        if value.dtype != like.dtype:
+            value = value.to(like.dtype)
+        if value.shape != like.shape:
+            value = value.expand(like.shape)
+        return value.contiguous()
+
+    def insert(self, observation, hidden_state, action, action_log_prob, value_prediction, reward, mask) -> None:
+        """RolloutStorage::insert (storage.cpp:176-193): all seven fields written by ONE launch."""
+        k = self.step
+        rows = (self._row(observation, self.observations[k + 1], "observation"),
+                self._row(hidden_state, self.hidden_states[k + 1], "hidden_state"),
+                self._row(action, self.actions[k], "action"),
+                self._row(action_log_prob, self.action_log_probs[k], "action_log_prob"),
+                self._row(value_prediction, self.value_predictions[k], "value_prediction"),
+                self._row(reward, self.rewards[k], "reward"),
+                self._row(mask, self.masks[k + 1], "mask"))
+        st = self.storage_desc()
+        check(cabi.load().cpprl_b200_storage_insert(C.byref(st), k, *[_ptr(r) for r in rows], _stream()))
+        self.step = (k + 1) % self.num_steps
+
+    def after_update(self) -> None:
+        """storage.cpp:106-111: time row 0 <- time row T of observations, hidden states and masks, one launch."""
+        st = self.storage_desc()
+        check(cabi.load().cpprl_b200_storage_after_update(C.byref(st), _stream()))
+
+    def set_first_observation(self, observation: torch.Tensor) -> None:  # storage.cpp:220-223
+        row = self._row(observation, self.observations[0], "observation")
+        st = self.storage_desc()
+        check(cabi.load().cpprl_b200_storage_set_first_observation(C.byref(st), _ptr(row), _stream()))
+
+    @classmethod
+    def concatenate(cls, parts: Sequence["RolloutStorage"], device="cuda") -> "RolloutStorage":
+        """The concatenating constructor (storage.cpp:51-104): the workers' storages joined along the environment
+        axis, one launch per part covering all eight fields."""
+        first = parts[0]
+        total = sum(p.num_processes for p in parts)
+        out = cls(first.num_steps, total, tuple(first.observations.shape[2:]), first.action_space,
+                  first.hidden_states.shape[-1], device=device)
+        dst = out.storage_desc()
+        offset = 0
+        for p in parts:
+            src = p.storage_desc()
+            check(cabi.load().cpprl_b200_storage_concat(C.byref(dst), C.byref(src), offset, _stream()))
+            offset += p.num_processes
+        return out
 
     def desc(self) -> cabi.Rollout:
         r = cabi.Rollout()

@@ -38,6 +38,16 @@ class Rollout(C.Structure):
     ]
 
 
+class Storage(C.Structure):
+    _fields_ = [
+        ("T", C.c_int64), ("N", C.c_int64), ("obs_dim", C.c_int64), ("hidden_dim", C.c_int64),
+        ("action_cols", C.c_int64), ("action_elem_bytes", C.c_int32),
+        ("d_observations", C.c_void_p), ("d_hidden_states", C.c_void_p), ("d_rewards", C.c_void_p),
+        ("d_value_preds", C.c_void_p), ("d_returns", C.c_void_p), ("d_action_log_probs", C.c_void_p),
+        ("d_actions", C.c_void_p), ("d_masks", C.c_void_p),
+    ]
+
+
 class PPOOptions(C.Structure):
     _fields_ = [
         ("clip_param", C.c_float), ("num_epoch", C.c_int32), ("num_mini_batch", C.c_int32),
@@ -109,6 +119,10 @@ SIGNATURES = {
     "cpprl_b200_ppo_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
     "cpprl_b200_a2c_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "cpprl_b200_rms_update_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64] + [C.c_void_p] * 5),
+    "cpprl_b200_storage_insert": (C.c_int, [C.POINTER(Storage), C.c_int64] + [C.c_void_p] * 8),
+    "cpprl_b200_storage_after_update": (C.c_int, [C.POINTER(Storage), C.c_void_p]),
+    "cpprl_b200_storage_set_first_observation": (C.c_int, [C.POINTER(Storage), C.c_void_p, C.c_void_p]),
+    "cpprl_b200_storage_concat": (C.c_int, [C.POINTER(Storage), C.POINTER(Storage), C.c_int64, C.c_void_p]),
     "cpprl_b200_kernel_time_ms": (C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cpprl_b200_kernel_time_reset": (None, []),
     "cpprl_b200_kernel_time_enable": (None, [C.c_int]),

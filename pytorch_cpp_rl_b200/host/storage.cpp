@@ -117,27 +117,103 @@ RolloutStorage::RolloutStorage(std::vector<RolloutStorage *> parts, torch::Devic
     : device(device), num_steps(parts.at(0)->get_rewards().size(0)), step(0)
 {
     // concatenate the workers' storages along the environment axis (storage.cpp:51-104)
-    auto join = [&](const torch::Tensor &(RolloutStorage::*get)() const) {
-        std::vector<torch::Tensor> pieces;
-        for (auto *p : parts)
-            pieces.push_back((p->*get)());
-        return torch::cat(pieces, 1).to(device);
+    if (!device.is_cuda())
+    {
+        // host-resident bookkeeping copy (nothing on the update path runs on it until ->to(cuda))
+        auto join = [&](const torch::Tensor &(RolloutStorage::*get)() const) {
+            std::vector<torch::Tensor> pieces;
+            for (auto *p : parts)
+                pieces.push_back((p->*get)());
+            return torch::cat(pieces, 1).to(device);
+        };
+        observations = join(&RolloutStorage::get_observations);
+        hidden_states = join(&RolloutStorage::get_hidden_states);
+        rewards = join(&RolloutStorage::get_rewards);
+        value_predictions = join(&RolloutStorage::get_value_predictions);
+        returns = join(&RolloutStorage::get_returns);
+        action_log_probs = join(&RolloutStorage::get_action_log_probs);
+        actions = join(&RolloutStorage::get_actions);
+        masks = join(&RolloutStorage::get_masks);
+        return;
+    }
+    // device path: allocate the joined buffers, then ONE launch per part scatters its eight fields into its
+    // environment columns (cpprl_b200_storage_concat)
+    int64_t total = 0;
+    for (auto *p : parts)
+        total += p->get_rewards().size(1);
+    auto like = [&](const torch::Tensor &t) {
+        auto shape = t.sizes().vec();
+        shape[1] = total;
+        return torch::empty(shape, t.options().device(device));
     };
-    observations = join(&RolloutStorage::get_observations);
-    hidden_states = join(&RolloutStorage::get_hidden_states);
-    rewards = join(&RolloutStorage::get_rewards);
-    value_predictions = join(&RolloutStorage::get_value_predictions);
-    returns = join(&RolloutStorage::get_returns);
-    action_log_probs = join(&RolloutStorage::get_action_log_probs);
-    actions = join(&RolloutStorage::get_actions);
-    masks = join(&RolloutStorage::get_masks);
+    auto *first = parts.at(0);
+    observations = like(first->observations);
+    hidden_states = like(first->hidden_states);
+    rewards = like(first->rewards);
+    value_predictions = like(first->value_predictions);
+    returns = like(first->returns);
+    action_log_probs = like(first->action_log_probs);
+    actions = like(first->actions);
+    masks = like(first->masks);
+    cpprl_b200_storage dst;
+    describe_storage(dst);
+    int64_t offset = 0;
+    for (auto *p : parts)
+    {
+        // a part living elsewhere (host, another GPU) is brought over first; the staging copy is the H2D transfer itself
+        RolloutStorage staged = *p;
+        staged.to(device);
+        cpprl_b200_storage src;
+        staged.describe_storage(src);
+        check(cpprl_b200_storage_concat(&dst, &src, offset, current_stream(observations)));
+        offset += src.N;
+    }
+}
+
+void RolloutStorage::describe_storage(cpprl_b200_storage &out)
+{
+    for (auto *t : {&observations, &hidden_states, &rewards, &value_predictions, &returns, &action_log_probs, &actions,
+                    &masks})
+    {
+        detail::need_cuda(*t, "RolloutStorage: rollout buffer");
+        if (!t->is_contiguous()) // a rebound, non-contiguous buffer is made dense and stays the storage's
+            *t = t->contiguous();
+    }
+    out.T = rewards.size(0);
+    out.N = rewards.size(1);
+    out.obs_dim = observations.numel() / (observations.size(0) * observations.size(1));
+    out.hidden_dim = hidden_states.size(2);
+    out.action_cols = actions.size(2);
+    out.action_elem_bytes = static_cast<int32_t>(actions.element_size());
+    out.d_observations = fptr(observations);
+    out.d_hidden_states = fptr(hidden_states);
+    out.d_rewards = fptr(rewards);
+    out.d_value_preds = fptr(value_predictions);
+    out.d_returns = fptr(returns);
+    out.d_action_log_probs = fptr(action_log_probs);
+    out.d_actions = actions.data_ptr();
+    out.d_masks = fptr(masks);
+}
+
+// what Tensor::copy_ accepts (any device, convertible dtype, broadcastable shape) as a dense device row of the
+// destination's dtype
+static torch::Tensor as_row(const torch::Tensor &value, const torch::Tensor &row)
+{
+    return value.to(row.options()).expand_as(row).contiguous();
 }
 
 void RolloutStorage::after_update()
 {
-    observations[0].copy_(observations[-1]);
-    hidden_states[0].copy_(hidden_states[-1]);
-    masks[0].copy_(masks[-1]);
+    if (!observations.is_cuda())
+    { // host-resident storage: handle bookkeeping only
+        observations[0].copy_(observations[-1]);
+        hidden_states[0].copy_(hidden_states[-1]);
+        masks[0].copy_(masks[-1]);
+        return;
+    }
+    cpprl_b200_storage st;
+    describe_storage(st);
+    check(cpprl_b200_storage_after_update(&st, current_stream(observations)));
 }
 
 void RolloutStorage::compute_returns(torch::Tensor next_value, bool use_gae, float gamma, float tau)
@@ -171,13 +247,28 @@ void RolloutStorage::insert(torch::Tensor observation, torch::Tensor hidden_stat
                             torch::Tensor action_log_prob, torch::Tensor value_prediction, torch::Tensor reward,
                             torch::Tensor mask)
 {
-    observations[step + 1].copy_(observation);
-    hidden_states[step + 1].copy_(hidden_state);
-    actions[step].copy_(action);
-    action_log_probs[step].copy_(action_log_prob);
-    value_predictions[step].copy_(value_prediction);
-    rewards[step].copy_(reward);
-    masks[step + 1].copy_(mask);
+    if (!observations.is_cuda())
+    { // host-resident storage: handle bookkeeping only
+        observations[step + 1].copy_(observation);
+        hidden_states[step + 1].copy_(hidden_state);
+        actions[step].copy_(action);
+        action_log_probs[step].copy_(action_log_prob);
+        value_predictions[step].copy_(value_prediction);
+        rewards[step].copy_(reward);
+        masks[step + 1].copy_(mask);
+    }
+    else
+    {
+        // all seven fields in ONE launch (cpprl_b200_storage_insert) instead of seven copy kernels
+        cpprl_b200_storage st;
+        describe_storage(st);
+        auto o = as_row(observation, observations[step + 1]), h = as_row(hidden_state, hidden_states[step + 1]);
+        auto a = as_row(action, actions[step]), lp = as_row(action_log_prob, action_log_probs[step]);
+        auto v = as_row(value_prediction, value_predictions[step]), r = as_row(reward, rewards[step]);
+        auto m = as_row(mask, masks[step + 1]);
+        check(cpprl_b200_storage_insert(&st, step, fptr(o), fptr(h), a.data_ptr(), fptr(lp), fptr(v), fptr(r), fptr(m),
+                                        current_stream(observations)));
+    }
     step = (step + 1) % num_steps;
 }
 
@@ -192,7 +283,18 @@ std::unique_ptr<Generator> RolloutStorage::recurrent_generator(torch::Tensor adv
                                                 value_predictions, returns, masks, action_log_probs, advantages);
 }
 
-void RolloutStorage::set_first_observation(torch::Tensor observation) { observations[0].copy_(observation); }
+void RolloutStorage::set_first_observation(torch::Tensor observation)
+{
+    if (!observations.is_cuda())
+    {
+        observations[0].copy_(observation);
+        return;
+    }
+    cpprl_b200_storage st;
+    describe_storage(st);
+    auto o = as_row(observation, observations[0]);
+    check(cpprl_b200_storage_set_first_observation(&st, fptr(o), current_stream(observations)));
+}
 
 void RolloutStorage::to(torch::Device dev)
 {

@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "cpprl/cpprl.h"
+#include "cpprl_b200.h"
 #include "oracle/ref_driver.h"
 
 extern "C"
@@ -129,6 +130,76 @@ static void test_generators()
     auto flat_obs = s2.get_observations().narrow(0, 0, 4).reshape({24, 7});
     CHECK(torch::equal(m2.observations, flat_obs.index({idx[0].to(kDev)})));
     CHECK(torch::equal(m2.advantages, adv2.reshape({24, 1}).index({idx[0].to(kDev)})));
+}
+
+// ---- the reference's storage scenarios on the device (storage.cpp:298-339, 438-488, 504-581) -----------------------
+static void test_storage_write_side()
+{
+    std::printf("storage write side\n");
+    const uint64_t before = cpprl_b200_launch_count();
+    { // insert(): CPU inputs of convertible dtypes land on rows step+1 / step of the device buffers, ONE launch
+        RolloutStorage storage(3, 4, {5, 2}, ActionSpace{"Discrete", {3}}, 10, kDev);
+        auto obs = torch::rand({4, 5, 2}) + 1, hid = torch::rand({4, 10}) + 1;
+        auto act = torch::randint(1, 3, {4, 1}), lp = torch::rand({4, 1}) + 1, v = torch::rand({4, 1}) + 1, r = torch::rand({4, 1}) + 1;
+        const uint64_t l0 = cpprl_b200_launch_count();
+        storage.insert(obs, hid, act, lp, v, r, torch::zeros({4, 1}));
+        CHECK(cpprl_b200_launch_count() - l0 == 1);
+        CHECK(torch::equal(storage.get_observations()[1].cpu(), obs));
+        CHECK(torch::equal(storage.get_hidden_states()[1].cpu(), hid));
+        CHECK(torch::equal(storage.get_actions()[0].cpu(), act.to(torch::kLong)));
+        CHECK(torch::equal(storage.get_action_log_probs()[0].cpu(), lp));
+        CHECK(torch::equal(storage.get_value_predictions()[0].cpu(), v));
+        CHECK(torch::equal(storage.get_rewards()[0].cpu(), r));
+        CHECK(storage.get_masks()[1].sum().item().toFloat() == 0.f);
+        CHECK(storage.get_masks()[0].sum().item().toFloat() == 4.f);
+        CHECK(storage.get_observations()[0].abs().sum().item().toFloat() == 0.f);
+    }
+    { // after_update(): expected 6 / 2 / 0 at the positions the reference probes
+        RolloutStorage storage(3, 2, {3}, ActionSpace{"Discrete", {3}}, 2, kDev);
+        float obs[3][6] = {{0, 1, 2, 1, 2, 3}, {0, 1, 2, 1, 2, 3}, {5, 6, 7, 7, 8, 9}};
+        float hid[3][4] = {{0, 1, 0, 1}, {0, 1, 0, 1}, {1, 2, 3, 4}}, msk[3][2] = {{0, 1}, {0, 1}, {0, 0}};
+        for (int t = 0; t < 3; ++t)
+            storage.insert(torch::from_blob(obs[t], {2, 3}).clone(), torch::from_blob(hid[t], {2, 2}).clone(), torch::zeros({2, 1}),
+                           torch::zeros({2, 1}), torch::zeros({2, 1}), torch::zeros({2, 1}), torch::from_blob(msk[t], {2, 1}).clone());
+        storage.after_update();
+        CHECK(storage.get_observations()[0][0][1].item().toFloat() == 6.f);
+        CHECK(storage.get_hidden_states()[0][0][1].item().toFloat() == 2.f);
+        CHECK(storage.get_masks()[0][0][0].item().toFloat() == 0.f);
+    }
+    { // the concatenating constructor: five one-environment storages, column i == storage i in every field
+        std::vector<RolloutStorage> storages;
+        for (int i = 0; i < 5; ++i)
+        {
+            storages.push_back({3, 1, {4}, ActionSpace{"Discrete", {3}}, 5, kDev});
+            float vals[3] = {1, 2, 3}, msk[3] = {1, 0, 1};
+            for (int t = 0; t < 3; ++t)
+                storages[i].insert(torch::rand({1, 4}), torch::rand({1, 5}), torch::rand({1, 1}), torch::rand({1, 1}),
+                                   torch::full({1, 1}, vals[t]), torch::full({1, 1}, vals[t]), torch::full({1, 1}, msk[t]));
+        }
+        std::vector<RolloutStorage *> pointers;
+        for (auto &st : storages)
+            pointers.push_back(&st);
+        const uint64_t l0 = cpprl_b200_launch_count();
+        RolloutStorage combined(pointers, kDev);
+        CHECK(cpprl_b200_launch_count() - l0 == 5); // one launch per part, all eight fields
+        CHECK((shape_of(combined.get_observations()) == std::vector<int64_t>{4, 5, 4}));
+        CHECK((shape_of(combined.get_hidden_states()) == std::vector<int64_t>{4, 5, 5}));
+        CHECK((shape_of(combined.get_rewards()) == std::vector<int64_t>{3, 5, 1}));
+        CHECK((shape_of(combined.get_actions()) == std::vector<int64_t>{3, 5, 1}));
+        CHECK(combined.get_actions().dtype() == torch::kLong);
+        for (int i = 0; i < 5; ++i)
+        {
+            CHECK(torch::equal(combined.get_observations().narrow(1, i, 1), storages[i].get_observations()));
+            CHECK(torch::equal(combined.get_hidden_states().narrow(1, i, 1), storages[i].get_hidden_states()));
+            CHECK(torch::equal(combined.get_rewards().narrow(1, i, 1), storages[i].get_rewards()));
+            CHECK(torch::equal(combined.get_value_predictions().narrow(1, i, 1), storages[i].get_value_predictions()));
+            CHECK(torch::equal(combined.get_returns().narrow(1, i, 1), storages[i].get_returns()));
+            CHECK(torch::equal(combined.get_action_log_probs().narrow(1, i, 1), storages[i].get_action_log_probs()));
+            CHECK(torch::equal(combined.get_actions().narrow(1, i, 1), storages[i].get_actions()));
+            CHECK(torch::equal(combined.get_masks().narrow(1, i, 1), storages[i].get_masks()));
+        }
+    }
+    CHECK(cpprl_b200_launch_count() > before);
 }
 
 // ---- observation_normalizer.cpp:95-129 ----------------------------------------------------------------------------
@@ -416,6 +487,7 @@ int main()
     }
     test_compute_returns_known_answer();
     test_generators();
+    test_storage_write_side();
     test_normalizer();
     test_policy_surface();
     test_learning();

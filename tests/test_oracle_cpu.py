@@ -186,3 +186,55 @@ def test_live_reference_cross_check(ref):
     wp = sess.get_params()
     err = np.abs(pol.flat - wp) / np.maximum(np.abs(wp), w.learning_rate)
     assert np.quantile(err, 0.99) <= 1e-4
+
+
+# ---- the write side of the rollout buffer -----------------------------------------------
+def test_rollout_insert_known_answer():
+    """src/storage.cpp:298-339 ("insert() inserts values"): non-zero inputs land on rows 1 / 0, the mask row 1 is 0."""
+    rng = np.random.default_rng(0)
+    ro = O.new_rollout(3, 4, (5, 2), True, 1, 10)
+    assert ro.actions.dtype == np.int64 and ro.masks.min() == 1.0 and ro.observations.shape == (4, 4, 5, 2)
+    step = O.rollout_insert(ro, 0, rng.random((4, 5, 2), np.float32) + 1, rng.random((4, 10), np.float32) + 1,
+                            rng.integers(1, 3, (4, 1)), rng.random((4, 1), np.float32) + 1,
+                            rng.random((4, 1), np.float32) + 1, rng.random((4, 1), np.float32) + 1, np.zeros((4, 1)))
+    assert step == 1
+    assert ro.observations[1, 0, 0, 0] != 0 and ro.hidden_states[1, 0, 0] != 0 and ro.actions[0, 0, 0] != 0
+    assert ro.action_log_probs[0, 0, 0] != 0 and ro.value_predictions[0, 0, 0] != 0 and ro.rewards[0, 0, 0] != 0
+    assert ro.masks[1, 0, 0] == 0 and ro.observations[0].max() == 0 and ro.masks[0].min() == 1
+
+
+def test_rollout_after_update_known_answer():
+    """src/storage.cpp:438-488: three inserts, then after_update moves row T of observations / hidden states / masks
+    to row 0 (expected 6, 2, 0 at the probed positions)."""
+    ro = O.new_rollout(3, 2, (3,), True, 1, 2)
+    z = np.zeros((2, 1), np.float32)
+    step = 0
+    for obs, hid, msk in (([0, 1, 2, 1, 2, 3], [0, 1, 0, 1], [0, 1]), ([0, 1, 2, 1, 2, 3], [0, 1, 0, 1], [0, 1]),
+                          ([5, 6, 7, 7, 8, 9], [1, 2, 3, 4], [0, 0])):
+        step = O.rollout_insert(ro, step, np.array(obs, np.float32).reshape(2, 3), np.array(hid, np.float32).reshape(2, 2),
+                                z, z, z, z, np.array(msk, np.float32).reshape(2, 1))
+    assert step == 0  # wrapped: (step + 1) % num_steps
+    O.rollout_after_update(ro)
+    assert ro.observations[0, 0, 1] == 6 and ro.hidden_states[0, 0, 1] == 2 and ro.masks[0, 0, 0] == 0
+
+
+def test_rollout_concatenate_known_answer():
+    """src/storage.cpp:504-581: five one-environment storages joined; column i of every field is storage i."""
+    rng = np.random.default_rng(1)
+    parts = []
+    for _ in range(5):
+        ro = O.new_rollout(3, 1, (4,), True, 1, 5)
+        step = 0
+        for v, m in ((1, 1), (2, 0), (3, 1)):
+            step = O.rollout_insert(ro, step, rng.random((1, 4), np.float32), rng.random((1, 5), np.float32),
+                                    rng.random((1, 1)), rng.random((1, 1), np.float32), np.float32(v), np.float32(v),
+                                    np.float32(m))
+        parts.append(ro)
+    joined = O.rollout_concatenate(parts)
+    assert joined.observations.shape == (4, 5, 4) and joined.hidden_states.shape == (4, 5, 5)
+    assert joined.rewards.shape == (3, 5, 1) and joined.actions.shape == (3, 5, 1) and joined.masks.shape == (4, 5, 1)
+    for i, p in enumerate(parts):
+        for name in ("observations", "hidden_states", "rewards", "value_predictions", "returns", "action_log_probs",
+                     "actions", "masks"):
+            assert np.array_equal(getattr(joined, name)[:, i:i + 1], getattr(p, name)), name
+    assert np.array_equal(joined.rewards[:, 0, 0], [1, 2, 3]) and np.array_equal(joined.masks[:, 0, 0], [1, 1, 0, 1])
