@@ -269,9 +269,9 @@ def gae_sweep(torch, api, hbm_peak, T=256, N=1 << 20, iters=5):
             "ms_per_launch": ms, "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak}
 
 
-def insert_sweep(torch, api, hbm_peak, T=8, N=1024, iters=8):
+def insert_sweep(torch, api, hbm_peak, T=2, N=4096, iters=8):
     """RolloutStorage::insert HBM GB/s with Atari frames (cpprl_b200_storage_insert, one launch for all seven
-    fields): N x 4x84x84 fp32 = 115.6 MB read + written per launch (> L2 together with the rotating time rows)."""
+    fields): N x 4x84x84 fp32 = 462 MB read and 462 MB written per launch (>> L2)."""
     space = api.ActionSpace("Discrete", [6])
     st = api.RolloutStorage(T, N, (4, 84, 84), space, 1)
     rows = [torch.rand(N, 4, 84, 84, device="cuda") for _ in range(2)]

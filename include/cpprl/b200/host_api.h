@@ -47,6 +47,7 @@ struct UpdateDatum
 };
 
 class RolloutStorage;
+class Policy;
 
 class Algorithm
 {
@@ -225,6 +226,9 @@ class RolloutStorage
     void after_update();
     // GAE / n-step scan on the device (cpprl_b200_compute_returns); side effects as storage.cpp:113-144
     void compute_returns(torch::Tensor next_value, bool use_gae, float gamma, float tau);
+    // extension: compute_returns(policy->get_values(observations[-1], hidden_states[-1], masks[-1]), ...) as ONE
+    // C-ABI call without the next_value temporary (cpprl_b200_bootstrap_returns)
+    void bootstrap_returns(Policy &policy, bool use_gae, float gamma, float tau);
     std::unique_ptr<Generator> feed_forward_generator(torch::Tensor advantages, int num_mini_batch);
     void insert(torch::Tensor observation, torch::Tensor hidden_state, torch::Tensor action,
                 torch::Tensor action_log_prob, torch::Tensor value_prediction, torch::Tensor reward, torch::Tensor mask);

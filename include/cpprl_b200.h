@@ -336,6 +336,20 @@ int cpprl_b200_storage_set_first_observation(const cpprl_b200_storage *st, const
 int cpprl_b200_storage_concat(const cpprl_b200_storage *dst, const cpprl_b200_storage *part, int64_t env_offset,
                               void *stream);
 
+/* ---- (f3) bootstrap value + returns ---------------------------------------------------------------------
+ * replaces PolicyImpl::get_values, src/model/policy.cpp:132-144: the value head of the fused forward on B rows
+ * (arguments as evaluate_actions; no actions needed).  value [B]. */
+int cpprl_b200_get_values(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                          const float *d_masks, int64_t B, float *d_value, void *stream);
+/* replaces the bootstrap sequence of the example driver, example/gym_client.cpp:266-275:
+ *     next_value = policy->get_values(observations[T], hidden_states[T], masks[T]);
+ *     storage.compute_returns(next_value, use_gae, gamma, tau);
+ * as one call with no temporary and no host round trip: the value forward of time row T writes straight to where
+ * compute_returns stores next_value (value_preds[T] with GAE, returns[T] otherwise) and the scan follows on the
+ * same stream.  Results are those of the two separate calls, bit for bit. */
+int cpprl_b200_bootstrap_returns(const cpprl_b200_policy *policy, const cpprl_b200_storage *st, int use_gae, float gamma,
+                                 float tau, void *stream);
+
 /* ---- timing hooks ---------------------------------------------------------------------------------
  * The fused kernels record CUDA events on the caller's stream around each launch; these return the
  * accumulated device time and launch count of the named kernel family since the last reset

@@ -211,6 +211,21 @@ class Policy:
                                          _ptr(hxs_out), _stream()))
         return [value, action, logp, hxs_out if hxs_out is not None else rnn_hxs]
 
+    def get_values(self, inputs, rnn_hxs, masks) -> torch.Tensor:
+        """PolicyImpl::get_values (policy.cpp:132-144): value [B,1] of the fused forward, no actions needed."""
+        _need_cuda(inputs)
+        B = inputs.shape[0]
+        obs = inputs.reshape(B, -1).float().contiguous()
+        value = torch.empty(B, 1, device=obs.device)
+        hxs = msk = None
+        if self.is_recurrent():
+            _need_cuda(rnn_hxs, masks)
+            hxs, msk = rnn_hxs.float().contiguous(), masks.float().reshape(-1).contiguous()
+        pd = self.desc()
+        check(cabi.load().cpprl_b200_get_values(C.byref(pd), _ptr(obs), _ptr(hxs), 0 if hxs is None else hxs.shape[0],
+                                                _ptr(msk), B, _ptr(value), _stream()))
+        return value
+
     def evaluate_actions(self, inputs, rnn_hxs, masks, actions) -> List[torch.Tensor]:
         """{value [B,1], action_log_probs [B,1], entropy [], rnn_hxs} — policy.cpp:83-115 (forward only)."""
         _need_cuda(inputs, actions)
@@ -302,6 +317,12 @@ class RolloutStorage:
         st = self.storage_desc()
         check(cabi.load().cpprl_b200_storage_insert(C.byref(st), k, *[_ptr(r) for r in rows], _stream()))
         self.step = (k + 1) % self.num_steps
+
+    def bootstrap_returns(self, policy: "Policy", use_gae: bool, gamma: float, tau: float) -> None:
+        """`compute_returns(policy.get_values(obs[T], hxs[T], masks[T]), ...)` (gym_client.cpp:266-275) as one call:
+        the value forward of time row T lands where compute_returns stores next_value, then the scan; no temporary."""
+        st, pd = self.storage_desc(), policy.desc()
+        check(cabi.load().cpprl_b200_bootstrap_returns(C.byref(pd), C.byref(st), int(use_gae), gamma, tau, _stream()))
 
     def after_update(self) -> None:
         """storage.cpp:106-111: time row 0 <- time row T of observations, hidden states and masks, one launch."""

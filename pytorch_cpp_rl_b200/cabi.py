@@ -123,6 +123,8 @@ SIGNATURES = {
     "cpprl_b200_storage_after_update": (C.c_int, [C.POINTER(Storage), C.c_void_p]),
     "cpprl_b200_storage_set_first_observation": (C.c_int, [C.POINTER(Storage), C.c_void_p, C.c_void_p]),
     "cpprl_b200_storage_concat": (C.c_int, [C.POINTER(Storage), C.POINTER(Storage), C.c_int64, C.c_void_p]),
+    "cpprl_b200_get_values": (C.c_int, [C.POINTER(Policy), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    "cpprl_b200_bootstrap_returns": (C.c_int, [C.POINTER(Policy), C.POINTER(Storage), C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "cpprl_b200_kernel_time_ms": (C.c_int, [C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "cpprl_b200_kernel_time_reset": (None, []),
     "cpprl_b200_kernel_time_enable": (None, [C.c_int]),

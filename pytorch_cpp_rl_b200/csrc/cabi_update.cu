@@ -1507,23 +1507,10 @@ static float *g_act_dist = nullptr;
 static void *g_act_zero = nullptr;
 static size_t g_act_dist_cap = 0, g_act_zero_cap = 0;
 
-extern "C" int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
-                              const float *d_masks, int64_t B, uint64_t seed, uint64_t offset, float *d_value,
-                              void *d_actions, float *d_logp, float *d_hxs_out, void *stream)
+// scratch of the act / get_values entry points: the distribution parameters [B][A] + one float of entropy, and
+// placeholder actions (zeros) for the forward kernels' log-prob stage
+static int ensure_act_scratch(int64_t B, int A, bool normal, cudaStream_t s)
 {
-    if (int rc = require_device())
-        return rc;
-    if (int rc = validate_policy(policy, "act"))
-        return rc;
-    if (!d_obs || !d_actions || !d_value || !d_logp)
-        return fail(CPPRL_B200_EINVAL, "act: null pointer");
-    if (B <= 0 || B > 0x7fffffffll)
-        return fail(CPPRL_B200_EINVAL, "act: bad batch size");
-    cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const int A = static_cast<int>(policy->num_actions);
-    const bool normal = policy->head_kind == CPPRL_B200_HEAD_NORMAL;
-    std::lock_guard<std::mutex> lock(g_eval_mu);
-    // scratch: the distribution parameters [B][A] + one float of entropy, and placeholder actions (zeros)
     const size_t need_dist = static_cast<size_t>(B) * A + 4, need_zero = static_cast<size_t>(B) * (normal ? A * sizeof(float) : sizeof(int64_t));
     if (need_dist > g_act_dist_cap)
     {
@@ -1542,6 +1529,85 @@ extern "C" int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_ob
         CPPRL_CUDA_TRY(cudaMemset(g_act_zero, 0, need_zero));
         g_act_zero_cap = need_zero;
     }
+    return 0;
+}
+
+// PolicyImpl::get_values (policy.cpp:132-144): the fused forward with placeholder actions; log-probabilities and the
+// entropy go to scratch.  Caller holds g_eval_mu.
+static int get_values_locked(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                             const float *d_masks, int64_t B, float *d_value, cudaStream_t s)
+{
+    const int A = static_cast<int>(policy->num_actions);
+    if (int rc = ensure_act_scratch(B, A, policy->head_kind == CPPRL_B200_HEAD_NORMAL, s))
+        return rc;
+    return evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, g_act_zero, B, d_value, g_act_dist, g_act_dist + B, nullptr,
+                         nullptr, s);
+}
+
+extern "C" int cpprl_b200_get_values(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                                     const float *d_masks, int64_t B, float *d_value, void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "get_values"))
+        return rc;
+    if (!d_obs || !d_value)
+        return fail(CPPRL_B200_EINVAL, "get_values: null pointer");
+    if (B <= 0 || B > 0x7fffffffll)
+        return fail(CPPRL_B200_EINVAL, "get_values: bad batch size");
+    std::lock_guard<std::mutex> lock(g_eval_mu);
+    return get_values_locked(policy, d_obs, d_hxs, n_hxs, d_masks, B, d_value, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int cpprl_b200_bootstrap_returns(const cpprl_b200_policy *policy, const cpprl_b200_storage *st, int use_gae,
+                                            float gamma, float tau, void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "bootstrap_returns"))
+        return rc;
+    if (!st || st->T <= 0 || st->N <= 0 || !st->d_observations || !st->d_hidden_states || !st->d_rewards || !st->d_value_preds ||
+        !st->d_returns || !st->d_masks)
+        return fail(CPPRL_B200_EINVAL, "bootstrap_returns: bad storage description");
+    if (st->obs_dim != policy->obs_dim)
+        return fail(CPPRL_B200_EINVAL, "bootstrap_returns: observation width of the storage differs from the policy's");
+    const bool recurrent = policy->base_kind == CPPRL_B200_BASE_GRU_MLP;
+    if (recurrent && st->hidden_dim != policy->hidden)
+        return fail(CPPRL_B200_EINVAL, "bootstrap_returns: hidden-state width of the storage differs from the policy's");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int64_t T = st->T, N = st->N;
+    // the value of the last observation is written where compute_returns would copy next_value to
+    // (value_predictions[T] with GAE, storage.cpp:120; returns[T] otherwise, storage.cpp:135): no temporary
+    float *next_value = (use_gae ? st->d_value_preds : st->d_returns) + T * N;
+    {
+        std::lock_guard<std::mutex> lock(g_eval_mu);
+        if (int rc = get_values_locked(policy, st->d_observations + T * N * st->obs_dim,
+                                       recurrent ? st->d_hidden_states + T * N * st->hidden_dim : nullptr, recurrent ? N : 0,
+                                       st->d_masks + T * N, N, next_value, s))
+            return rc;
+    }
+    return cpprl_b200_compute_returns(st->d_rewards, st->d_value_preds, st->d_masks, next_value, st->d_returns, T, N, use_gae,
+                                      gamma, tau, stream);
+}
+
+extern "C" int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+                              const float *d_masks, int64_t B, uint64_t seed, uint64_t offset, float *d_value,
+                              void *d_actions, float *d_logp, float *d_hxs_out, void *stream)
+{
+    if (int rc = require_device())
+        return rc;
+    if (int rc = validate_policy(policy, "act"))
+        return rc;
+    if (!d_obs || !d_actions || !d_value || !d_logp)
+        return fail(CPPRL_B200_EINVAL, "act: null pointer");
+    if (B <= 0 || B > 0x7fffffffll)
+        return fail(CPPRL_B200_EINVAL, "act: bad batch size");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int A = static_cast<int>(policy->num_actions);
+    const bool normal = policy->head_kind == CPPRL_B200_HEAD_NORMAL;
+    std::lock_guard<std::mutex> lock(g_eval_mu);
+    if (int rc = ensure_act_scratch(B, A, normal, s))
+        return rc;
     float *d_entropy = g_act_dist + static_cast<size_t>(B) * A;
     if (int rc = evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, g_act_zero, B, d_value, d_logp, d_entropy, d_hxs_out,
                                g_act_dist, s))

@@ -25,6 +25,7 @@ struct CopySegment
 struct CopyBatch
 {
     CopySegment seg[kMaxSegments];
+    int block_begin[kMaxSegments + 1]; // segment i owns blocks [block_begin[i], block_begin[i + 1])
     int count;
 };
 
@@ -57,12 +58,16 @@ __device__ __forceinline__ void copy_segment(const CopySegment &sg, int64_t firs
     }
 }
 
-// blockIdx.y selects the segment; blocks beyond a small segment's extent leave at once.
+// Every segment owns a contiguous range of blocks sized to its length (a [N] column gets one block, the frames
+// get the rest of the machine), so no block is launched only to leave.
 __global__ void __launch_bounds__(kCopyThreads) storage_copy_kernel(const __grid_constant__ CopyBatch batch)
 {
-    const CopySegment &sg = batch.seg[blockIdx.y];
-    const int64_t first = static_cast<int64_t>(blockIdx.x) * kCopyThreads + threadIdx.x;
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * kCopyThreads;
+    int k = 0;
+    while (k + 1 < batch.count && static_cast<int>(blockIdx.x) >= batch.block_begin[k + 1])
+        ++k;
+    const CopySegment &sg = batch.seg[k];
+    const int64_t first = static_cast<int64_t>(blockIdx.x - batch.block_begin[k]) * kCopyThreads + threadIdx.x;
+    const int64_t stride = static_cast<int64_t>(batch.block_begin[k + 1] - batch.block_begin[k]) * kCopyThreads;
     if (sg.vec16)
         copy_segment<uint4>(sg, first, stride);
     else
@@ -93,25 +98,22 @@ void add_segment(CopyBatch &b, const void *src, void *dst, int64_t row_bytes, in
     sg.vec16 = aligned16(src) && aligned16(dst) && row_bytes % 16 == 0 && (rows == 1 || (src_pitch % 16 == 0 && dst_pitch % 16 == 0));
 }
 
-int launch_copy(const CopyBatch &b, const char *family, cudaStream_t s)
+int launch_copy(CopyBatch &b, const char *family, cudaStream_t s)
 {
     if (b.count == 0)
         return 0;
-    int64_t max_words = 0;
+    const int64_t per_block = static_cast<int64_t>(kCopyThreads) * kCopyUnroll;
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8; // 8 CTAs of 256 threads = a full SM
+    b.block_begin[0] = 0;
     for (int i = 0; i < b.count; ++i)
     {
         const int64_t words = b.seg[i].row_bytes * b.seg[i].rows / (b.seg[i].vec16 ? 16 : 4);
-        max_words = words > max_words ? words : max_words;
+        int64_t blocks = (words + per_block - 1) / per_block;
+        blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+        b.block_begin[i + 1] = b.block_begin[i] + static_cast<int>(blocks);
     }
-    const int64_t per_block = static_cast<int64_t>(kCopyThreads) * kCopyUnroll;
-    int64_t blocks = (max_words + per_block - 1) / per_block;
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8; // 8 CTAs of 256 threads = a full SM
-    if (blocks > cap)
-        blocks = cap;
-    if (blocks < 1)
-        blocks = 1;
     KernelTimer timer(family, s);
-    storage_copy_kernel<<<dim3(static_cast<unsigned>(blocks), static_cast<unsigned>(b.count)), kCopyThreads, 0, s>>>(b);
+    storage_copy_kernel<<<static_cast<unsigned>(b.block_begin[b.count]), kCopyThreads, 0, s>>>(b);
     CPPRL_LAUNCH_CHECK("storage_copy_kernel");
     return 0;
 }

@@ -328,12 +328,21 @@ torch::Tensor PolicyImpl::get_probs(torch::Tensor inputs, torch::Tensor rnn_hxs,
 
 torch::Tensor PolicyImpl::get_values(torch::Tensor inputs, torch::Tensor rnn_hxs, torch::Tensor masks) const
 {
-    // bootstrap value for compute_returns: the fused forward with placeholder actions
+    // bootstrap value for compute_returns (policy.cpp:132-144): the value head of the fused forward
+    cpprl_b200_policy desc;
+    describe(desc);
     const int64_t B = inputs.size(0);
-    const bool discrete = action_space.type == "Discrete";
-    auto placeholder = discrete ? torch::zeros({B, 1}, torch::TensorOptions(torch::kLong).device(inputs.device()))
-                                : torch::zeros({B, action_space.shape.at(0)}, inputs.options().dtype(torch::kFloat));
-    return evaluate_actions(inputs, rnn_hxs, masks, placeholder)[0];
+    auto obs = detail::dense(inputs.reshape({B, -1}).to(torch::kFloat), "get_values: inputs");
+    auto value = torch::empty({B, 1}, obs.options());
+    torch::Tensor hxs, msk;
+    if (base->is_recurrent())
+    {
+        hxs = detail::dense(rnn_hxs.to(torch::kFloat), "get_values: rnn_hxs");
+        msk = detail::dense(masks.to(torch::kFloat).reshape({-1}), "get_values: masks");
+    }
+    check(cpprl_b200_get_values(&desc, fptr(obs), hxs.defined() ? fptr(hxs) : nullptr, hxs.defined() ? hxs.size(0) : 0,
+                                msk.defined() ? fptr(msk) : nullptr, B, fptr(value), current_stream(obs)));
+    return value;
 }
 
 void PolicyImpl::update_observation_normalizer(torch::Tensor observations)

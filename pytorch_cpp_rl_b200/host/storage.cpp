@@ -228,6 +228,16 @@ void RolloutStorage::compute_returns(torch::Tensor next_value, bool use_gae, flo
                                      rewards.size(1), use_gae ? 1 : 0, gamma, tau, current_stream(r)));
 }
 
+void RolloutStorage::bootstrap_returns(Policy &policy, bool use_gae, float gamma, float tau)
+{
+    // get_values(observations[-1], hidden_states[-1], masks[-1]) -> compute_returns (gym_client.cpp:266-275) in one call
+    cpprl_b200_policy pd;
+    policy->describe(pd);
+    cpprl_b200_storage st;
+    describe_storage(st);
+    check(cpprl_b200_bootstrap_returns(&pd, &st, use_gae ? 1 : 0, gamma, tau, current_stream(rewards)));
+}
+
 std::unique_ptr<Generator> RolloutStorage::feed_forward_generator(torch::Tensor advantages, int num_mini_batch)
 {
     const auto num_processes = actions.size(1);

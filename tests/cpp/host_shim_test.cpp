@@ -202,6 +202,107 @@ static void test_storage_write_side()
     CHECK(cpprl_b200_launch_count() > before);
 }
 
+// ---- combine constructor, checkpoint round trip, reward normaliser ------------------------------
+static void test_combine_checkpoint_reward_normaliser()
+{
+    std::printf("normaliser combine / checkpoint / reward normaliser\n");
+    auto opts = torch::TensorOptions().device(kDev);
+    { // observation_normalizer.cpp:145-190: 1, 2 and 3 device updates; unweighted means, counts summed to 6
+        std::vector<ObservationNormalizer> normalizers;
+        for (int i = 0; i < 3; ++i)
+        {
+            normalizers.push_back(ObservationNormalizer(3));
+            normalizers[i]->to(kDev);
+            for (int j = 0; j <= i; ++j)
+                normalizers[i]->update(torch::rand({3}).to(kDev));
+        }
+        ObservationNormalizer combined(normalizers);
+        auto mean = combined->get_mean(), var = combined->get_variance();
+        for (int k = 0; k < 3; ++k)
+        {
+            float m = 0, v = 0;
+            for (auto &n : normalizers)
+                m += n->get_mean()[k], v += n->get_variance()[k];
+            CHECK(std::fabs(mean[k] - m / 3) <= 1e-6f);
+            CHECK(std::fabs(var[k] - v / 3) <= 1e-6f);
+        }
+        CHECK(combined->get_step_count() == 6);
+        CHECK(std::fabs(combined->get_clip_value() - 10.f) <= 1e-6f);
+        // the combined normaliser is usable on the device after ->to()
+        combined->to(kDev);
+        auto y = combined->process_observation(torch::rand({4, 3}, opts));
+        CHECK((shape_of(y) == std::vector<int64_t>{4, 3}));
+    }
+    { // checkpoint: the kernels step the parameters and normaliser buffers IN PLACE; torch::save / torch::load must
+      // see those values (gym_client-style resume), and the restored policy must evaluate identically
+        torch::manual_seed(11);
+        ActionSpace space{"Box", {3}};
+        Policy policy(space, std::make_shared<MlpBase>(6, false, 64), true);
+        policy->to(kDev);
+        RolloutStorage storage(8, 16, {6}, space, 1, kDev);
+        PPO ppo(policy, 0.2, 2, 2, 1, 0.5, 1e-3, 1e-3, 1e-5, 0.5, 0.01);
+        auto obs = torch::randn({16, 6}, opts);
+        storage.set_first_observation(obs);
+        for (int t = 0; t < 8; ++t)
+        {
+            auto act = policy->act(obs, torch::Tensor(), torch::ones({16, 1}, opts));
+            obs = torch::randn({16, 6}, opts);
+            storage.insert(obs, torch::zeros({16, 1}, opts), act[1], act[2], act[0], torch::randn({16, 1}, opts), torch::ones({16, 1}, opts));
+        }
+        storage.compute_returns(policy->get_values(storage.get_observations()[-1], storage.get_hidden_states()[-1], storage.get_masks()[-1]),
+                                true, 0.99, 0.95);
+        auto before = policy->parameters()[0].clone();
+        ppo.update(storage);
+        CHECK(!torch::equal(before, policy->parameters()[0])); // the update moved the torch-visible tensors
+        const std::string path = "/tmp/cpprl_b200_policy_checkpoint.pt";
+        torch::save(policy, path);
+        torch::manual_seed(12); // different initial weights
+        Policy restored(space, std::make_shared<MlpBase>(6, false, 64), true);
+        restored->to(kDev);
+        torch::load(restored, path);
+        restored->to(kDev);
+        auto pa = policy->named_parameters(), pb = restored->named_parameters();
+        CHECK(pa.size() == pb.size());
+        for (auto &kv : pa)
+            CHECK(torch::equal(kv.value().cpu(), pb[kv.key()].cpu()));
+        auto ba = policy->named_buffers(), bb = restored->named_buffers();
+        for (auto &kv : ba)
+            CHECK(torch::equal(kv.value().cpu(), bb[kv.key()].cpu()));
+        CHECK(ba["observation_normalizer.rms.count"].item().toFloat() > 100.f); // 9 x 16 rows went through the kernel
+        auto x = torch::randn({32, 6}, opts), a = torch::randn({32, 3}, opts);
+        auto ea = policy->evaluate_actions(x, torch::Tensor(), torch::Tensor(), a);
+        auto eb = restored->evaluate_actions(x, torch::Tensor(), torch::Tensor(), a);
+        CHECK(torch::equal(ea[0], eb[0]));
+        CHECK(torch::equal(ea[1], eb[1]));
+        std::remove(path.c_str());
+    }
+    { // reward normaliser as the example driver uses it (gym_client.cpp:167,217-220): RunningMeanStd(1) over the
+      // discounted returns of all environments, on the device
+        const int num_envs = 32;
+        RunningMeanStd returns_rms(1);
+        returns_rms->to(kDev);
+        auto returns = torch::zeros({num_envs}, opts);
+        double count = 1e-4, mean = 0, var = 1; // float64 restatement of running_mean_std.cpp:20-43
+        torch::manual_seed(13);
+        for (int step = 0; step < 20; ++step)
+        {
+            auto reward = torch::randn({num_envs}) * 3 + 1;
+            returns = returns * 0.99 + reward.to(kDev);
+            returns_rms->update(returns);
+            auto r = returns.cpu().to(torch::kDouble);
+            const double bm = r.mean().item().toDouble(), bv = r.var(false).item().toDouble(), bc = num_envs;
+            const double delta = bm - mean, tot = count + bc;
+            const double m2 = var * count + bv * bc + delta * delta * count * bc / tot;
+            mean += delta * bc / tot;
+            var = m2 / tot;
+            count = tot;
+        }
+        CHECK(std::fabs(returns_rms->get_mean().item().toFloat() - mean) <= 1e-5 * std::fabs(mean) + 1e-6);
+        CHECK(std::fabs(returns_rms->get_variance().item().toFloat() - var) <= 1e-5 * var);
+        CHECK(returns_rms->get_count() == 20 * num_envs);
+    }
+}
+
 // ---- observation_normalizer.cpp:95-129 ----------------------------------------------------------------------------
 static void test_normalizer()
 {
@@ -489,6 +590,7 @@ int main()
     test_generators();
     test_storage_write_side();
     test_normalizer();
+    test_combine_checkpoint_reward_normaliser();
     test_policy_surface();
     test_learning();
     test_parity(true, false);

@@ -176,3 +176,42 @@ def test_rollout_step_is_graph_capturable():
     assert torch.equal(st.observations[1], obs)
     assert torch.equal(st.actions[0], want_action.view(N, A)) and torch.equal(st.value_predictions[0], want_value.view(N, 1))
     assert torch.equal(st.action_log_probs[0], want_logp.view(N, 1)) and torch.equal(st.rewards[0], reward)
+
+
+# ---- bootstrap value + returns as one call ---------------------------------------------------
+@pytest.mark.parametrize("cfg", ["cfg1", "cfg3", "cfg4", "cnn_small"])
+@pytest.mark.parametrize("use_gae", [True, False])
+def test_bootstrap_returns_equals_two_calls(cfg, use_gae):
+    """compute_returns(get_values(obs[T], hxs[T], masks[T])) (gym_client.cpp:266-275) fused into one C-ABI call gives
+    the bits of the two separate calls, and get_values gives the bits of evaluate_actions' value."""
+    from pytorch_cpp_rl_b200.workloads import CONFIGS, synth_rollout
+    from tests import helpers as H
+    import dataclasses
+    if cfg == "cnn_small":
+        w = dataclasses.replace(CONFIGS["cfg5"], T=4, N=8)
+    else:
+        w = CONFIGS[cfg]
+        w = dataclasses.replace(w, T=min(w.T, 16), N=min(w.N, 64))
+    r = synth_rollout(w, 3)
+    rng = np.random.default_rng(4)
+    n_params = api.Policy(api.ActionSpace("Discrete" if w.head == "categorical" else "Box", [w.num_actions]), w.obs_dim,
+                          normalize_observations=w.normalize_obs, hidden=w.hidden, recurrent=(w.base == "gru"),
+                          obs_shape=w.obs_shape if w.base == "cnn" else None).params.numel()
+    params = (rng.standard_normal(n_params) * 0.05).astype(np.float32)
+    policy, st = H.make_gpu_side(w, r, params)
+    policy2, st2 = H.make_gpu_side(w, r, params)
+    T, N = w.T, w.N
+    obs_T, hxs_T, masks_T = st.observations[T], st.hidden_states[T], st.masks[T]
+    next_value = policy.get_values(obs_T, hxs_T, masks_T)
+    if w.head == "categorical":
+        placeholder = torch.zeros(N, 1, dtype=torch.int64, device="cuda")
+    else:
+        placeholder = torch.zeros(N, w.num_actions, device="cuda")
+    want_value = policy.evaluate_actions(obs_T.contiguous(), hxs_T.contiguous() if w.base == "gru" else None,
+                                         masks_T.contiguous() if w.base == "gru" else None, placeholder)[0]
+    assert torch.equal(next_value, want_value)
+    st.compute_returns(next_value, use_gae, w.gamma, w.tau)
+    st2.bootstrap_returns(policy2, use_gae, w.gamma, w.tau)
+    assert torch.equal(st.returns, st2.returns)
+    assert torch.equal(st.value_predictions, st2.value_predictions)
+    assert float(st2.returns[:T].abs().sum()) > 0
