@@ -139,6 +139,7 @@ struct ObsIm2col
     const long long *perm;
     long long row_base;
     int rows, C;
+    const int *tf32_inexact; // nullable; see ExactFlagOf in cnn_gemm_tc.cuh
     __device__ __forceinline__ RowCtx row(int r) const
     {
         const bool ok = r < rows * kCnnP1;
@@ -804,6 +805,45 @@ __global__ void __launch_bounds__(256) cnn_optimizer_kernel(const CnnUpdateArgs 
 }
 } // namespace
 
+// ---- TF32 exactness of the observations ------------------------------------------------------------------------------------
+namespace
+{
+__global__ void __launch_bounds__(256) cnn_obs_scan_kernel(const float *__restrict__ obs, long long n4, long long n, int *__restrict__ flag)
+{
+    unsigned int low = 0u;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride)
+    {
+        const float4 v = ld_stream4(obs + 4 * i);
+        low |= __float_as_uint(v.x) | __float_as_uint(v.y) | __float_as_uint(v.z) | __float_as_uint(v.w);
+    }
+    if (blockIdx.x == 0 && threadIdx.x < n - 4 * n4)
+        low |= __float_as_uint(obs[4 * n4 + threadIdx.x]);
+    if (__any_sync(0xffffffffu, (low & 0x1fffu) != 0u) && (threadIdx.x & 31) == 0)
+        *flag = 1;
+}
+} // namespace
+
+int cnn_scan_observations(const float *obs, long long n, int *flag, cudaStream_t s)
+{
+    CPPRL_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), s));
+    if (n <= 0)
+        return 0;
+    const char *off = std::getenv("CPPRL_B200_CNN_NO_EXACT"); // A/B switch for tests and measurements
+    if ((reinterpret_cast<uintptr_t>(obs) & 15u) != 0 || (off && off[0] == '1'))
+    { // unaligned view (or switched off): keep the full path
+        CPPRL_CUDA_TRY(cudaMemsetAsync(flag, 1, sizeof(int), s));
+        return 0;
+    }
+    const long long n4 = n / 4;
+    long long blocks = (n4 + 256 * 8 - 1) / (256 * 8);
+    const long long cap = static_cast<long long>(sm_count()) * 8;
+    blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
+    cnn_obs_scan_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(obs, n4, n, flag);
+    CPPRL_LAUNCH_CHECK("cnn_obs_scan_kernel");
+    return 0;
+}
+
 // ---- host orchestration -------------------------------------------------------------------------------------------------
 namespace
 {
@@ -884,7 +924,7 @@ int cnn_forward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, i
 {
     const int K1 = a.C * 64;
     const float *img = ws.img;
-    if (int rc = launch_gemm<256, 32, 8, 4, false>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C},
+    if (int rc = launch_gemm<256, 32, 8, 4, false>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C, a.obs_inexact},
                                                    MatLoad{img + a.il.w1, K1, kCnnC1},
                                                    BiasReluStore{ws.act1, a.params + a.po.b1, kCnnC1, 255.f}, rows * kCnnP1, kCnnC1,
                                                    K1, 1, false, stop, s))
@@ -971,7 +1011,7 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
                                                    s))
         return rc;
     // conv1 (its input needs no gradient)
-    if (int rc = launch_gemm<256, 32, 8, 4, true>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C},
+    if (int rc = launch_gemm<256, 32, 8, 4, true>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C, a.obs_inexact},
                                                   MatLoad{ws.dz1, rows * kCnnP1, kCnnC1},
                                                   AtomicAddStore{ws.gimg + a.il.w1, kCnnC1, 255.f}, K1, kCnnC1, rows * kCnnP1,
                                                   splits_for((K1 + 255) / 256 * (use_tensor_cores() ? 2 : 1), static_cast<long long>(rows) * kCnnP1), true,

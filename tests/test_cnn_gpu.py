@@ -41,8 +41,10 @@ def test_evaluate_actions_cnn_vs_reference(ref, head, B, C):
     np.testing.assert_allclose(float(out[2]), ent, rtol=5e-5)
 
 
-def _run_cnn_ppo(ref, w, seed, n_updates=2):
+def _run_cnn_ppo(ref, w, seed, n_updates=2, mutate=None):
     r = synth_rollout(w, seed)
+    if mutate is not None:
+        mutate(r)
     sess = H.make_ref_session(ref, w, init_seed=seed)
     H.fill_policy_outputs(sess, w, r)
     H.ref_load_rollout(sess, r)
@@ -94,6 +96,47 @@ def test_ppo_update_cnn_multi_pass(ref):
         _run_cnn_ppo(ref, _cnn(), 1, n_updates=1)
     finally:
         del os.environ["CPPRL_B200_CNN_CHUNK"]
+
+
+def test_ppo_update_cnn_fractional_pixels(ref):
+    """Observations OFF the TF32 grid (frames with fractional values): the per-update scan must flag them and conv1
+    must keep all three TF32 products — same tolerances against the reference as the integer-pixel case."""
+    def jitter(r):
+        rng = np.random.default_rng(9)
+        r["observations"] += rng.random(r["observations"].shape, np.float32) * 0.999
+        assert (r["observations"].view(np.uint32) & 0x1fff).any()
+    _run_cnn_ppo(ref, _cnn(), 0, n_updates=1, mutate=jitter)
+
+
+def test_cnn_exact_pixel_path_same_bits():
+    """Raw 0..255 pixels lie on the TF32 grid, so conv1 drops the A_lo x B_hi product (cnn_gemm_tc.cuh): the skipped
+    product is exactly zero, hence the results are those of the full three-product path (up to the run-to-run order of
+    the weight gradients' fp32 atomics)."""
+    w = _cnn()
+    r = synth_rollout(w, 5)
+    assert not (r["observations"].view(np.uint32) & 0x1fff).any()
+    results = []
+    for switch in ("0", "1"):
+        os.environ["CPPRL_B200_CNN_NO_EXACT"] = switch
+        try:
+            n_params = sum(int(np.prod(shape)) for _, shape in api.cnn_param_shapes(w.obs_shape[0], w.num_actions, "Discrete"))
+            params = (np.random.default_rng(6).standard_normal(n_params) * 0.03).astype(np.float32)
+            policy, st = H.make_gpu_side(w, r, params)
+            algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef,
+                           w.entropy_coef, w.learning_rate, w.epsilon, 0.5, w.kl_target)
+            st.compute_returns(torch.from_numpy(r["next_value"]).cuda(), w.use_gae, w.gamma, w.tau)
+            stats = algo.update(st, 1.0, perms=H.draw_perms(77, w.rows, w.num_epoch))
+            a2c = api.A2C(policy, 1.0, w.value_loss_coef, w.entropy_coef, 7e-4, w.epsilon, w.alpha)
+            stats += a2c.update(st, 1.0)
+            results.append((policy.params.clone(), [d.value for d in stats]))
+        finally:
+            del os.environ["CPPRL_B200_CNN_NO_EXACT"]
+    # not bitwise: the weight gradients are reduced with fp32 atomics, whose order changes from run to run
+    err = (results[0][0] - results[1][0]).abs() / results[1][0].abs().clamp_min(w.learning_rate)
+    e = err.cpu().numpy()  # near-dead units take sign-like Adam steps (see _run_cnn_ppo): bulk tight, bounded tail
+    assert np.quantile(e, 0.99) <= 1e-5 and e.max() <= 0.5, (np.quantile(e, 0.99), e.max())
+    np.testing.assert_allclose(results[0][1], results[1][1], rtol=1e-5, atol=1e-7)
+    assert float((results[0][0] - torch.from_numpy(params).cuda()).abs().max()) > 0
 
 
 def test_ppo_update_cnn_normal_head(ref):
