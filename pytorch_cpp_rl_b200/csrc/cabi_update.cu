@@ -637,9 +637,9 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         cnn_workspace_carve(h->cws, h->scratch.tape, c.C, c.A, chunk, true);
         c.obs = ro->d_observations;
         // one pass over the frames this update reads (0.6 ms for cfg5's 3.7 GB): raw pixels sit on the TF32 grid and
-        // conv1's two GEMMs then run one MMA per k-step instead of two, with the same bits out
-        c.obs_inexact = cnn_inexact_flag(h->cws);
-        if (int rc = cnn_scan_observations(c.obs, local_rows * policy->obs_dim, cnn_inexact_flag(h->cws), h->stream))
+        // conv1's two GEMMs then run the instantiation with one MMA per k-step instead of two, same bits out (one stream
+        // synchronisation brings the answer to the host)
+        if (int rc = cnn_scan_observations(c.obs, local_rows * policy->obs_dim, cnn_inexact_flag(h->cws), &c.obs_exact, h->stream))
             return rc;
         c.actions = ro->d_actions;
         c.value_preds = ro->d_value_preds;
@@ -1173,8 +1173,7 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
         CnnWorkspace ws;
         cnn_workspace_carve(ws, h->scratch.tape, c.C, c.A, chunk, true);
         c.obs = ro->d_observations;
-        c.obs_inexact = cnn_inexact_flag(ws);
-        if (int rc = cnn_scan_observations(c.obs, rows * policy->obs_dim, cnn_inexact_flag(ws), s))
+        if (int rc = cnn_scan_observations(c.obs, rows * policy->obs_dim, cnn_inexact_flag(ws), &c.obs_exact, s))
             return rc;
         c.actions = ro->d_actions;
         c.value_preds = ro->d_value_preds;

@@ -107,22 +107,19 @@ __host__ __device__ constexpr int a_lbo_bytes() { return (kBM / 8) * kGroupBytes
 __host__ __device__ constexpr int a_operand_bytes() { return (kBK / 4) * a_lbo_bytes(); }
 __host__ __device__ constexpr size_t smem_bytes(int BN) { return static_cast<size_t>(2) * 2 * (a_operand_bytes() + operand_bytes(BN)) + 64; }
 
-// A loader may carry `const int *tf32_inexact` (device, nullable): when it points at 0 every element the loader yields is
-// ON the TF32 grid (raw 0..255 pixels are), so A_lo == 0 exactly, the A_lo x B_hi product contributes exactly nothing
-// and is skipped together with the lo plane's split and shared-memory stores: one MMA per k-step instead of two, same
-// bits out.  The flag is data dependent (cnn_obs_scan_kernel checks every observation once per update); a loader
-// without the member, a null pointer or a non-zero flag select the full three-product path.
+// A loader type may declare `static constexpr bool kTf32Exact = true`: every element it yields is ON the TF32 grid (raw
+// 0..255 pixels are), so A_lo == 0 exactly, the A_lo x B_hi product contributes exactly nothing and is compiled out
+// together with the lo plane's split and shared-memory stores: one MMA per k-step instead of two, same bits out.
+// The host picks that loader type only after cnn_obs_scan_kernel has checked every observation of the update.
 template <class L, class = void>
-struct ExactFlagOf
+struct ExactOf
 {
-    static constexpr bool kHas = false;
-    static __device__ __forceinline__ const int *get(const L &) { return nullptr; }
+    static constexpr bool value = false;
 };
 template <class L>
-struct ExactFlagOf<L, decltype(void(L::tf32_inexact))>
+struct ExactOf<L, decltype(void(L::kTf32Exact))>
 {
-    static constexpr bool kHas = true;
-    static __device__ __forceinline__ const int *get(const L &l) { return l.tf32_inexact; }
+    static constexpr bool value = L::kTf32Exact;
 };
 
 // A_T: A(m, k) = X[k][m] (the loader's vectors run along m: transposed on the way into shared memory); else
@@ -146,12 +143,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
     // lines instead of 32 (the L1 wavefront count had been the limiter of those kernels).  The thread then owns the
     // same k chunk of four rows (four row contexts).  conv1's NCHW gather keeps lanes along the output pixels.
     constexpr bool ALONG_K = !A_T && ALoad::kLanesAlongK;
-    bool a_exact = false; // uniform over the grid
-    if (ExactFlagOf<ALoad>::kHas)
-    {
-        const int *flag = ExactFlagOf<ALoad>::get(al);
-        a_exact = flag != nullptr && __ldg(flag) == 0;
-    }
+    constexpr bool A_EXACT = ExactOf<ALoad>::value;
     uint64_t *mbar = reinterpret_cast<uint64_t *>(tc_smem + 2 * STAGE_BYTES);
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(mbar + 2);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -247,7 +239,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         // an exact A has no lo plane: the values go to shared memory as they are
         auto store_a = [&](int off, const float4 &x)
         {
-            if (ExactFlagOf<ALoad>::kHas && a_exact)
+            if (A_EXACT)
                 *reinterpret_cast<float4 *>(a_hi + off) = x;
             else
                 store_split(a_hi, a_lo, off, x);
@@ -291,7 +283,7 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         {
             const uint32_t a_off = (s * STAGE_BYTES + j * 2 * A_LBO) >> 4, b_off = (s * STAGE_BYTES + 2 * A_BYTES + j * 2 * B_LBO) >> 4;
             mma_tf32_halves(acc, a_desc_lo + a_off, b_desc_lo + b_off, desc_hi, idesc2, (first_tile && j == 0) ? 0u : 1u); // [hi*hi | hi*lo]
-            if (!(ExactFlagOf<ALoad>::kHas && a_exact))
+            if (!A_EXACT)
                 mma_tf32_halves(acc, a_desc_lo + a_off + (A_BYTES >> 4), b_desc_lo + b_off, desc_hi, idesc, 1u); // lo*hi into the first half
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(&mbar[s]))

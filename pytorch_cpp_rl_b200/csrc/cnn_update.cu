@@ -139,7 +139,6 @@ struct ObsIm2col
     const long long *perm;
     long long row_base;
     int rows, C;
-    const int *tf32_inexact; // nullable; see ExactFlagOf in cnn_gemm_tc.cuh
     __device__ __forceinline__ RowCtx row(int r) const
     {
         const bool ok = r < rows * kCnnP1;
@@ -160,6 +159,12 @@ struct ObsIm2col
     __device__ __forceinline__ int tile_part(int k0) const { return (k0 >> 6) * (kCnnIn * kCnnIn) + ((k0 & 32) >> 3) * kCnnIn; }
     __device__ __forceinline__ float4 load_parts(const RowCtx &ctx, int part, int k) const { return ld_or_zero(ctx.p, part, k < ctx.lim); }
     __device__ __forceinline__ float4 operator()(int r, int k) const { return load(row(r), k); }
+};
+
+// the same loader for frames known to lie on the TF32 grid (see ExactOf in cnn_gemm_tc.cuh)
+struct ObsIm2colExact : ObsIm2col
+{
+    static constexpr bool kTf32Exact = true;
 };
 
 // im2col of an NHWC activation: X[(i, oy, ox)][(ky, kx, c)]
@@ -824,23 +829,23 @@ __global__ void __launch_bounds__(256) cnn_obs_scan_kernel(const float *__restri
 }
 } // namespace
 
-int cnn_scan_observations(const float *obs, long long n, int *flag, cudaStream_t s)
+int cnn_scan_observations(const float *obs, long long n, int *flag, int *exact, cudaStream_t s)
 {
-    CPPRL_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), s));
-    if (n <= 0)
-        return 0;
+    *exact = 0;
     const char *off = std::getenv("CPPRL_B200_CNN_NO_EXACT"); // A/B switch for tests and measurements
-    if ((reinterpret_cast<uintptr_t>(obs) & 15u) != 0 || (off && off[0] == '1'))
-    { // unaligned view (or switched off): keep the full path
-        CPPRL_CUDA_TRY(cudaMemsetAsync(flag, 1, sizeof(int), s));
-        return 0;
-    }
+    if (n <= 0 || (reinterpret_cast<uintptr_t>(obs) & 15u) != 0 || (off && off[0] == '1'))
+        return 0; // nothing to scan, an unaligned view, or switched off: keep the full path
+    CPPRL_CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(int), s));
     const long long n4 = n / 4;
     long long blocks = (n4 + 256 * 8 - 1) / (256 * 8);
     const long long cap = static_cast<long long>(sm_count()) * 8;
     blocks = blocks > cap ? cap : (blocks < 1 ? 1 : blocks);
     cnn_obs_scan_kernel<<<static_cast<unsigned>(blocks), 256, 0, s>>>(obs, n4, n, flag);
     CPPRL_LAUNCH_CHECK("cnn_obs_scan_kernel");
+    int inexact = 1;
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(&inexact, flag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CPPRL_CUDA_TRY(cudaStreamSynchronize(s));
+    *exact = inexact == 0;
     return 0;
 }
 
@@ -924,10 +929,12 @@ int cnn_forward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, i
 {
     const int K1 = a.C * 64;
     const float *img = ws.img;
-    if (int rc = launch_gemm<256, 32, 8, 4, false>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C, a.obs_inexact},
-                                                   MatLoad{img + a.il.w1, K1, kCnnC1},
-                                                   BiasReluStore{ws.act1, a.params + a.po.b1, kCnnC1, 255.f}, rows * kCnnP1, kCnnC1,
-                                                   K1, 1, false, stop, s))
+    const ObsIm2col obs_rows{a.obs, a.perm, a.row_base + base, rows, a.C};
+    const MatLoad w1{img + a.il.w1, K1, kCnnC1};
+    const BiasReluStore act1_out{ws.act1, a.params + a.po.b1, kCnnC1, 255.f};
+    if (int rc = a.obs_exact ? launch_gemm<256, 32, 8, 4, false>(ObsIm2colExact{obs_rows}, w1, act1_out, rows * kCnnP1, kCnnC1, K1, 1,
+                                                                 false, stop, s)
+                             : launch_gemm<256, 32, 8, 4, false>(obs_rows, w1, act1_out, rows * kCnnP1, kCnnC1, K1, 1, false, stop, s))
         return rc;
     if (int rc = launch_gemm<128, 64, 8, 4, false>(ActIm2col<kCnnO1, kCnnO2, 4, 2, kCnnC1>{ws.act1, rows},
                                                    MatLoad{img + a.il.w2, kCnnK2, kCnnC2},
@@ -1011,11 +1018,12 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
                                                    s))
         return rc;
     // conv1 (its input needs no gradient)
-    if (int rc = launch_gemm<256, 32, 8, 4, true>(ObsIm2col{a.obs, a.perm, a.row_base + base, rows, a.C, a.obs_inexact},
-                                                  MatLoad{ws.dz1, rows * kCnnP1, kCnnC1},
-                                                  AtomicAddStore{ws.gimg + a.il.w1, kCnnC1, 255.f}, K1, kCnnC1, rows * kCnnP1,
-                                                  splits_for((K1 + 255) / 256 * (use_tensor_cores() ? 2 : 1), static_cast<long long>(rows) * kCnnP1), true,
-                                                  stop, s))
+    const ObsIm2col obs_rows{a.obs, a.perm, a.row_base + base, rows, a.C};
+    const MatLoad dz1{ws.dz1, rows * kCnnP1, kCnnC1};
+    const AtomicAddStore gw1{ws.gimg + a.il.w1, kCnnC1, 255.f};
+    const int z1 = splits_for((K1 + 255) / 256 * (use_tensor_cores() ? 2 : 1), static_cast<long long>(rows) * kCnnP1);
+    if (int rc = a.obs_exact ? launch_gemm<256, 32, 8, 4, true>(ObsIm2colExact{obs_rows}, dz1, gw1, K1, kCnnC1, rows * kCnnP1, z1, true, stop, s)
+                             : launch_gemm<256, 32, 8, 4, true>(obs_rows, dz1, gw1, K1, kCnnC1, rows * kCnnP1, z1, true, stop, s))
         return rc;
     return launch_colsum(ws.dz1, static_cast<long long>(rows) * kCnnP1, kCnnC1, ws.gflat + a.po.b1, stop, s);
 }

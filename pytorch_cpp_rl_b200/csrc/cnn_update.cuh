@@ -50,9 +50,9 @@ struct CnnUpdateArgs
     CnnImageLayout il;
     int C, A, head;
     const float *obs;      // [rows(+N), C, 84, 84] raw pixels 0..255 (divided by 255 in the load, cnn_base.cpp:37)
-    // nullable device flag: 0 = every observation lies on the TF32 grid (raw 0..255 pixels do), written by
-    // cnn_scan_observations once per update; lets conv1's GEMMs drop the A_lo x B_hi product (cnn_gemm_tc.cuh)
-    const int *obs_inexact;
+    // non-zero: cnn_scan_observations found every observation of this update on the TF32 grid (raw 0..255 pixels
+    // are); conv1's GEMMs then run the instantiation without the A_lo x B_hi product (cnn_gemm_tc.cuh)
+    int obs_exact;
     const void *actions;
     const float *value_preds, *returns, *old_logp;
     long long rows;
@@ -81,8 +81,9 @@ CnnParamOffsets cnn_param_offsets(int C, int A, int head);
 CnnImageLayout cnn_image_layout(int C);
 size_t cnn_workspace_floats(int C, int A, int chunk, bool training);
 void cnn_workspace_carve(CnnWorkspace &ws, float *base, int C, int A, int chunk, bool training);
-// *flag = 1 if any of the n floats at obs has bits below the TF32 mantissa, else 0 (flag: one int of device memory)
-int cnn_scan_observations(const float *obs, long long n, int *flag, cudaStream_t s);
+// *exact = 1 if none of the n floats at obs has bits below the TF32 mantissa (flag: one int of device scratch; the
+// call synchronises the stream once to bring the answer to the host: the kernel variant is a host-side choice)
+int cnn_scan_observations(const float *obs, long long n, int *flag, int *exact, cudaStream_t s);
 inline int *cnn_inexact_flag(const CnnWorkspace &ws) { return reinterpret_cast<int *>(ws.consts + 8); } // padding of consts
 int cnn_build_images(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s);
 int cnn_minibatch(const CnnUpdateArgs &a, const CnnWorkspace &ws, cudaStream_t s); // forward + backward + decide + optimiser
