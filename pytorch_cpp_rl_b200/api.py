@@ -121,6 +121,30 @@ class ObservationNormalizer:
     def update(self, observations: torch.Tensor) -> None:
         self.rms.update(observations)
 
+    def get_step_count(self) -> int:  # observation_normalizer.h / running_mean_std.h:25: truncated to int
+        return int(self.rms.count.item())
+
+    @classmethod
+    def combine(cls, others: Sequence["ObservationNormalizer"], device="cuda") -> "ObservationNormalizer":
+        """The combining constructor (observation_normalizer.cpp:19-67): UNWEIGHTED means of the others' clips, means
+        and variances, step counts truncated and summed — host bookkeeping over small buffers, as in the reference."""
+        n = len(others)
+        out = cls(others[0].rms.mean.numel(), 0.0, device)
+        clip = torch.zeros(1, dtype=torch.float32)
+        mean = torch.zeros(out.rms.mean.numel(), dtype=torch.float32)
+        var = torch.zeros_like(mean)
+        total = 0
+        for o in others:
+            clip += o.clip.cpu()
+            mean += o.rms.mean.cpu()
+            var += o.rms.variance.cpu()
+            total += o.get_step_count()
+        out.clip.copy_(clip / n)
+        out.rms.mean.copy_(mean / n)
+        out.rms.variance.copy_(var / n)
+        out.rms.count.fill_(total + 1e-8)  # set_count, running_mean_std.h:28
+        return out
+
 
 class Policy:
     """Flat-parameter policy (MlpBase, GRU-fronted MlpBase or CnnBase + Categorical / Normal head).  `params` is

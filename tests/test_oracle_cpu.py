@@ -238,3 +238,19 @@ def test_rollout_concatenate_known_answer():
                      "actions", "masks"):
             assert np.array_equal(getattr(joined, name)[:, i:i + 1], getattr(p, name)), name
     assert np.array_equal(joined.rewards[:, 0, 0], [1, 2, 3]) and np.array_equal(joined.masks[:, 0, 0], [1, 1, 0, 1])
+
+
+def test_combine_normalizers_known_answer():
+    """src/observation_normalizer.cpp:145-190: three normalisers after 1, 2 and 3 updates; the combination holds the
+    unweighted means of their means / variances and a step count of 6."""
+    rng = np.random.default_rng(2)
+    others = []
+    for i in range(3):
+        rms = O.RunningMeanStd(3)
+        for _ in range(i + 1):
+            rms.update(rng.random(3, np.float32))
+        others.append((10.0, rms))
+    clip, combined = O.combine_normalizers(others)
+    np.testing.assert_allclose(combined.mean, np.mean([r.mean for _, r in others], axis=0), rtol=1e-6)
+    np.testing.assert_allclose(combined.variance, np.mean([r.variance for _, r in others], axis=0), rtol=1e-6)
+    assert int(combined.count[0]) == 6 and clip == np.float32(10.0)

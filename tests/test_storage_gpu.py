@@ -215,3 +215,25 @@ def test_bootstrap_returns_equals_two_calls(cfg, use_gae):
     assert torch.equal(st.returns, st2.returns)
     assert torch.equal(st.value_predictions, st2.value_predictions)
     assert float(st2.returns[:T].abs().sum()) > 0
+
+
+# ---- the combining constructor of the observation normaliser ------------------------------------
+def test_observation_normalizer_combine():
+    """observation_normalizer.cpp:19-67 and its test :145-190 on device normalisers (1, 2 and 3 kernel updates)."""
+    rng = np.random.default_rng(8)
+    gpu, ref = [], []
+    for i in range(3):
+        n, rms = api.ObservationNormalizer(3), O.RunningMeanStd(3)
+        for _ in range(i + 1):
+            x = rng.random((1, 3), np.float32)
+            n.update(torch.from_numpy(x).cuda())
+            rms.update(x)
+        gpu.append(n)
+        ref.append((10.0, rms))
+    combined = api.ObservationNormalizer.combine(gpu)
+    clip, want = O.combine_normalizers(ref)
+    np.testing.assert_allclose(combined.rms.mean.cpu().numpy(), want.mean, rtol=1e-5, atol=1e-7)
+    np.testing.assert_allclose(combined.rms.variance.cpu().numpy(), want.variance, rtol=1e-5, atol=1e-7)
+    assert combined.get_step_count() == 6 and float(combined.clip) == float(clip)
+    y = combined.process_observation(torch.from_numpy(rng.random((4, 3), np.float32)).cuda())  # usable on the device
+    assert y.shape == (4, 3) and bool(torch.isfinite(y).all())
