@@ -104,16 +104,36 @@ def make_ref_session(w: Workload, seed: int):
     return ref, sess, r
 
 
-def cpu_sample_workload(w: Workload) -> Workload:
-    """Bounded sample of the workload for the CPU arms: the recurrent and convolutional updates take tens of seconds to
-    minutes per update on the host, so they are timed on fewer environments of the same shape (same rows per
-    minibatch pass for the GRU: one environment; 1/32 of the rows per minibatch for the CNN) -- transitions/s is
-    per-row work either way."""
+def cpu_sample_workload(w: Workload):
+    """Bounded sample of the workload for the CPU arms -> (sample workload, fraction of the full update it covers).
+    The recurrent and convolutional updates take tens of seconds to minutes per update on the host.  The GRU sample is
+    fewer environments with the reference's own minibatch shape (one environment x T steps per minibatch either way);
+    the CNN sample keeps the FULL rollout and the full 8192-row minibatches and runs ONE of the epochs (small conv
+    batches would understate the CPU's per-row throughput), its time is scaled by the epoch count."""
     if w.base == "gru" and w.N > 32:
-        return w.scaled(N=32, num_mini_batch=32)
-    if w.base == "cnn" and w.N > 8:
-        return w.scaled(N=8)
-    return w
+        return w.scaled(N=32, num_mini_batch=32), 1.0
+    if w.base == "cnn" and w.algo == "ppo" and w.num_epoch > 1:
+        return w.scaled(num_epoch=1), 1.0 / w.num_epoch
+    return w, 1.0
+
+
+def config_of(w: Workload, world: int) -> dict:
+    """The `config` object of the JSON line: the SAME for the GPU arm and the reference arm of one workload."""
+    return {"workload": f"{w.name}: {w.description}", "rows_per_step": w.rows, "optimizer_steps": w.optimizer_steps,
+            "l2": "GPU arm: flushed between timed iterations (256 MiB write)",
+            "parallelism": "single GPU" if world == 1 else
+            f"{world} independent replicas (the recurrent path does not shard: SURVEY 8e)" if w.base == "gru" else
+            f"dp{world}: {world * w.N} envs sharded by environment over {world} GPUs ({w.N} per GPU), global "
+            f"minibatch {world * w.rows // max(1, w.num_mini_batch)} rows, gradient all-reduce "
+            + ("kernel between backward and optimiser" if w.base == "cnn" else "inside the fused kernel") +
+            " over NVLink peer memory"}
+
+
+def sample_text(ws: Workload, full: Workload, frac: float) -> str:
+    if frac != 1.0:
+        return (f"{ws.num_epoch} of the {full.num_epoch} epochs of the full {full.name} rollout at the full minibatch size "
+                f"({ws.rows // max(1, ws.num_mini_batch)} rows), time scaled by {1 / frac:.0f}")
+    return f"{ws.N} of the {full.N} environments of {full.name} ({ws.rows} rows, same rows per minibatch)"
 
 
 def time_reference(w: Workload, steps: int, warmup: int, threads: int, budget_s: float = 1e9):
@@ -139,20 +159,20 @@ def run_reference(args, w: Workload, rank: int, world: int):
         return
     threads = os.cpu_count() or 1
     full = w
-    w = cpu_sample_workload(w)
+    w, frac = cpu_sample_workload(w)
     sampled = w is not full
     sec, done, tv = time_reference(w, args.steps, min(args.warmup, 1) if sampled else args.warmup, threads,
                                    budget_s=120.0 if sampled else 1e9)
+    sec /= frac  # a sample that runs a fraction of the epochs stands for that fraction of the update's time
     value = w.rows / sec
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{w.name}: {w.description}", "reference": f"oracle/_ref (libtorch {tv} CPU)"},
+        "config": config_of(full, args.gpus), "reference_build": f"oracle/_ref (libtorch {tv} CPU)",
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference",
                          "sample": f"{done} x (compute_returns + update) of " +
-                                   (f"{w.N} of the {full.N} environments of {w.name} ({w.rows} rows)" if sampled
-                                    else f"the full {w.name} rollout")},
+                                   (sample_text(w, full, frac) if sampled else f"the full {w.name} rollout")},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -430,14 +450,15 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     cpu = None
     if world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        ws = cpu_sample_workload(w)
+        ws, frac = cpu_sample_workload(w)
         sampled = ws is not w
         wu = 1 if sampled else 2
-        secN, doneN, tv = time_reference(ws, 50, wu, threads, budget_s=8.0)
+        secN, doneN, tv = time_reference(ws, 50, wu, threads, budget_s=20.0 if sampled else 8.0)
+        secN /= frac
         # the single-thread leg only where it can win (small MLP rollouts); the heavy bases scale with threads
         sec1, done1 = (secN * threads, 0) if sampled else time_reference(ws, 50, wu, 1, budget_s=8.0)[:2]
         best, cores, done = (sec1, 1, done1) if sec1 <= secN else (secN, threads, doneN)
-        what = f"{ws.N} of the {w.N} environments of {w.name} ({ws.rows} rows)" if sampled else f"the full {w.name} rollout"
+        what = sample_text(ws, w, frac) if sampled else f"the full {w.name} rollout"
         cpu = {"value": ws.rows / best, "unit": UNIT, "cores": cores, "kind": "reference",
                "sample": f"{done} x (compute_returns + update) of {what}, oracle/_ref libtorch {tv}",
                "value_1_thread": (ws.rows / sec1) if done1 else None, "value_all_threads": ws.rows / secN,
@@ -447,14 +468,7 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"{w.name}: {w.description}", "rows_per_step": w.rows, "optimizer_steps": w.optimizer_steps,
-                   "l2": "flushed between timed iterations (256 MiB write)",
-                   "parallelism": "single GPU" if world == 1 else
-                   f"{world} independent replicas (the recurrent path does not shard: SURVEY 8e)" if w.base == "gru" else
-                   f"dp{world}: {world * w.N} envs sharded by environment over {world} GPUs ({w.N} per GPU), global "
-                   f"minibatch {world * w.rows // max(1, w.num_mini_batch)} rows, gradient all-reduce "
-                   + ("kernel between backward and optimiser" if w.base == "cnn" else "inside the fused kernel") +
-                   " over NVLink peer memory"},
+        "config": config_of(w, world),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": side.h2d_bytes, "d2h_bytes_per_step": side.d2h_bytes,
                 "ms_per_step": e2e_s * 1e3,
                 "permutations": "device (sharded update)" if world > 1 and w.base != "gru" else "host torch.randperm, the reference's CPU random stream",

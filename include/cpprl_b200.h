@@ -296,6 +296,10 @@ int cpprl_b200_a2c_set_comm(cpprl_b200_a2c *h, cpprl_b200_comm *comm, int64_t gl
 /* RunningMeanStd update whose batch is the union of every rank's rows x [M_local, D]. */
 int cpprl_b200_rms_update_sharded(cpprl_b200_comm *comm, const float *d_x, int64_t M, int64_t D, float *d_count,
                                   float *d_mean, float *d_var, void *d_workspace, void *stream);
+/* Synchronises `stream` and returns CPPRL_B200_ENCCL if a sharded normaliser update on this communicator gave up
+ * waiting for a peer (the statistics were left untouched in that case), 0 otherwise.  The PPO / A2C updates report
+ * the same condition through their fetch_stats. */
+int cpprl_b200_comm_check(cpprl_b200_comm *comm, void *stream);
 
 /* ---- (f2) the write side of the rollout buffer ------------------------------------------------------
  * Writable description of a RolloutStorage (src/storage.cpp:15-49), every buffer time-major contiguous. */

@@ -119,6 +119,7 @@ SIGNATURES = {
     "cpprl_b200_ppo_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64]),
     "cpprl_b200_a2c_set_comm": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "cpprl_b200_rms_update_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64] + [C.c_void_p] * 5),
+    "cpprl_b200_comm_check": (C.c_int, [C.c_void_p, C.c_void_p]),
     "cpprl_b200_storage_insert": (C.c_int, [C.POINTER(Storage), C.c_int64] + [C.c_void_p] * 8),
     "cpprl_b200_storage_after_update": (C.c_int, [C.POINTER(Storage), C.c_void_p]),
     "cpprl_b200_storage_set_first_observation": (C.c_int, [C.POINTER(Storage), C.c_void_p, C.c_void_p]),

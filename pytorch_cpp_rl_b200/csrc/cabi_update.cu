@@ -4,7 +4,9 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
+#include <utility>
 #include <vector>
 
 #include <curand_kernel.h>
@@ -21,10 +23,11 @@ namespace cpprl_b200
 // from mlp_update.cu / returns_scan.cu
 size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta);
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s);
-int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums,
+int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums, void *d_ws,
                              cudaStream_t s);
+size_t advantage_workspace_bytes();
 int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean, float *d_var,
-                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s);
+                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s, int *d_comm_error);
 int launch_shard_permutation(const int64_t *d_perm, int64_t n_mb, int64_t B, int64_t n_global, int64_t env0,
                              int64_t n_local, int64_t *d_out, int *d_counts, cudaStream_t s);
 CommView comm_view(const cpprl_b200_comm *c);
@@ -188,6 +191,7 @@ struct Scratch
     unsigned int *barrier = nullptr;
     UpdateState *state = nullptr;
     double *adv_sums = nullptr;
+    void *adv_ws = nullptr; // per-CTA partials + arrival counter of the deterministic advantage moments
     void *rms_ws = nullptr;
     size_t rms_ws_bytes = 0;
     float *tape = nullptr; // GRU path: per-CTA activation tapes
@@ -215,6 +219,8 @@ struct Scratch
             CPPRL_CUDA_TRY(cudaMalloc(&state, sizeof(UpdateState)));
             CPPRL_CUDA_TRY(cudaMemset(state, 0, sizeof(UpdateState)));
             CPPRL_CUDA_TRY(cudaMalloc(&adv_sums, 4 * sizeof(double)));
+            CPPRL_CUDA_TRY(cudaMalloc(&adv_ws, advantage_workspace_bytes()));
+            CPPRL_CUDA_TRY(cudaMemset(adv_ws, 0, advantage_workspace_bytes()));
         }
         if (img > image_floats)
         {
@@ -241,12 +247,13 @@ struct Scratch
     }
     void release()
     {
-        cudaFree(image), cudaFree(gpart), cudaFree(barrier), cudaFree(state), cudaFree(adv_sums), cudaFree(rms_ws);
+        cudaFree(image), cudaFree(gpart), cudaFree(barrier), cudaFree(state), cudaFree(adv_sums), cudaFree(adv_ws), cudaFree(rms_ws);
         cudaFree(tape);
         image = gpart = tape = nullptr;
         barrier = nullptr;
         state = nullptr;
         adv_sums = nullptr;
+        adv_ws = nullptr;
         rms_ws = nullptr;
     }
 };
@@ -564,7 +571,7 @@ static int ppo_begin_gru(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, con
     reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
     CPPRL_LAUNCH_CHECK("reset_state_kernel");
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.adv_sums, 0, 2 * sizeof(double), s));
-    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, ro->T * ro->N, h->scratch.adv_sums, s))
+    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, ro->T * ro->N, h->scratch.adv_sums, h->scratch.adv_ws, s))
         return rc;
     h->active = true;
     return 0;
@@ -671,7 +678,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         CPPRL_LAUNCH_CHECK("reset_state_kernel");
         double *moments = sharded ? comm_local_adv(h->comm) : h->scratch.adv_sums;
         CPPRL_CUDA_TRY(cudaMemsetAsync(moments, 0, 2 * sizeof(double), cs));
-        if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, moments, cs))
+        if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, moments, h->scratch.adv_ws, cs))
             return rc;
         if (sharded)
             if (int rc = cnn_adv_exchange(c.comm, ++*comm_update_seq(h->comm), h->scratch.adv_sums, h->scratch.state, cs))
@@ -758,7 +765,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
     CPPRL_LAUNCH_CHECK("reset_state_kernel");
     CPPRL_CUDA_TRY(cudaMemsetAsync(const_cast<double *>(a.adv_sums), 0, 2 * sizeof(double), s));
-    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, const_cast<double *>(a.adv_sums), s))
+    if (int rc = launch_advantage_moments(ro->d_returns, ro->d_value_preds, local_rows, const_cast<double *>(a.adv_sums), h->scratch.adv_ws, s))
         return rc;
     h->active = true;
     return 0;
@@ -953,7 +960,7 @@ extern "C" int cpprl_b200_ppo_end_async(cpprl_b200_ppo *h)
         // finish_update: the normaliser sees ALL (T+1)*N observation rows (ppo.cpp:149-154)
         const int64_t M = (h->rollout.T + 1) * h->rollout.N;
         if (int rc = launch_rms_update(h->rollout.d_observations, M, p.obs_dim, p.d_norm_count, p.d_norm_mean,
-                                       p.d_norm_var, h->scratch.rms_ws, h->comm, h->stream))
+                                       p.d_norm_var, h->scratch.rms_ws, h->comm, h->stream, &h->scratch.state->comm_error))
             return rc;
     }
     CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, h->stream));
@@ -1096,7 +1103,7 @@ static int a2c_update_gru(cpprl_b200_a2c *h, const cpprl_b200_policy *policy, co
     if (policy->d_norm_mean)
     {
         if (int rc = launch_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
-                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, nullptr, s))
+                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, nullptr, s, nullptr))
             return rc;
     }
     a.obs = ro->d_observations;
@@ -1208,12 +1215,16 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
     const ImageLayout il = make_image_layout(Dp, Ap);
     Plan plan;
-    if (int rc = choose_plan(rows, il, po, Dp, Ap, true, plan))
-        return rc;
     const CommView view = comm_view(h->comm);
+    // sharded: CTA b pairs with CTA b of the peers and the exchange records sit at blockIdx * (per_cta + stats), so the
+    // grid and per_cta must come from a RANK-INDEPENDENT quantity -- the mean shard, ceil(T * global_envs / world) --
+    // not from this rank's own row count (shards may differ by one environment, api.shard_range); a rank that holds
+    // more rows than the plan simply walks more than one tile per CTA
+    const int64_t plan_rows = sharded ? (rows_global + view.world - 1) / view.world : rows;
+    if (int rc = choose_plan(plan_rows, il, po, Dp, Ap, true, plan))
+        return rc;
     if (sharded)
     {
-        // identical grid on every rank (CTA b pairs with CTA b of the peers); shards have equal shapes
         plan.n_active = plan.grid;
         if (static_cast<int64_t>(plan.grid) * (plan.per_cta + kNumStats) > view.x_stride)
             return fail(CPPRL_B200_EINVAL, "a2c_update: the communicator was created for fewer parameters than this policy has");
@@ -1223,11 +1234,14 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
         return rc;
 
     KernelTimer timer("update", s);
+    // (the state record is reset first: the sharded normaliser update below may raise comm_error in it)
+    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
+    CPPRL_LAUNCH_CHECK("reset_state_kernel");
     if (policy->d_norm_mean)
     {
         // the normaliser is updated BEFORE the forward pass (a2c.cpp:52-55)
         if (int rc = launch_rms_update(ro->d_observations, (ro->T + 1) * ro->N, policy->obs_dim, policy->d_norm_count,
-                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, h->comm, s))
+                                       policy->d_norm_mean, policy->d_norm_var, h->scratch.rms_ws, h->comm, s, &h->scratch.state->comm_error))
             return rc;
     }
     MlpUpdateArgs a;
@@ -1271,8 +1285,6 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.barrier = h->scratch.barrier;
     a.state = h->scratch.state;
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
-    reset_state_kernel<<<1, 1, 0, s>>>(h->scratch.state);
-    CPPRL_LAUNCH_CHECK("reset_state_kernel");
     if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
         return rc;
     CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, s));
@@ -1305,8 +1317,28 @@ extern "C" int cpprl_b200_a2c_update(cpprl_b200_a2c *h, const cpprl_b200_policy 
 // =====================================================================================================
 // forward evaluation
 // =====================================================================================================
+// Scratch of the forward entry points (evaluate_actions, get_values, act, bootstrap_returns): weight image, barrier word,
+// CNN / GRU tape, distribution buffer, placeholder actions.  These entry points take an arbitrary `void *stream`, so
+// the scratch is keyed by (device, stream): work enqueued on different streams or devices never shares a buffer, and a
+// buffer that has to grow is only ever in use on its own stream (synchronised before it is freed).  g_eval_mu guards
+// the map and serialises the host-side enqueue.
+struct EvalScratch
+{
+    Scratch sc;
+    float *act_dist = nullptr;
+    void *act_zero = nullptr;
+    size_t act_dist_cap = 0, act_zero_cap = 0;
+};
 static std::mutex g_eval_mu;
-static Scratch g_eval_scratch;
+static std::map<std::pair<int, cudaStream_t>, EvalScratch> g_eval_map;
+
+// Caller holds g_eval_mu.
+static EvalScratch &eval_scratch_for(cudaStream_t s)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return g_eval_map[std::make_pair(dev, s)];
+}
 
 extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
 {
@@ -1325,10 +1357,11 @@ extern "C" int64_t cpprl_b200_policy_num_params(const cpprl_b200_policy *policy)
 }
 
 // forward of any base on B explicit rows; d_dist (nullable, [B][A]) receives what act() samples from.  Caller holds g_eval_mu.
-static int evaluate_impl(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
+static int evaluate_impl(EvalScratch &es, const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
                          const float *d_masks, const void *d_actions, int64_t B, float *d_value, float *d_logp,
                          float *d_entropy, float *d_hxs_out, float *d_dist, cudaStream_t s)
 {
+    Scratch &g_eval_scratch = es.sc;
 
     if (policy->base_kind == CPPRL_B200_BASE_CNN)
     {
@@ -1453,8 +1486,8 @@ extern "C" int cpprl_b200_evaluate_actions(const cpprl_b200_policy *policy, cons
     if (B <= 0 || B > 0x7fffffffll)
         return fail(CPPRL_B200_EINVAL, "evaluate_actions: bad batch size");
     std::lock_guard<std::mutex> lock(g_eval_mu);
-    return evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, d_actions, B, d_value, d_logp, d_entropy, d_hxs_out, nullptr,
-                         static_cast<cudaStream_t>(stream));
+    return evaluate_impl(eval_scratch_for(static_cast<cudaStream_t>(stream)), policy, d_obs, d_hxs, n_hxs, d_masks, d_actions, B,
+                         d_value, d_logp, d_entropy, d_hxs_out, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 // ---- PolicyImpl::act (policy.cpp:52-81): forward + sample + log-prob ----------------------------------------------------
@@ -1510,14 +1543,13 @@ __global__ void __launch_bounds__(256)
     }
 }
 
-static float *g_act_dist = nullptr;
-static void *g_act_zero = nullptr;
-static size_t g_act_dist_cap = 0, g_act_zero_cap = 0;
-
 // scratch of the act / get_values entry points: the distribution parameters [B][A] + one float of entropy, and
 // placeholder actions (zeros) for the forward kernels' log-prob stage
-static int ensure_act_scratch(int64_t B, int A, bool normal, cudaStream_t s)
+static int ensure_act_scratch(EvalScratch &es, int64_t B, int A, bool normal, cudaStream_t s)
 {
+    float *&g_act_dist = es.act_dist;
+    void *&g_act_zero = es.act_zero;
+    size_t &g_act_dist_cap = es.act_dist_cap, &g_act_zero_cap = es.act_zero_cap;
     const size_t need_dist = static_cast<size_t>(B) * A + 4, need_zero = static_cast<size_t>(B) * (normal ? A * sizeof(float) : sizeof(int64_t));
     if (need_dist > g_act_dist_cap)
     {
@@ -1544,10 +1576,11 @@ static int ensure_act_scratch(int64_t B, int A, bool normal, cudaStream_t s)
 static int get_values_locked(const cpprl_b200_policy *policy, const float *d_obs, const float *d_hxs, int64_t n_hxs,
                              const float *d_masks, int64_t B, float *d_value, cudaStream_t s)
 {
+    EvalScratch &es = eval_scratch_for(s);
     const int A = static_cast<int>(policy->num_actions);
-    if (int rc = ensure_act_scratch(B, A, policy->head_kind == CPPRL_B200_HEAD_NORMAL, s))
+    if (int rc = ensure_act_scratch(es, B, A, policy->head_kind == CPPRL_B200_HEAD_NORMAL, s))
         return rc;
-    return evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, g_act_zero, B, d_value, g_act_dist, g_act_dist + B, nullptr,
+    return evaluate_impl(es, policy, d_obs, d_hxs, n_hxs, d_masks, es.act_zero, B, d_value, es.act_dist, es.act_dist + B, nullptr,
                          nullptr, s);
 }
 
@@ -1613,10 +1646,12 @@ extern "C" int cpprl_b200_act(const cpprl_b200_policy *policy, const float *d_ob
     const int A = static_cast<int>(policy->num_actions);
     const bool normal = policy->head_kind == CPPRL_B200_HEAD_NORMAL;
     std::lock_guard<std::mutex> lock(g_eval_mu);
-    if (int rc = ensure_act_scratch(B, A, normal, s))
+    EvalScratch &es = eval_scratch_for(s);
+    if (int rc = ensure_act_scratch(es, B, A, normal, s))
         return rc;
+    float *const g_act_dist = es.act_dist;
     float *d_entropy = g_act_dist + static_cast<size_t>(B) * A;
-    if (int rc = evaluate_impl(policy, d_obs, d_hxs, n_hxs, d_masks, g_act_zero, B, d_value, d_logp, d_entropy, d_hxs_out,
+    if (int rc = evaluate_impl(es, policy, d_obs, d_hxs, n_hxs, d_masks, es.act_zero, B, d_value, d_logp, d_entropy, d_hxs_out,
                                g_act_dist, s))
         return rc;
     int slog = 0;

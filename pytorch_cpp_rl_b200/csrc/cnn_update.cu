@@ -867,13 +867,13 @@ int launch_gemm_tc(const AL &al, const BL &bl, const EP &ep, int M, int N, int K
                    cudaStream_t s)
 {
     auto kernel = tc::gemm_tc_kernel<BN, A_T, AL, BL, EP>;
-    static bool configured = false;
-    if (!configured)
+    static std::atomic<uint64_t> configured{0};
+    if (!configured_on_device(configured))
     {
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(tc::smem_bytes(BN))));
         // two CTAs per SM (BN <= 64) need the whole 228 KB carve-out; the driver's default sizes it for one
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        configured = true;
+        mark_configured_on_device(configured);
     }
     int k_slice = K;
     if (z_is_k_split)
@@ -953,13 +953,13 @@ int cnn_forward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, i
 
 int launch_heads(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, int rows, float inv_b, cudaStream_t s)
 {
-    static bool configured = false;
+    static std::atomic<uint64_t> configured{0};
     const size_t smem = static_cast<size_t>(2) * (a.A + 1) * kCnnHid * sizeof(float);
-    if (!configured)
+    if (!configured_on_device(configured))
     {
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(cnn_heads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             2 * kHeadsMaxOut * kCnnHid * static_cast<int>(sizeof(float))));
-        configured = true;
+        mark_configured_on_device(configured);
     }
     const int grid = std::max(1, std::min(2 * sm_count(), (rows + 7) / 8));
     cnn_heads_kernel<<<grid, 256, smem, s>>>(a, ws.h, ws.dh, ws.gflat, ws.sums, base, rows, inv_b);

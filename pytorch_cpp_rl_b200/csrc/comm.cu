@@ -39,7 +39,7 @@ unsigned int *comm_step_seq(cpprl_b200_comm *c) { return &c->step_seq; }
 unsigned int *comm_update_seq(cpprl_b200_comm *c) { return &c->update_seq; }
 unsigned int *comm_rms_seq(cpprl_b200_comm *c) { return &c->rms_seq; }
 double *comm_local_adv(cpprl_b200_comm *c) { return c->local->adv; }
-double *comm_local_rms(cpprl_b200_comm *c) { return c->local->rms; }
+double *comm_local_rms(cpprl_b200_comm *c) { return c->local->rms[0]; }
 
 namespace
 {
@@ -211,6 +211,20 @@ extern "C" void cpprl_b200_comm_destroy(cpprl_b200_comm *c)
             cudaIpcCloseMemHandle(c->area[r]);
     cudaFree(c->local);
     delete c;
+}
+
+extern "C" int cpprl_b200_comm_check(cpprl_b200_comm *c, void *stream)
+{
+    if (!c)
+        return fail(CPPRL_B200_EINVAL, "comm_check: null communicator");
+    // error words kernels raise in this rank's own exchange area when a peer's record never arrived
+    int rms_error = 0;
+    CPPRL_CUDA_TRY(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+    CPPRL_CUDA_TRY(cudaMemcpy(&rms_error, &c->local->rms_error, sizeof(int), cudaMemcpyDeviceToHost));
+    if (rms_error)
+        return fail(CPPRL_B200_ENCCL, "rms_update_sharded: a peer rank never published its sums (bounded wait expired); "
+                                      "the normaliser was left untouched");
+    return 0;
 }
 
 extern "C" int cpprl_b200_comm_info(const cpprl_b200_comm *c, int *rank, int *world)

@@ -19,9 +19,13 @@ struct ExchangeArea
     unsigned int step_flag[kMaxCtas + 12];
     // advantage moments {sum, sum of squares} of the local shard + flag (sequence = update count)
     double adv[4];
-    unsigned int adv_flag, rms_flag, pad0, pad1;
-    // observation-normaliser exchange: column sums, column sums of squares, row count
-    double rms[2 * kXMaxDim + 2];
+    unsigned int adv_flag, rms_flag;
+    int rms_error; // a peer never published its normaliser sums (bounded wait expired): the merge was skipped
+    unsigned int pad1;
+    // observation-normaliser exchange: column sums, column sums of squares, row count; two buffers selected by the
+    // parity of the sequence number, so back-to-back updates never overwrite sums a slower peer is still reading
+    // (a rank enters sequence n+2 only after every peer published n+1, i.e. finished reading n)
+    double rms[2][2 * kXMaxDim + 2];
     // followed by the gradient exchange: LLWord xbuf[2 (parity)][world (sender)][x_stride]
 };
 

@@ -50,6 +50,21 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 int require_device(); // 0 if current device is sm_10x, else ECUDA with message
 int sm_count();
 
+// Function attributes (dynamic shared-memory limit, carve-out) are per DEVICE: a launcher keeps one bit per device
+// ordinal and configures its kernel the first time it runs on each.
+inline bool configured_on_device(const std::atomic<uint64_t> &mask)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (mask.load(std::memory_order_acquire) >> (dev & 63)) & 1u;
+}
+inline void mark_configured_on_device(std::atomic<uint64_t> &mask)
+{
+    int dev = 0;
+    cudaGetDevice(&dev);
+    mask.fetch_or(1ull << (dev & 63), std::memory_order_release);
+}
+
 // ---- device side ---------------------------------------------------------------------------
 #ifdef __CUDACC__
 __device__ __forceinline__ float warp_sum(float v)

@@ -996,11 +996,11 @@ size_t gru_update_smem_bytes(int Dp, int A, int Ap, int head, int T)
 
 int launch_gru_update(const GruUpdateArgs &args, int grid, cudaStream_t s)
 {
-    static bool configured = false;
-    if (!configured)
+    static std::atomic<uint64_t> configured{0};
+    if (!configured_on_device(configured))
     {
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(gru_update_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        configured = true;
+        mark_configured_on_device(configured);
     }
     const size_t smem = gru_update_smem_bytes(args.Dp, args.A, args.Ap, args.head, args.T);
     gru_update_kernel<<<grid, kGruThreads, smem, s>>>(args);

@@ -978,11 +978,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 template <int R>
 int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaStream_t s)
 {
-    static bool configured = false;
-    if (!configured)
+    static std::atomic<uint64_t> configured{0};
+    if (!configured_on_device(configured))
     {
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(mlp_update_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        configured = true;
+        mark_configured_on_device(configured);
     }
     // the grid barrier counts arrivals from zero in every launch
     CPPRL_CUDA_TRY(cudaMemsetAsync(args.barrier, 0, sizeof(unsigned int), s));

@@ -119,10 +119,19 @@ __global__ void __launch_bounds__(kScanThreads)
 // ---- advantages -----------------------------------------------------------------------------
 constexpr int kAdvThreads = 256;
 
-// sums[0] += sum(ret - v), sums[1] += sum((ret - v)^2) over the first T*N elements, in double.
+// sums[0] = sum(ret - v), sums[1] = sum((ret - v)^2) over the first n elements, in double.  Every CTA writes its
+// partial pair to ws->partials[blockIdx]; the LAST CTA to finish adds the partials in index order (one warp: lane l
+// takes l, l + 32, ... then a fixed shuffle tree), so the result does not depend on the order the CTAs ran in -- the
+// update gives the same bits every run.  The arrival counter cleans itself for the next launch.
+struct AdvWorkspace
+{
+    unsigned int counter, pad;
+    double partials[1][2]; // [blocks][2]
+};
+
 __global__ void __launch_bounds__(kAdvThreads)
     advantage_moments_kernel(const float *__restrict__ returns, const float *__restrict__ value_preds, int64_t n,
-                             double *__restrict__ sums)
+                             double *__restrict__ sums, AdvWorkspace *__restrict__ ws)
 {
     double s = 0.0, ss = 0.0;
     const int64_t stride = static_cast<int64_t>(gridDim.x) * kAdvThreads;
@@ -135,21 +144,41 @@ __global__ void __launch_bounds__(kAdvThreads)
     s = warp_sum(s);
     ss = warp_sum(ss);
     __shared__ double sh[2][kAdvThreads / 32];
+    __shared__ bool is_last;
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
     if (l == 0)
         sh[0][w] = s, sh[1][w] = ss;
     __syncthreads();
-    if (w == 0)
+    if (w != 0)
+        return;
+    s = l < kAdvThreads / 32 ? sh[0][l] : 0.0;
+    ss = l < kAdvThreads / 32 ? sh[1][l] : 0.0;
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    if (l == 0)
     {
-        s = l < kAdvThreads / 32 ? sh[0][l] : 0.0;
-        ss = l < kAdvThreads / 32 ? sh[1][l] : 0.0;
-        s = warp_sum(s);
-        ss = warp_sum(ss);
-        if (l == 0)
-        {
-            atomicAdd(&sums[0], s);
-            atomicAdd(&sums[1], ss);
-        }
+        __stcg(&ws->partials[blockIdx.x][0], s);
+        __stcg(&ws->partials[blockIdx.x][1], ss);
+        __threadfence();
+        is_last = atomicAdd(&ws->counter, 1u) == gridDim.x - 1;
+    }
+    __syncwarp();
+    if (!is_last)
+        return;
+    __threadfence();
+    s = 0.0, ss = 0.0;
+    for (unsigned int b = l; b < gridDim.x; b += 32)
+    {
+        s += __ldcg(&ws->partials[b][0]);
+        ss += __ldcg(&ws->partials[b][1]);
+    }
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    if (l == 0)
+    {
+        sums[0] = s;
+        sums[1] = ss;
+        ws->counter = 0u;
     }
 }
 
@@ -184,15 +213,25 @@ __global__ void __launch_bounds__(kAdvThreads)
 
 namespace cpprl_b200
 {
-// sums[0] += sum(adv), sums[1] += sum(adv^2); the caller zeroes d_sums.
-int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums,
-                             cudaStream_t s)
+static int64_t advantage_blocks(int64_t n)
 {
     int64_t blocks = (n + kAdvThreads * 4 - 1) / (kAdvThreads * 4);
     const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
     if (blocks > cap)
         blocks = cap;
-    advantage_moments_kernel<<<static_cast<unsigned>(blocks), kAdvThreads, 0, s>>>(d_returns, d_value_preds, n, d_sums);
+    return blocks < 1 ? 1 : blocks;
+}
+
+// bytes of the partial-sum workspace launch_advantage_moments needs (zeroed ONCE by its owner: the arrival counter
+// returns to zero at the end of every launch)
+size_t advantage_workspace_bytes() { return sizeof(AdvWorkspace) + static_cast<size_t>(sm_count()) * 8 * 2 * sizeof(double); }
+
+// sums[0] = sum(adv), sums[1] = sum(adv^2), deterministic (see advantage_moments_kernel).
+int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums, void *d_ws,
+                             cudaStream_t s)
+{
+    advantage_moments_kernel<<<static_cast<unsigned>(advantage_blocks(n)), kAdvThreads, 0, s>>>(
+        d_returns, d_value_preds, n, d_sums, static_cast<AdvWorkspace *>(d_ws));
     CPPRL_LAUNCH_CHECK("advantage_moments_kernel");
     return 0;
 }
@@ -255,12 +294,15 @@ extern "C" int cpprl_b200_advantages(const float *d_returns, const float *d_valu
     const int64_t n = T * N;
     KernelTimer timer("advantages", s);
     CPPRL_CUDA_TRY(cudaMemsetAsync(d_moments, 0, 4 * sizeof(double), s));
-    int64_t blocks = (n + kAdvThreads * 4 - 1) / (kAdvThreads * 4);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    if (blocks > cap)
-        blocks = cap;
-    advantage_moments_kernel<<<static_cast<unsigned>(blocks), kAdvThreads, 0, s>>>(d_returns, d_value_preds, n, d_moments);
-    CPPRL_LAUNCH_CHECK("advantage_moments_kernel");
+    // the caller's d_moments holds four doubles only: the per-CTA partials go to a stream-ordered temporary
+    void *ws = nullptr;
+    CPPRL_CUDA_TRY(cudaMallocAsync(&ws, advantage_workspace_bytes(), s));
+    CPPRL_CUDA_TRY(cudaMemsetAsync(ws, 0, sizeof(AdvWorkspace), s));
+    const int64_t blocks = advantage_blocks(n);
+    int rc = launch_advantage_moments(d_returns, d_value_preds, n, d_moments, ws, s);
+    CPPRL_CUDA_TRY(cudaFreeAsync(ws, s));
+    if (rc)
+        return rc;
     advantage_write_kernel<<<static_cast<unsigned>(blocks), kAdvThreads, 0, s>>>(d_returns, d_value_preds, n, normalize,
                                                                                  d_advantages, d_moments);
     CPPRL_LAUNCH_CHECK("advantage_write_kernel");

@@ -43,7 +43,8 @@ constexpr int kRmsThreads = 256;
 __global__ void __launch_bounds__(kRmsThreads)
     rms_update_kernel(const float *__restrict__ x, int64_t M, int D, double *__restrict__ ws,
                       unsigned int *__restrict__ done_counter, float *__restrict__ count,
-                      float *__restrict__ mean, float *__restrict__ var, const CommView comm, unsigned int seq)
+                      float *__restrict__ mean, float *__restrict__ var, const CommView comm, unsigned int seq,
+                      int *__restrict__ comm_error)
 {
     extern __shared__ double sh[]; // [2][lanes_used]
     // threads 0..lanes_used-1 each stay on one column: lanes_used is a multiple of D
@@ -91,29 +92,45 @@ __global__ void __launch_bounds__(kRmsThreads)
         // env-sharded update: the batch is the union of every rank's rows.  Publish this rank's column sums and row
         // count, wait for the peers', and add them in rank order (identical merge on every rank).
         ExchangeArea *mine = comm.area[comm.rank];
-        for (int c = tid; c < 2 * D; c += kRmsThreads)
-            mine->rms[c] = __ldcg(&ws[c]);
+        const int par = static_cast<int>(seq & 1u);
+        __shared__ int peer_missing;
         if (tid == 0)
-            mine->rms[2 * D] = static_cast<double>(M);
+            peer_missing = 0;
+        for (int c = tid; c < 2 * D; c += kRmsThreads)
+            mine->rms[par][c] = __ldcg(&ws[c]);
+        if (tid == 0)
+            mine->rms[par][2 * D] = static_cast<double>(M);
         __threadfence_system();
         __syncthreads();
         if (tid == 0)
             flag_publish(&mine->rms_flag, seq);
-        if (tid < comm.world && tid != comm.rank)
-            flag_wait(&comm.area[tid]->rms_flag, seq);
+        if (tid < comm.world && tid != comm.rank && !flag_wait(&comm.area[tid]->rms_flag, seq))
+            peer_missing = 1;
         __syncthreads();
+        if (peer_missing)
+        {
+            // a peer never published: merging stale or zero sums would silently corrupt the normaliser, so the
+            // statistics are left untouched and the host turns the flag into CPPRL_B200_ENCCL
+            if (tid == 0)
+            {
+                mine->rms_error = 1;
+                if (comm_error)
+                    *comm_error = 1;
+            }
+            return;
+        }
         for (int c = tid; c < 2 * D; c += kRmsThreads)
         {
             double sum = 0.0;
             for (int r = 0; r < comm.world; ++r)
-                sum += r == comm.rank ? __ldcg(&ws[c]) : peer_load(&comm.area[r]->rms[c]);
+                sum += r == comm.rank ? __ldcg(&ws[c]) : peer_load(&comm.area[r]->rms[par][c]);
             ws[c] = sum;
         }
         if (tid == 0)
         {
             double rows = 0.0;
             for (int r = 0; r < comm.world; ++r)
-                rows += r == comm.rank ? static_cast<double>(M) : peer_load(&comm.area[r]->rms[2 * D]);
+                rows += r == comm.rank ? static_cast<double>(M) : peer_load(&comm.area[r]->rms[par][2 * D]);
             sh_rows = rows;
         }
         __syncthreads();
@@ -237,7 +254,7 @@ extern "C" int64_t cpprl_b200_rms_workspace_bytes(int64_t /*M*/, int64_t D)
 namespace cpprl_b200
 {
 int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean, float *d_var,
-                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s)
+                      void *d_workspace, cpprl_b200_comm *comm, cudaStream_t s, int *d_comm_error)
 {
     if (!d_x || !d_count || !d_mean || !d_var || !d_workspace)
         return fail(CPPRL_B200_EINVAL, "rms_update: null pointer");
@@ -262,7 +279,7 @@ int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, fl
     const CommView view = comm_view(comm);
     const unsigned int seq = view.world > 1 ? ++*comm_rms_seq(comm) : 0u;
     rms_update_kernel<<<static_cast<unsigned>(blocks), kRmsThreads, sizeof(double) * 2 * lanes_used, s>>>(
-        d_x, M, static_cast<int>(D), ws, counter, d_count, d_mean, d_var, view, seq);
+        d_x, M, static_cast<int>(D), ws, counter, d_count, d_mean, d_var, view, seq, d_comm_error);
     CPPRL_LAUNCH_CHECK("rms_update_kernel");
     return 0;
 }
@@ -271,13 +288,16 @@ int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, fl
 extern "C" int cpprl_b200_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, float *d_mean,
                                      float *d_var, void *d_workspace, void *stream)
 {
-    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, nullptr, static_cast<cudaStream_t>(stream));
+    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, nullptr, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 extern "C" int cpprl_b200_rms_update_sharded(cpprl_b200_comm *comm, const float *d_x, int64_t M, int64_t D,
                                              float *d_count, float *d_mean, float *d_var, void *d_workspace, void *stream)
 {
-    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, comm, static_cast<cudaStream_t>(stream));
+    if (!comm)
+        return fail(CPPRL_B200_EINVAL, "rms_update_sharded: null communicator");
+    // a missing peer raises the communicator's error word: cpprl_b200_comm_check reports it as CPPRL_B200_ENCCL
+    return launch_rms_update(d_x, M, D, d_count, d_mean, d_var, d_workspace, comm, static_cast<cudaStream_t>(stream), nullptr);
 }
 
 extern "C" int cpprl_b200_normalize_observations(const float *d_x, int64_t M, int64_t D, const float *d_mean,

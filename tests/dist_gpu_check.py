@@ -99,6 +99,10 @@ def main():
     ok &= run_case(CONFIGS["cfg3"].scaled(T=16, N=1536, num_epoch=2, num_mini_batch=2), 2, rank, world, n_updates=1)
     ok &= run_case(CONFIGS["cfg1"].scaled(N=10, kl_target=0.01, learning_rate=3e-2), 5, rank, world, n_updates=3)
     ok &= run_case(CONFIGS["cfg2"].scaled(N=512), 3, rank, world)
+    # shards that differ by one environment (api.shard_range): at world=2 the ranks' own row counts would pick
+    # different grids (41 vs 40 tiles); the launch plan must come from the rank-independent mean shard
+    ok &= run_case(CONFIGS["cfg2"].scaled(N=513), 6, rank, world)
+    ok &= run_case(CONFIGS["cfg2"].scaled(N=4099), 8, rank, world, n_updates=1)
     cnn = CONFIGS["cfg5"].scaled(T=8, N=8, num_epoch=2, num_mini_batch=2)
     ok &= run_case(cnn, 0, rank, world, n_updates=1)
     ok &= run_case(cnn.scaled(T=6, N=6, num_mini_batch=3, kl_target=0.003, learning_rate=3e-3, num_epoch=3), 4, rank, world)
