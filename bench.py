@@ -471,7 +471,9 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "config": config_of(w, world),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": side.h2d_bytes, "d2h_bytes_per_step": side.d2h_bytes,
                 "ms_per_step": e2e_s * 1e3,
-                "permutations": "device (sharded update)" if world > 1 and w.base != "gru" else "host torch.randperm, the reference's CPU random stream",
+                "permutations": "device (sharded update)" if world > 1 and w.base != "gru" else
+                "the reference's CPU random stream (torch's CPU generator state in / out), drawn by the library's host threads "
+                "while the device runs: bit-identical to torch.randperm",
                 "with_device_permutations": None if e2e_dev_s is None else
                 {"value": world * w.rows / e2e_dev_s, "ms_per_step": e2e_dev_s * 1e3,
                  "h2d_bytes_per_step": side.h2d_bytes - w.num_epoch * side.perm_len * 8}},

@@ -227,6 +227,19 @@ int cpprl_b200_ppo_update(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, co
                           const cpprl_b200_ppo_options *opt, const int64_t *h_perms, int64_t perm_len,
                           cpprl_b200_ppo_stats *stats, void *stream);
 
+/* The same update with the permutations drawn HERE from the reference's own random stream: `rng_state` is the state
+ * of torch's default CPU generator (at::CPUGeneratorImpl::get_state / torch.get_rng_state(),
+ * cpprl_b200_rng_state_bytes() = 5056 bytes) on entry and the state to put back (set_state) on return — exactly
+ * where the reference's torch::randperm calls (feed_forward_generator.cpp:31-34, recurrent_generator.cpp:38; one per
+ * epoch, none after the KL early stop of ppo.cpp:100-104) would have left it, with bit-identical permutations.  The
+ * epochs' Fisher-Yates walks run on background host threads while the device works on the previous epoch. */
+int cpprl_b200_ppo_update_rng(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                              const cpprl_b200_ppo_options *opt, void *rng_state, cpprl_b200_ppo_stats *stats, void *stream);
+/* Host only: `count` back-to-back torch::randperm(n, kLong) results [count][n] from the generator state blob
+ * (updated in place).  n must be below 2^32 / 20 (randperm_cpu's 32-bit branch). */
+int cpprl_b200_host_randperm(void *rng_state, int64_t n, int64_t count, int64_t *out, int max_threads);
+int64_t cpprl_b200_rng_state_bytes(void);
+
 /* The same update in stages, so the host can draw epoch e+1's permutation while epoch e runs and can
  * honour the KL early stop without drawing permutations the reference would not draw:
  *   begin (advantage moments) -> epoch x num_epoch (each: async H2D of the permutation + one persistent

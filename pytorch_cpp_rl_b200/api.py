@@ -524,6 +524,7 @@ class PPO:
         self.original_learning_rate = learning_rate
         self.epsilon, self.max_grad_norm, self.kl_target = epsilon, max_grad_norm, kl_target
         self.device_permutations = False  # opt-in: draw the per-epoch permutations with the CUDA generator (see update)
+        self.host_rng_threads = True      # draw torch's CPU-stream permutations in the library (False: torch.randperm here)
         self._h = C.c_void_p()
         check(cabi.load().cpprl_b200_ppo_create(C.byref(self._h), policy.params.numel()))
 
@@ -569,6 +570,15 @@ class PPO:
             assert perms.dtype == torch.int64 and not perms.is_cuda
             check(lib.cpprl_b200_ppo_update(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(perms.data_ptr()),
                                             perms.shape[1], C.byref(stats), _stream()))
+        elif (getattr(self, "_comm", None) is None and not self.device_permutations and self.host_rng_threads
+              and (N if self.policy.is_recurrent() else T * N) < (2 ** 32 - 1) // 20):
+            # the reference's own random stream, drawn by the library: torch's CPU generator state goes in, the state
+            # after the epochs' torch::randperm calls comes out (bit-identical permutations, tests/test_host_rng_cpu.py);
+            # the epochs' Fisher-Yates walks run on background threads while the device runs the previous epoch
+            state = torch.get_rng_state()
+            check(lib.cpprl_b200_ppo_update_rng(self._h, C.byref(pd), C.byref(rd), C.byref(od), C.c_void_p(state.data_ptr()),
+                                                C.byref(stats), _stream()))
+            torch.set_rng_state(state)
         else:
             n = N if self.policy.is_recurrent() else T * (getattr(self, "_global_envs", 0) or N)
             can_stop = self.kl_target * 1.5 < 1e3  # a mean log-prob difference cannot reach this: no stop possible

@@ -98,6 +98,9 @@ SIGNATURES = {
     "cpprl_b200_ppo_state": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]),
     "cpprl_b200_ppo_set_step": (C.c_int, [C.c_void_p, C.c_int64]),
     "cpprl_b200_ppo_update": (C.c_int, [C.c_void_p, C.POINTER(Policy), C.POINTER(Rollout), C.POINTER(PPOOptions), C.c_void_p, C.c_int64, C.POINTER(PPOStats), C.c_void_p]),
+    "cpprl_b200_ppo_update_rng": (C.c_int, [C.c_void_p, C.POINTER(Policy), C.POINTER(Rollout), C.POINTER(PPOOptions), C.c_void_p, C.POINTER(PPOStats), C.c_void_p]),
+    "cpprl_b200_host_randperm": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int]),
+    "cpprl_b200_rng_state_bytes": (C.c_int64, []),
     "cpprl_b200_ppo_begin": (C.c_int, [C.c_void_p, C.POINTER(Policy), C.POINTER(Rollout), C.POINTER(PPOOptions), C.c_void_p]),
     "cpprl_b200_ppo_epoch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),
     "cpprl_b200_ppo_epoch_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64]),

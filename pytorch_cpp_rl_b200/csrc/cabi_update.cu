@@ -12,6 +12,7 @@
 #include <curand_kernel.h>
 
 #include "common.cuh"
+#include "host_rng.h"
 #include "cnn_update.cuh"
 #include "gru_update.cuh"
 #include "mlp_update.cuh"
@@ -400,6 +401,11 @@ struct cpprl_b200_ppo
     int64_t *d_lperm = nullptr; // the global permutation compacted to this rank's rows, [n_mb][mbs]
     int *d_counts = nullptr;    // rows of each minibatch owned by this rank
     size_t lperm_cap = 0, counts_cap = 0;
+    // cpprl_b200_ppo_update_rng: every epoch's permutation of the reference's CPU random stream, drawn by background
+    // threads straight into pinned memory (host_rng.cu)
+    int64_t *h_rng_perms = nullptr; // pinned [num_epoch][perm_len]
+    size_t rng_perms_cap = 0;
+    PermStream *perm_stream = nullptr;
 };
 
 extern "C" int cpprl_b200_ppo_create(cpprl_b200_ppo **out, int64_t n_params)
@@ -455,6 +461,9 @@ extern "C" void cpprl_b200_ppo_destroy(cpprl_b200_ppo *h)
         cudaStreamDestroy(h->copy_stream);
     if (h->h_state)
         cudaFreeHost(h->h_state);
+    delete h->perm_stream; // joins its threads before the pinned buffer they write goes away
+    if (h->h_rng_perms)
+        cudaFreeHost(h->h_rng_perms);
     h->scratch.release();
     delete h;
 }
@@ -891,15 +900,10 @@ extern "C" int cpprl_b200_ppo_epoch_device(cpprl_b200_ppo *h, const int64_t *d_p
     return ppo_launch_epoch(h, d_perm);
 }
 
-extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, int64_t perm_len)
+// One epoch from a HOST permutation: H2D on the copy stream into device buffer (epoch & 1), kernel after it.  A
+// pageable source goes through the handle's pinned staging buffer; a pinned source is copied from where it lies.
+static int ppo_epoch_host(cpprl_b200_ppo *h, const int64_t *h_perm, int64_t perm_len, bool src_pinned)
 {
-    if (!h || !h_perm)
-        return fail(CPPRL_B200_EINVAL, "ppo_epoch: null argument");
-    if (!h->active)
-        return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
-    if (perm_len != h->mbs * h->n_mb)
-        return fail(CPPRL_B200_EINVAL, h->gru ? "ppo_epoch: permutation length must be N for recurrent policies"
-                                              : "ppo_epoch: permutation length must be T*N");
     if (static_cast<size_t>(perm_len) > h->perm_cap)
     {
         CPPRL_CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -920,12 +924,17 @@ extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, in
     // the pinned buffer is free once its previous H2D finished; the device buffer once its kernel finished
     if (h->consumed_valid[b])
     {
-        CPPRL_CUDA_TRY(cudaEventSynchronize(h->copied[b]));
+        if (!src_pinned)
+            CPPRL_CUDA_TRY(cudaEventSynchronize(h->copied[b]));
         CPPRL_CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->consumed[b], 0));
     }
-    std::memcpy(h->h_perm[b], h_perm, perm_len * sizeof(int64_t));
-    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->d_perm[b], h->h_perm[b], perm_len * sizeof(int64_t), cudaMemcpyHostToDevice,
-                                   h->copy_stream));
+    const int64_t *src = h_perm;
+    if (!src_pinned)
+    {
+        std::memcpy(h->h_perm[b], h_perm, perm_len * sizeof(int64_t));
+        src = h->h_perm[b];
+    }
+    CPPRL_CUDA_TRY(cudaMemcpyAsync(h->d_perm[b], src, perm_len * sizeof(int64_t), cudaMemcpyHostToDevice, h->copy_stream));
     CPPRL_CUDA_TRY(cudaEventRecord(h->copied[b], h->copy_stream));
     CPPRL_CUDA_TRY(cudaStreamWaitEvent(h->stream, h->copied[b], 0));
     int rc = ppo_launch_epoch(h, h->d_perm[b]);
@@ -934,6 +943,18 @@ extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, in
     CPPRL_CUDA_TRY(cudaEventRecord(h->consumed[b], h->stream));
     h->consumed_valid[b] = true;
     return 0;
+}
+
+extern "C" int cpprl_b200_ppo_epoch(cpprl_b200_ppo *h, const int64_t *h_perm, int64_t perm_len)
+{
+    if (!h || !h_perm)
+        return fail(CPPRL_B200_EINVAL, "ppo_epoch: null argument");
+    if (!h->active)
+        return fail(CPPRL_B200_ESTATE, "ppo_epoch called without ppo_begin");
+    if (perm_len != h->mbs * h->n_mb)
+        return fail(CPPRL_B200_EINVAL, h->gru ? "ppo_epoch: permutation length must be N for recurrent policies"
+                                              : "ppo_epoch: permutation length must be T*N");
+    return ppo_epoch_host(h, h_perm, perm_len, false);
 }
 
 extern "C" int cpprl_b200_ppo_stopped(cpprl_b200_ppo *h, int *stopped)
@@ -1011,6 +1032,74 @@ extern "C" int cpprl_b200_ppo_update(cpprl_b200_ppo *h, const cpprl_b200_policy 
             return rc;
         }
     return cpprl_b200_ppo_end(h, stats);
+}
+
+// PPO::update with the permutations the reference itself would draw (ppo.cpp:63-84 builds one generator per epoch,
+// each drawing torch::randperm from the default CPU generator): `rng_state` is that generator's state
+// (at::CPUGeneratorImpl::get_state, cpprl_b200_rng_state_bytes() bytes) on entry and what it must be set to on return.
+// The epochs' permutations are drawn by background threads while the device runs (host_rng.cu); after a KL early stop
+// the state is the one after the last epoch the reference would have started.
+extern "C" int cpprl_b200_ppo_update_rng(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
+                                         const cpprl_b200_ppo_options *opt, void *rng_state, cpprl_b200_ppo_stats *stats,
+                                         void *stream)
+{
+    if (!rng_state || !stats || !opt || !h)
+        return fail(CPPRL_B200_EINVAL, "ppo_update_rng: null argument");
+    if (int rc = cpprl_b200_ppo_begin(h, policy, rollout, opt, stream))
+        return rc;
+    const int64_t n = h->mbs * h->n_mb;
+    const int epochs = opt->num_epoch;
+    auto bail = [&](int rc) {
+        h->active = false;
+        return rc;
+    };
+    if (!PermStream::supported(n))
+        return bail(fail(CPPRL_B200_EUNSUPPORTED, "ppo_update_rng: rollout too large for randperm's 32-bit branch"));
+    if (static_cast<size_t>(n) * epochs > h->rng_perms_cap)
+    {
+        delete h->perm_stream;
+        h->perm_stream = nullptr;
+        if (h->h_rng_perms)
+            cudaFreeHost(h->h_rng_perms);
+        h->h_rng_perms = nullptr, h->rng_perms_cap = 0;
+        if (int rc = check_cuda(cudaMallocHost(&h->h_rng_perms, static_cast<size_t>(n) * epochs * sizeof(int64_t)), "cudaMallocHost(perms)"))
+            return bail(rc);
+        h->rng_perms_cap = static_cast<size_t>(n) * epochs;
+    }
+    if (!h->perm_stream)
+        h->perm_stream = new PermStream();
+    std::vector<int64_t *> outs(static_cast<size_t>(epochs));
+    for (int e = 0; e < epochs; ++e)
+        outs[e] = h->h_rng_perms + static_cast<int64_t>(e) * n;
+    // the device buffers of the previous update may still be read by its last kernels: the H2D below waits on the
+    // `consumed` events; the PINNED block is rewritten by the threads right away, so its last copies must be done
+    if (int rc = check_cuda(cudaStreamSynchronize(h->copy_stream), "cudaStreamSynchronize(copy)"))
+        return bail(rc);
+    if (int rc = h->perm_stream->start(rng_state, n, epochs, outs.data(), 0))
+        return bail(rc);
+    const bool can_stop = static_cast<double>(opt->kl_target) * 1.5 < 1e3; // a mean log-prob difference cannot reach that
+    int drawn = 0, rc = 0;
+    for (int e = 0; e < epochs && rc == 0; ++e)
+    {
+        if (can_stop && e > 0)
+        {
+            int stopped = 0;
+            rc = cpprl_b200_ppo_stopped(h, &stopped);
+            if (rc || stopped)
+                break; // the reference leaves its epoch loop here: no further randperm is drawn (ppo.cpp:100-104)
+        }
+        h->perm_stream->wait(e);
+        drawn = e + 1;
+        rc = ppo_epoch_host(h, outs[e], n, true);
+    }
+    if (drawn > 0)
+        h->perm_stream->state_after(drawn - 1, rng_state);
+    if (rc == 0)
+        rc = cpprl_b200_ppo_end(h, stats); // synchronises: every H2D of the pinned block has finished
+    h->perm_stream->join();
+    if (rc)
+        return bail(rc);
+    return 0;
 }
 
 // =====================================================================================================

@@ -38,9 +38,19 @@ constexpr int kRedMaxPer = (148 + kRedSplit - 1) / kRedSplit; // partials one wa
 // Shared-memory carve-up (offsets in floats), identical on host and device.
 struct SmemPlan
 {
-    int img, gsm, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, xn, actn, scn, rowidn, actin, norm, red, own, sig,
+    int img, gsm, g2, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, xn, actn, scn, rowidn, actin, norm, red, own, sig,
         misc, total;
 };
+
+// Gradients whose sums are formed by more than one thread (head weights and b2: the two row halves of P5b; b1: the
+// four warps of a tower in P7) would need shared-memory atomics, whose order varies from run to run.  Instead every
+// contributing thread but the first owns a slot of a SECOND accumulator, and the slots are added to the gradient in
+// a fixed order before it is published: the update gives the same bits every run.
+//   G2:  [0, Ap*64) head weights, row half 1 | [.., +64) value weights, half 1
+//   the bias slots -- b2[tower] of half 1 (128 floats), b1[tower][warp 1..3] (384) -- overlay the phase-2 reduction
+//   scratch RED, which is idle while tiles are being processed (cfg3's 64-row plan has 3 KB of shared memory to spare)
+__host__ __device__ inline int g2_floats(int Ap) { return Ap * kHid + kHid; }
+constexpr int kG2BiasFloats = 2 * kHid + 2 * 3 * kHid;
 
 __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
 {
@@ -49,6 +59,7 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     int o = 0;
     p.img = o, o += img_floats;
     p.gsm = o, o += (Pstride + 3) & ~3;
+    p.g2 = o, o += g2_floats(Ap); // second accumulators of the gradients that several threads share (see G2 below)
     p.x = o, o += Dp * LD;
     for (int t = 0; t < 2; ++t)
         p.h1[t] = o, o += kHid * LD;
@@ -70,7 +81,11 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.rowidn = o, o += 2 * LD;  // long long per row
     p.actin = o, o += 2 * LD;   // int64 actions (Categorical)
     p.norm = o, o += 2 * Dp + 4; // observation normaliser: mean[Dp], sqrt(var + 1e-8)[Dp], clip
-    p.red = o, o += kRedSplit * (per_cta + kNumStats); // phase-2 reduction scratch: [split][owned params + stats]
+    // phase-2 reduction scratch: [split][owned params + stats]; in phase 1 the bias slots of the second accumulators
+    {
+        const int red = kRedSplit * (per_cta + kNumStats);
+        p.red = o, o += (per_cta > 0 && red < kG2BiasFloats) ? kG2BiasFloats : red;
+    }
     p.own = o, o += 3 * per_cta;                       // this CTA's slice of params / Adam exp_avg / exp_avg_sq
     p.sig = o, o += 2 * Ap;                            // Normal head: {sigma^2, log sigma} per action
     p.misc = o, o += 32;
@@ -199,6 +214,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     // every pointer is `smem + integer` so the compiler keeps the shared state space (LDS/STS, never generic LD/ST)
     float *img = smem + sp.img;
     float *gsm = smem + sp.gsm;
+    float *G2 = smem + sp.g2;
+    float *G2_WO = G2, *G2_WV = G2 + a.Ap * kHid;
+    float *G2_B2 = smem + sp.red, *G2_B1 = G2_B2 + 2 * kHid; // overlay RED (idle in phase 1)
     float *X = smem + sp.x;
     float *h1t = smem + sp.h1[0] + tower * (kHid * LD); // this thread's tower
     float *h2t = smem + sp.h2[0] + tower * (kHid * LD);
@@ -456,6 +474,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
             for (int i = tid; i < Pstride; i += kUpdThreads)
                 gsm[i] = 0.f;
+            for (int i = tid; i < g2_floats(a.Ap); i += kUpdThreads)
+                G2[i] = 0.f;
+            if (training) // (forward launches carry no reduction scratch)
+                for (int i = tid; i < kG2BiasFloats; i += kUpdThreads)
+                    G2_B2[i] = 0.f;
             if (!staged)
             {
                 const long long row = item_rowid(step, blockIdx.x);
@@ -723,7 +746,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         dh[qd].z = fmaf(d.z, wk, dh[qd].z);
                         dh[qd].w = fmaf(d.w, wk, dh[qd].w);
                     }
-                    atomicAdd(&gsm[wbase + o * kHid], g0 + g1);
+                    // row half 0 owns the gradient slot, half 1 its twin in G2 (no atomics: deterministic)
+                    if (half == 0)
+                        gsm[wbase + o * kHid] += g0 + g1;
+                    else
+                        (tower == 0 ? G2_WO : G2_WV)[o * kHid + k] += g0 + g1;
                 }
                 float bsum = 0.f;
 #pragma unroll
@@ -737,7 +764,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     bsum += (dz.x + dz.y) + (dz.z + dz.w);
                     *reinterpret_cast<float4 *>(h2 + 4 * qd) = dz;
                 }
-                atomicAdd(&gsm[po_b2 + k], bsum);
+                if (half == 0)
+                    gsm[po_b2 + k] += bsum;
+                else
+                    G2_B2[tower * kHid + k] += bsum;
             }
             __syncthreads();
             CPPRL_MARK(6);
@@ -766,7 +796,16 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         bsum += (dz.x + dz.y) + (dz.z + dz.w);
                         *reinterpret_cast<float4 *>(hp) = dz;
                     }
-                    atomicAdd(&gsm[po_b1 + jb + 16 * q], bsum);
+                    // the two row groups of this warp (lanes jb and jb + 16) first, then one slot per warp of the tower
+                    bsum += __shfl_xor_sync(0xffffffffu, bsum, 16);
+                    if (lane < 16)
+                    {
+                        const int wt = warp & 3; // warp inside the tower
+                        if (wt == 0)
+                            gsm[po_b1 + jb + 16 * q] += bsum;
+                        else
+                            G2_B1[(tower * 3 + wt - 1) * kHid + jb + 16 * q] += bsum;
+                    }
                 }
             }
             __syncthreads();
@@ -780,9 +819,24 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             break;
 
         CPPRL_MARK(9);
-        // ---- publish this CTA's partial ----------------------------------------------------------------------
+        // ---- fold the second accumulators into the gradient in a fixed order, then publish this CTA's partial ----
         if (active)
         {
+            for (int i = tid; i < (A + 1) * kHid; i += kUpdThreads)
+            {
+                const int o = i >> 6, k = i & 63;
+                if (o < A)
+                    gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
+                else
+                    gsm[a.po.wv + k] += G2_WV[k];
+            }
+            for (int i = tid; i < 2 * kHid; i += kUpdThreads)
+            {
+                const int t = i >> 6, k = i & 63;
+                gsm[(t ? a.po.b2[1] : a.po.b2[0]) + k] += G2_B2[i];
+                gsm[(t ? a.po.b1[1] : a.po.b1[0]) + k] += (G2_B1[(t * 3 + 0) * kHid + k] + G2_B1[(t * 3 + 1) * kHid + k]) + G2_B1[(t * 3 + 2) * kHid + k];
+            }
+            __syncthreads();
             float4 *dst = reinterpret_cast<float4 *>(a.gpart + static_cast<size_t>(blockIdx.x) * Pstride);
             const float4 *src = reinterpret_cast<const float4 *>(gsm);
             for (int i = tid; i < Pstride / 4; i += kUpdThreads)

@@ -41,29 +41,45 @@ std::vector<UpdateDatum> PPO::update(RolloutStorage &rollouts, float decay_level
     opt.epsilon = epsilon;
     opt.kl_target = kl_target;
 
-    // feed-forward generators check the minibatch count before drawing anything (storage.cpp:152-162)
+    // The permutations the reference's generator constructors draw (one torch::randperm per epoch on the default CPU
+    // generator, none after a KL early stop: ppo.cpp:63-104) come from the library: the generator's state goes in,
+    // the epochs' Fisher-Yates walks run on background threads while the device works on the previous epoch, and the
+    // state torch::randperm would have left behind comes back (bit-identical permutations: tests/test_host_rng_cpu.py).
     const int64_t rows = rd.T * rd.N;
     const bool recurrent = policy->is_recurrent();
     const int64_t perm_len = recurrent ? rd.N : rows;
-    check(cpprl_b200_ppo_begin(handle, &pd, &rd, &opt, detail::current_stream(rollouts.get_rewards())));
-    // a mean log-prob difference cannot reach 1e3: with such a target the stop can never trigger and the host need
-    // not synchronise between epochs to learn whether the generator of the next epoch would have been constructed
-    const bool can_stop = static_cast<double>(kl_target) * 1.5 < 1e3;
-    for (int epoch = 0; epoch < num_epoch; ++epoch)
-    {
-        if (can_stop && epoch > 0)
-        {
-            int stopped = 0;
-            check(cpprl_b200_ppo_stopped(handle, &stopped));
-            if (stopped)
-                break;
-        }
-        // the permutation the reference's generator constructor draws for this epoch, on the CPU generator
-        auto perm = torch::randperm(perm_len, torch::TensorOptions(torch::kLong));
-        check(cpprl_b200_ppo_epoch(handle, perm.data_ptr<int64_t>(), perm_len));
-    }
     cpprl_b200_ppo_stats st{};
-    check(cpprl_b200_ppo_end(handle, &st));
+    auto gen = at::detail::getDefaultCPUGenerator();
+    if (perm_len < static_cast<int64_t>(0xffffffffu / 20))
+    {
+        std::lock_guard<std::mutex> lock(gen.mutex());
+        auto state = gen.get_state().contiguous();
+        TORCH_CHECK(state.numel() == cpprl_b200_rng_state_bytes(), "unexpected CPU generator state size");
+        check(cpprl_b200_ppo_update_rng(handle, &pd, &rd, &opt, state.data_ptr(), &st,
+                                        detail::current_stream(rollouts.get_rewards())));
+        gen.set_state(state);
+    }
+    else
+    {
+        // randperm's 64-bit branch (more than 2^32 / 20 rows): drawn by torch itself, epoch by epoch
+        check(cpprl_b200_ppo_begin(handle, &pd, &rd, &opt, detail::current_stream(rollouts.get_rewards())));
+        // a mean log-prob difference cannot reach 1e3: with such a target the stop can never trigger and the host
+        // need not synchronise between epochs to learn whether the next epoch's generator would have been constructed
+        const bool can_stop = static_cast<double>(kl_target) * 1.5 < 1e3;
+        for (int epoch = 0; epoch < num_epoch; ++epoch)
+        {
+            if (can_stop && epoch > 0)
+            {
+                int stopped = 0;
+                check(cpprl_b200_ppo_stopped(handle, &stopped));
+                if (stopped)
+                    break;
+            }
+            auto perm = torch::randperm(perm_len, torch::TensorOptions(torch::kLong));
+            check(cpprl_b200_ppo_epoch(handle, perm.data_ptr<int64_t>(), perm_len));
+        }
+        check(cpprl_b200_ppo_end(handle, &st));
+    }
     std::vector<UpdateDatum> out{{"Value loss", st.value_loss},
                                  {"Action loss", st.action_loss},
                                  {"Clip fraction", st.clip_fraction},

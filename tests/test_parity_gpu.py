@@ -414,3 +414,46 @@ def test_sharded_update_world1_matches_plain(ref):
     np.testing.assert_allclose(results[0][1], results[1][1], rtol=1e-5, atol=1e-7)
     np.testing.assert_allclose(results[0][0].cpu().numpy(), results[1][0].cpu().numpy(), rtol=1e-5, atol=1e-7)
     assert torch.equal(results[0][2], results[1][2])
+
+
+@pytest.mark.parametrize("case", ["cfg1", "cfg1_klstop", "cfg3_reduced"])
+def test_ppo_update_draws_the_reference_random_stream(ref, case):
+    """update() without explicit permutations: the library draws them from torch's CPU generator state on background
+    threads (cpprl_b200_ppo_update_rng).  After torch.manual_seed(s) that must be the update the reference performs
+    after torch::manual_seed(s) -- bit-identical to passing torch.randperm's permutations explicitly -- and must leave
+    torch's generator where the reference's torch::randperm calls leave it (one per epoch STARTED, ppo.cpp:63-104)."""
+    w = {"cfg1": CONFIGS["cfg1"], "cfg1_klstop": CONFIGS["cfg1"].scaled(kl_target=0.01, learning_rate=3e-2),
+         "cfg3_reduced": CONFIGS["cfg3"].scaled(T=32, N=64, num_epoch=3, num_mini_batch=4)}[case]
+    seed = 5
+    r = synth_rollout(w, seed)
+    sess = H.make_ref_session(ref, w, init_seed=seed)
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    sides = [H.make_gpu_side(w, r, sess.get_params(), sess.get_normalizer() if w.normalize_obs else None) for _ in range(2)]
+    algos = [api.PPO(p, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef, w.entropy_coef,
+                     w.learning_rate, w.epsilon, 0.5, w.kl_target) for p, _ in sides]
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    stopped_early = False
+    for upd in range(3):
+        s = 4000 + upd
+        sess.compute_returns(r["next_value"], w.use_gae, w.gamma, w.tau)
+        want_stats, _ = sess.update(1.0, perm_seed=s)
+        for _, st in sides:
+            st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        explicit = np.array([d.value for d in algos[0].update(sides[0][1], 1.0, perms=H.draw_perms(s, w.rows, w.num_epoch))], np.float32)
+        torch.manual_seed(s)
+        drawn = np.array([d.value for d in algos[1].update(sides[1][1], 1.0)], np.float32)
+        after = torch.rand(4)
+        assert np.array_equal(explicit, drawn, equal_nan=True), (explicit, drawn)  # (0/0 means when the first minibatch stops)
+        assert torch.equal(sides[0][0].params, sides[1][0].params), "library-drawn permutations differ from torch.randperm's"
+        np.testing.assert_allclose(drawn[:4], want_stats[:4], rtol=1e-4, atol=2e-6, equal_nan=True)
+        # epochs the reference started = randperm calls it made
+        started = w.num_epoch
+        if len(want_stats) > 5:
+            stopped_early = True
+            started = int(want_stats[5]) // w.num_mini_batch + 1
+        torch.manual_seed(s)
+        for _ in range(started):
+            torch.randperm(w.rows)
+        assert torch.equal(after, torch.rand(4)), f"generator state after the update is not the one after {started} randperm calls"
+    assert stopped_early == (case == "cfg1_klstop")
