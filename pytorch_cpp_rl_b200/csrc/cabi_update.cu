@@ -22,7 +22,7 @@ struct cpprl_b200_comm;
 namespace cpprl_b200
 {
 // from mlp_update.cu / returns_scan.cu
-size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta);
+size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta, bool tc, int img_tail, int g_tail);
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s);
 int launch_advantage_moments(const float *d_returns, const float *d_value_preds, int64_t n, double *d_sums, void *d_ws,
                              cudaStream_t s);
@@ -99,17 +99,38 @@ bool gru_param_offsets(const cpprl_b200_policy &p, GruParamOffsets &po)
     return true;
 }
 
-ImageLayout make_image_layout(int Dp, int Ap)
+ImageLayout make_image_layout(int Dp, int Ap, bool tc = false)
 {
     ImageLayout il;
     int o = 0;
-    for (int t = 0; t < 2; ++t)
+    il.tc = tc ? 1 : 0;
+    if (tc)
     {
-        il.w1t[t] = o, o += Dp * kHid;
-        il.b1[t] = o, o += kHid;
-        il.w2t[t] = o, o += kHid * kHid;
-        il.w2n[t] = o, o += kHid * kHid;
-        il.b2[t] = o, o += kHid;
+        // matrices first (one row per tensor-memory lane, loaded straight from global memory), then the tail the
+        // kernel keeps in shared memory
+        for (int t = 0; t < 2; ++t)
+            il.w1t[t] = o, o += kHid * Dp;
+        for (int t = 0; t < 2; ++t)
+            il.w2t[t] = o, o += kHid * kHid;
+        for (int t = 0; t < 2; ++t)
+            il.w2n[t] = o, o += kHid * kHid;
+        il.tail = o;
+        for (int t = 0; t < 2; ++t)
+            il.b1[t] = o, o += kHid;
+        for (int t = 0; t < 2; ++t)
+            il.b2[t] = o, o += kHid;
+    }
+    else
+    {
+        il.tail = 0;
+        for (int t = 0; t < 2; ++t)
+        {
+            il.w1t[t] = o, o += Dp * kHid;
+            il.b1[t] = o, o += kHid;
+            il.w2t[t] = o, o += kHid * kHid;
+            il.w2n[t] = o, o += kHid * kHid;
+            il.b2[t] = o, o += kHid;
+        }
     }
     il.wo = o, o += Ap * kHid;
     il.bo = o, o += Ap;
@@ -262,29 +283,43 @@ struct Scratch
 struct Plan
 {
     int R = 0, grid = 0, n_active = 0, per_cta = 0;
+    bool tc = false; // tensor-core variant of the fused kernel (mlp_tc.cuh)
+    ImageLayout il;
 };
 
-// Tile rows and grid for a minibatch of B rows: the smallest tile that still gives every SM at most one
-// tile, falling back to the smaller tile when the shared-memory plan of the larger one does not fit.
+// CPPRL_B200_MLP_TC=0 keeps every update on the fp32 CUDA-core kernel (A/B runs)
+bool mlp_tc_enabled()
+{
+    const char *e = std::getenv("CPPRL_B200_MLP_TC");
+    return !(e && e[0] == '0');
+}
+
+// Tile rows, grid and kernel variant for a minibatch of B rows: the smallest tile that still gives every SM at most one
+// tile, falling back to the smaller tile when the shared-memory plan of the larger one does not fit.  Minibatches that
+// fill the chip with 64-row tiles (more than 32 rows per SM) and have at most 32 observation columns train on the
+// tensor-core variant: 56-row tiles, so that 148 CTAs cover an 8192-row minibatch in one wave.
 // Training launches keep at least 16 CTAs so that the phase-2 slice of the parameter vector each CTA reduces,
 // steps and keeps resident in shared memory stays small; CTAs beyond the tile count only take part in phase 2.
-int choose_plan(int64_t B, const ImageLayout &il, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan)
+int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan)
 {
     const int sms = sm_count();
-    int R = (B <= 32ll * sms) ? 32 : 64;
-    const int64_t tiles32 = (B + 31) / 32, tiles64 = (B + 63) / 64;
-    auto shape = [&](int r, Plan &pl) {
-        const int64_t tiles = r == 32 ? tiles32 : tiles64;
+    auto shape = [&](int r, bool tc, Plan &pl) {
+        const int64_t tiles = (B + r - 1) / r;
         pl.R = r;
+        pl.tc = tc;
+        pl.il = make_image_layout(Dp, Ap, tc);
         pl.n_active = static_cast<int>(tiles < sms ? tiles : sms);
         pl.grid = training ? std::max(pl.n_active, std::min(16, sms)) : pl.n_active;
         const int p4 = po.Pstride - kNumStats; // parameter count rounded up to 4
         pl.per_cta = training ? round_up((p4 + pl.grid - 1) / pl.grid, 4) : 0;
-        return mlp_update_smem_bytes(r, il.floats, po.Pstride, Dp, Ap, pl.per_cta);
+        return mlp_update_smem_bytes(r, pl.il.floats, po.Pstride, Dp, Ap, pl.per_cta, tc, pl.il.tail, po.wv);
     };
-    if (R == 64 && shape(64, plan) > 227 * 1024)
+    if (training && B > 32ll * sms && Dp <= 32 && mlp_tc_enabled() && shape(kTcRows, true, plan) <= 227 * 1024)
+        return 0;
+    int R = (B <= 32ll * sms) ? 32 : 64;
+    if (R == 64 && shape(64, false, plan) > 227 * 1024)
         R = 32;
-    if (shape(R, plan) > 227 * 1024)
+    if (shape(R, false, plan) > 227 * 1024)
         return fail(CPPRL_B200_EUNSUPPORTED, "update: observation / action size needs more than 227 KB of shared memory");
     return 0;
 }
@@ -702,14 +737,14 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     mlp_param_offsets(*policy, po);
     const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
-    const ImageLayout il = make_image_layout(Dp, Ap);
     const CommView view = comm_view(h->comm);
     // sharded: tiles are sized for the expected local share of a minibatch; the grid (identical on every rank, CTA b
     // pairs with CTA b of the peers) covers the whole box-wide slice of parameters, and ragged minibatches that
     // exceed it simply take more than one tile per CTA
     const int64_t plan_rows = sharded ? (mbs + view.world - 1) / view.world : mbs;
-    if (int rc = choose_plan(plan_rows, il, po, Dp, Ap, true, h->plan))
+    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, h->plan))
         return rc;
+    const ImageLayout il = h->plan.il;
     if (sharded)
     {
         const int sms = sm_count();
@@ -717,7 +752,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
         h->plan.grid = std::max(h->plan.grid, std::min(16, sms));
         h->plan.n_active = h->plan.grid;
         h->plan.per_cta = round_up((po.Pstride - kNumStats + h->plan.grid - 1) / h->plan.grid, 4);
-        if (mlp_update_smem_bytes(h->plan.R, il.floats, po.Pstride, Dp, Ap, h->plan.per_cta) > 227 * 1024)
+        if (mlp_update_smem_bytes(h->plan.R, il.floats, po.Pstride, Dp, Ap, h->plan.per_cta, h->plan.tc, il.tail, po.wv) > 227 * 1024)
             return fail(CPPRL_B200_EUNSUPPORTED, "update: observation / action size needs more than 227 KB of shared memory");
         if (static_cast<int64_t>(h->plan.grid) * (h->plan.per_cta + kNumStats) > view.x_stride)
             return fail(CPPRL_B200_EINVAL, "ppo_update: the communicator was created for fewer parameters than this policy has");
@@ -745,6 +780,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     a.n_steps = static_cast<int>(h->n_mb);
     a.n_active = h->plan.n_active;
     a.per_cta = h->plan.per_cta;
+    a.tc = h->plan.tc ? 1 : 0;
     a.adv_sums = sharded ? comm_local_adv(h->comm) : h->scratch.adv_sums;
     if (sharded)
         a.adv_seq = ++*comm_update_seq(h->comm);
@@ -1302,7 +1338,6 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     mlp_param_offsets(*policy, po);
     const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
-    const ImageLayout il = make_image_layout(Dp, Ap);
     Plan plan;
     const CommView view = comm_view(h->comm);
     // sharded: CTA b pairs with CTA b of the peers and the exchange records sit at blockIdx * (per_cta + stats), so the
@@ -1310,8 +1345,9 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     // not from this rank's own row count (shards may differ by one environment, api.shard_range); a rank that holds
     // more rows than the plan simply walks more than one tile per CTA
     const int64_t plan_rows = sharded ? (rows_global + view.world - 1) / view.world : rows;
-    if (int rc = choose_plan(plan_rows, il, po, Dp, Ap, true, plan))
+    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, plan))
         return rc;
+    const ImageLayout il = plan.il;
     if (sharded)
     {
         plan.n_active = plan.grid;
@@ -1359,6 +1395,7 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.n_steps = 1;
     a.n_active = plan.n_active;
     a.per_cta = plan.per_cta;
+    a.tc = plan.tc ? 1 : 0;
     a.adv_sums = nullptr;
     a.algo = kAlgoA2C;
     a.c_actor = 1.f;
@@ -1525,10 +1562,10 @@ static int evaluate_impl(EvalScratch &es, const cpprl_b200_policy *policy, const
     mlp_param_offsets(*policy, po);
     const int Dp = round_up(static_cast<int>(policy->obs_dim), 8);
     const int Ap = round_up(static_cast<int>(policy->num_actions), 4);
-    const ImageLayout il = make_image_layout(Dp, Ap);
     Plan plan;
-    if (int rc = choose_plan(B, il, po, Dp, Ap, false, plan))
+    if (int rc = choose_plan(B, po, Dp, Ap, false, plan))
         return rc;
+    const ImageLayout il = plan.il;
     if (int rc = g_eval_scratch.ensure(il.floats, 0, 0))
         return rc;
     MlpUpdateArgs a;

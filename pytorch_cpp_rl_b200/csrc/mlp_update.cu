@@ -27,6 +27,7 @@
 #include "common.cuh"
 #include "mlp_update.cuh"
 #include "mlp_blocks.cuh"
+#include "mlp_tc.cuh"
 
 namespace cpprl_b200
 {
@@ -40,6 +41,10 @@ struct SmemPlan
 {
     int img, gsm, g2, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, xn, actn, scn, rowidn, actin, norm, red, own, sig,
         misc, total;
+    // tensor-core variant: hi / lo operand planes (see mlp_tc.cuh); offsets in floats like the others
+    int xb, xf, hb[2], hf[2];
+    int img_base; // first float of the GLOBAL image that the shared-memory image holds (tensor-core variant: its tail)
+    int g_base;   // first gradient index the shared-memory accumulator `gsm` holds (tensor-core variant: po.wv)
 };
 
 // Gradients whose sums are formed by more than one thread (head weights and b2: the two row halves of P5b; b1: the
@@ -52,17 +57,40 @@ struct SmemPlan
 __host__ __device__ inline int g2_floats(int Ap) { return Ap * kHid + kHid; }
 constexpr int kG2BiasFloats = 2 * kHid + 2 * 3 * kHid;
 
-__host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
+__host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta, bool tc = false,
+                                              int img_tail = 0, int g_tail = 0)
 {
     const int LD = R + 4;
     SmemPlan p;
     int o = 0;
-    p.img = o, o += img_floats;
-    p.gsm = o, o += (Pstride + 3) & ~3;
+    // tensor-core variant: the tower matrices live in tensor memory and their gradients in registers; shared memory
+    // holds the image's tail (biases, heads) and the gradient accumulators from the value head on (po.wv ..)
+    p.img_base = tc ? img_tail : 0;
+    p.g_base = tc ? g_tail : 0;
+    p.img = o, o += img_floats - p.img_base;
+    p.gsm = o, o += ((Pstride + 3) & ~3) - p.g_base;
     p.g2 = o, o += g2_floats(Ap); // second accumulators of the gradients that several threads share (see G2 below)
-    p.x = o, o += Dp * LD;
-    for (int t = 0; t < 2; ++t)
-        p.h1[t] = o, o += kHid * LD;
+    p.xb = p.xf = p.hb[0] = p.hb[1] = p.hf[0] = p.hf[1] = 0;
+    if (tc)
+    {
+        // operand planes, hi then lo each (bytes / 4); the row-major planes read one non-existent 8-row group past
+        // their end (N = 64 instructions over R <= 56 rows): something must follow them, which the order guarantees
+        const int lbo_b = (R / 8) * 128 + 16, plane_b = 16 * lbo_b, plane_f = (R / 4) * 1024, plane_xf = (R / 4) * 528;
+        const int plane_xb = (Dp / 4) * lbo_b;
+        p.xb = o, o += 2 * plane_xb / 4;
+        for (int t = 0; t < 2; ++t)
+            p.hb[t] = o, o += 2 * plane_b / 4;
+        p.xf = o, o += 2 * plane_xf / 4;
+        for (int t = 0; t < 2; ++t)
+            p.hf[t] = o, o += 2 * plane_f / 4;
+        p.x = p.h1[0] = p.h1[1] = 0; // (fp32 x / h1 tiles are not kept)
+    }
+    else
+    {
+        p.x = o, o += Dp * LD;
+        for (int t = 0; t < 2; ++t)
+            p.h1[t] = o, o += kHid * LD;
+    }
     for (int t = 0; t < 2; ++t)
         p.h2[t] = o, o += kHid * LD;
     p.logit = o, o += Ap * LD;
@@ -88,7 +116,7 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     }
     p.own = o, o += 3 * per_cta;                       // this CTA's slice of params / Adam exp_avg / exp_avg_sq
     p.sig = o, o += 2 * Ap;                            // Normal head: {sigma^2, log sigma} per action
-    p.misc = o, o += 32;
+    p.misc = o, o += 48;
     p.total = o;
     return p;
 }
@@ -106,24 +134,35 @@ __device__ __forceinline__ void image_scatter(const MlpUpdateArgs &a, float *__r
         if (i >= po.w1[t] && i < po.w1[t] + kHid * D)
         {
             const int e = i - po.w1[t], j = e / D, k = e - j * D;
-            image[il.w1t[t] + k * kHid + perm16(j)] = v;
+            if (il.tc)
+                image[il.w1t[t] + j * a.Dp + k] = v;
+            else
+                image[il.w1t[t] + k * kHid + perm16(j)] = v;
             return;
         }
         if (i >= po.b1[t] && i < po.b1[t] + kHid)
         {
-            image[il.b1[t] + perm16(i - po.b1[t])] = v;
+            image[il.b1[t] + (il.tc ? i - po.b1[t] : perm16(i - po.b1[t]))] = v;
             return;
         }
         if (i >= po.w2[t] && i < po.w2[t] + kHid * kHid)
         {
             const int e = i - po.w2[t], j = e >> 6, k = e & 63;
-            image[il.w2t[t] + k * kHid + perm16(j)] = v;
-            image[il.w2n[t] + j * kHid + perm16(k)] = v;
+            if (il.tc)
+            {
+                image[il.w2t[t] + j * kHid + k] = v;
+                image[il.w2n[t] + k * kHid + j] = v;
+            }
+            else
+            {
+                image[il.w2t[t] + k * kHid + perm16(j)] = v;
+                image[il.w2n[t] + j * kHid + perm16(k)] = v;
+            }
             return;
         }
         if (i >= po.b2[t] && i < po.b2[t] + kHid)
         {
-            image[il.b2[t] + perm16(i - po.b2[t])] = v;
+            image[il.b2[t] + (il.tc ? i - po.b2[t] : perm16(i - po.b2[t]))] = v;
             return;
         }
     }
@@ -202,18 +241,24 @@ __device__ __forceinline__ void grid_wait(unsigned int *bar, unsigned int target
 }
 
 // ---- the kernel -------------------------------------------------------------------------------------
-template <int R>
+template <int R, bool TC>
 __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpdateArgs a)
 {
-    constexpr int LD = Tile<R>::LD;
+    constexpr int LD = R + 4;
     extern __shared__ __align__(16) float smem[];
-    const SmemPlan sp = make_plan(R, a.il.floats, a.po.Pstride, a.Dp, a.Ap, a.per_cta);
+    const SmemPlan sp = make_plan(R, a.il.floats, a.po.Pstride, a.Dp, a.Ap, a.per_cta, TC, a.il.tail, a.po.wv);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tower = tid >> 7, u = tid & 127; // warps 0-3 run the actor tower, 4-7 the critic tower
     const int jb = u & 15, rb = u >> 4;
-    // every pointer is `smem + integer` so the compiler keeps the shared state space (LDS/STS, never generic LD/ST)
-    float *img = smem + sp.img;
-    float *gsm = smem + sp.gsm;
+    (void)jb, (void)rb;
+    // tensor-core variant: thread = (tensor-memory lane F = hidden unit jF of tower tF, column half ch of the tile)
+    const int q4 = warp & 3, ch = warp >> 2, F = 32 * q4 + lane, tF = F >> 6, jF = F & 63;
+    (void)ch, (void)tF, (void)jF;
+    // every pointer is `smem + integer` so the compiler keeps the shared state space (LDS/STS, never generic LD/ST).
+    // `img` and `gsm` are indexed with GLOBAL image / gradient offsets: the tensor-core variant keeps only their tails
+    // in shared memory (sp.img_base / sp.g_base are zero otherwise)
+    float *img = smem + (sp.img - sp.img_base);
+    float *gsm = smem + (sp.gsm - sp.g_base);
     float *G2 = smem + sp.g2;
     float *G2_WO = G2, *G2_WV = G2 + a.Ap * kHid;
     float *G2_B2 = smem + sp.red, *G2_B1 = G2_B2 + 2 * kHid; // overlay RED (idle in phase 1)
@@ -228,6 +273,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     long long *ROWID = reinterpret_cast<long long *>(smem + sp.rowid);
     float *MISC = smem + sp.misc;
     void *mbar = MISC + 24;
+    // tensor-core variant: five mbarriers (one per contraction stage of a tile) and the tensor-memory base address
+    uint64_t *tcbar = reinterpret_cast<uint64_t *>(MISC + 26);
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(MISC + 38);
     const float *w1t_img = img + (tower ? a.il.w1t[1] : a.il.w1t[0]);
     const float *b1_img = img + (tower ? a.il.b1[1] : a.il.b1[0]);
     const float *w2t_img = img + (tower ? a.il.w2t[1] : a.il.w2t[0]);
@@ -235,6 +283,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     const float *b2_img = img + (tower ? a.il.b2[1] : a.il.b2[0]);
     const int po_w1 = tower ? a.po.w1[1] : a.po.w1[0], po_b1 = tower ? a.po.b1[1] : a.po.b1[0];
     const int po_w2 = tower ? a.po.w2[1] : a.po.w2[0], po_b2 = tower ? a.po.b2[1] : a.po.b2[0];
+    (void)X, (void)h1t, (void)w1t_img, (void)b1_img, (void)w2t_img, (void)w2n_img, (void)b2_img, (void)po_w1, (void)po_b1, (void)po_w2,
+        (void)po_b2, (void)G2_B1, (void)tcbar, (void)tmem_slot;
 
     const int G = gridDim.x;
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
@@ -298,7 +348,51 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         MISC[0] = mean;
         MISC[1] = denom;
         mbar_init(mbar, 1);
+        if (TC)
+            for (int b = 0; b < 5; ++b)
+                mbar_init(&tcbar[b], b == 0 ? 1 : 2); // layer 1 has one issuing thread, the tower-wise stages two
     }
+    uint32_t tm = 0;        // tensor-memory base (tensor-core variant)
+    uint32_t tc_parity = 0; // parity of the four per-tile mbarriers: tiles processed so far & 1
+    (void)tm, (void)tc_parity;
+    if (TC)
+    {
+        if (warp == 0)
+        {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(mtc::kTmemCols)
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        mtc::fence_before();
+        __syncthreads();
+        mtc::fence_after();
+        tm = *tmem_slot;
+    }
+    const uint32_t lane_base = tm + (static_cast<uint32_t>(32 * q4) << 16); // this warp's 32 tensor-memory lanes
+    (void)lane_base;
+    // Matrix rows -> tensor memory in two steps, so that the global (L2) loads are in flight while something else runs:
+    // tc_fetch32 issues the eight 16-byte loads of this thread's 32 floats, tc_store32 splits them into hi / lo planes
+    // and writes columns [col, col + 32) / [col + 64, ..) of the thread's lane (warp-collective tcgen05.st).
+    auto tc_fetch32 = [&](const float *src, float4 (&w)[8]) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            w[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
+    };
+    auto tc_store32 = [&](uint32_t col, const float4 (&w)[8]) {
+        const float4 lo4[4] = {w[0], w[1], w[2], w[3]}, hi4[4] = {w[4], w[5], w[6], w[7]};
+        mtc::store_split16(col, 64, lo4);
+        mtc::store_split16(col + 16, 64, hi4);
+    };
+    // every exit path of the tensor-core variant hands its tensor memory back first (CTA-uniform decisions only)
+    auto leave = [&]() {
+        if (TC)
+        {
+            mtc::fence_before();
+            __syncthreads();
+            if (warp == 0)
+                asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(mtc::kTmemCols) : "memory");
+        }
+    };
     const int n_tiles_max = (a.B + R - 1) / R;
     (void)n_tiles_max;
     float *NMEAN = smem + sp.norm, *NSTD = NMEAN + Dp, *NCLIP = NSTD + Dp;
@@ -349,7 +443,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         {
             constexpr int LPR = kUpdThreads / R; // lanes per row: consecutive lanes fetch consecutive elements of a row
             const int r = tid / LPR, q = tid % LPR;
-            const long long row = ROWIDN[r];
+            const long long row = r < R ? ROWIDN[r] : -1; // (R need not divide the thread count)
             if (row >= 0)
             {
                 const float *src = a.obs + row * D;
@@ -391,7 +485,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 #pragma unroll 4
         for (int e = tid; e < Dp * R; e += kUpdThreads)
         {
-            const int k = e / R, r = e - k * R; // R is a power of two
+            const int k = e / R, r = e - k * R; // R is a compile-time constant
             const bool ok = k < D && r < nrows;
             float x = XN[k * LD + r];
             if (norm)
@@ -399,7 +493,23 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 x = (x - NMEAN[k]) / NSTD[k];
                 x = fminf(fmaxf(x, -clip), clip);
             }
-            X[k * LD + r] = ok ? x : 0.f;
+            x = ok ? x : 0.f;
+            if (TC)
+            {
+                // the observation tile as the two tensor-core operands it feeds, hi / lo planes each:
+                // row-major [row][column] (layer 1) and column-major [column][row] (dW1); rows past the tile are ZERO
+                using GeoT = mtc::Geo<TC ? R : 8>;
+                const float hi = mtc::tf32_hi(x), lo = x - hi;
+                unsigned char *xb = reinterpret_cast<unsigned char *>(smem + sp.xb), *xf = reinterpret_cast<unsigned char *>(smem + sp.xf);
+                const uint32_t ob = 16u * r + (k >> 2) * GeoT::kLboB + (k & 3) * 4u;
+                const uint32_t of = 16u * k + (r >> 2) * GeoT::kLboXF + (r & 3) * 4u;
+                *reinterpret_cast<float *>(xb + ob) = hi;
+                *reinterpret_cast<float *>(xb + GeoT::plane_xb(Dp) + ob) = lo;
+                *reinterpret_cast<float *>(xf + of) = hi;
+                *reinterpret_cast<float *>(xf + GeoT::kPlaneXF + of) = lo;
+            }
+            else
+                X[k * LD + r] = x;
         }
         if (a.head == 1)
 #pragma unroll 2
@@ -433,7 +543,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     bar_target += G;
     grid_wait(a.barrier, bar_target);
     if (stopped)
+    {
+        leave();
         return;
+    }
     const float inv_b = 1.f / static_cast<float>(a.B_norm);
     uint32_t img_phase = 0;
     bool staged = false; // the first work item of the next step was prefetched during this one
@@ -458,21 +571,34 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         const int n_act = min(n_tiles, G);
         const bool active = static_cast<int>(blockIdx.x) < n_act; // owns tiles of this minibatch, publishes a partial
         CPPRL_MARK(0);
+        float4 wreg[8], w1reg[4]; // matrix rows on their way to tensor memory (tensor-core variant)
+        (void)wreg, (void)w1reg;
         // ---- (re)load the weight image with one TMA bulk copy per 32 KB, clear the gradient accumulator ------
         if (active)
         {
             if (tid == 0)
             {
-                const uint32_t bytes = static_cast<uint32_t>(a.il.floats) * 4u;
+                // (tensor-core variant: only the image's tail -- biases and heads -- comes to shared memory)
+                const uint32_t bytes = static_cast<uint32_t>(a.il.floats - sp.img_base) * 4u;
                 // the image was written by generic-proxy stores of other CTAs (ordered by the grid barrier); make
                 // them visible to the async proxy that performs the bulk copy
                 asm volatile("fence.proxy.async;" ::: "memory");
                 mbar_expect_tx(mbar, bytes);
                 for (uint32_t off = 0; off < bytes; off += 32768u)
-                    bulk_g2s(reinterpret_cast<char *>(img) + off, reinterpret_cast<const char *>(a.image) + off,
-                             min(32768u, bytes - off), mbar);
+                    bulk_g2s(reinterpret_cast<char *>(smem + sp.img) + off,
+                             reinterpret_cast<const char *>(a.image + sp.img_base) + off, min(32768u, bytes - off), mbar);
             }
-            for (int i = tid; i < Pstride; i += kUpdThreads)
+            if (TC)
+            {
+                // this lane's row of W2 (the 32 columns of this thread's half) and of W1 (16 columns): the global image is
+                // complete (grid barrier); the loads fly while the shared-memory image arrives
+                tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]) + jF * kHid + 32 * ch, wreg);
+                const float *w1src = a.image + (tF ? a.il.w1t[1] : a.il.w1t[0]) + jF * Dp + 16 * ch;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    w1reg[i] = 16 * ch + 4 * i < Dp ? __ldcg(reinterpret_cast<const float4 *>(w1src) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            for (int i = sp.g_base + tid; i < Pstride; i += kUpdThreads)
                 gsm[i] = 0.f;
             for (int i = tid; i < g2_floats(a.Ap); i += kUpdThreads)
                 G2[i] = 0.f;
@@ -496,7 +622,24 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 SIG[2 * tid] = sigma * sigma;
                 SIG[2 * tid + 1] = logf(sigma);
             }
+            CPPRL_MARK(26);
+            if (TC)
+            {
+                tc_store32(lane_base + mtc::kColW + 32 * ch, wreg);
+                mtc::store_split16(lane_base + mtc::kColX + 16 * ch, 32, w1reg);
+                mtc::wait_st();
+                mtc::fence_before();
+            }
         }
+        // gradients of the tower matrices of this minibatch: registers of the tensor-core variant
+        float acc_w2[TC ? 32 : 1], acc_w1[TC ? 16 : 1], acc_b1 = 0.f, acc_b2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < (TC ? 32 : 1); ++i)
+            acc_w2[i] = 0.f;
+#pragma unroll
+        for (int i = 0; i < (TC ? 16 : 1); ++i)
+            acc_w1[i] = 0.f;
+        (void)acc_w2, (void)acc_w1, (void)acc_b1, (void)acc_b2;
         __syncthreads();
         const float ce_b = a.c_entropy * inv_b;
         CPPRL_MARK(1);
@@ -512,11 +655,110 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             const bool has_next = nstep < a.n_steps && (nstep == step || ntile * R < rows_of(nstep));
             finalize_stage(nrows); // the rows of THIS item are in place (waits for their cp.async group)
             const long long next_row = has_next ? item_rowid(nstep, ntile) : -1;
+            if (TC)
+            {
+                using GeoT = mtc::Geo<TC ? R : 8>;
+                constexpr int CH = GeoT::CH;
+                const uint32_t xb_hi = smem_u32(smem + sp.xb), xb_lo = xb_hi + GeoT::plane_xb(Dp);
+                unsigned char *hb_hi = reinterpret_cast<unsigned char *>(smem + sp.hb[tF]), *hb_lo = hb_hi + GeoT::kPlaneB;
+                unsigned char *hf_hi = reinterpret_cast<unsigned char *>(smem + sp.hf[tF]), *hf_lo = hf_hi + GeoT::kPlaneF;
+                CPPRL_MARK(20);
+                // ---- T1: layer 1 of both towers: D[F][r] = sum_k W1[F][k] x[r][k]  (A = W1 in tensor memory) --------
+                mtc::fence_async_smem(); // the operand planes finalize_stage wrote -> visible to the tensor core
+                mtc::fence_before();
+                if (tid < R)
+                    ROWIDN[tid] = next_row; // read by prefetch_issue after the next barrier
+                __syncthreads();
+                if (tid == 0)
+                {
+                    mtc::fence_after();
+                    const uint32_t d = tm + mtc::kColA, ah = tm + mtc::kColX, al = ah + 32, id = mtc::idesc_n(64);
+                    switch (Dp / 8) // (k-steps are compile-time constants: every descriptor is base + immediate)
+                    {
+                    case 1: mtc::issue_3xtf32<0, 1, GeoT::kLboB>(d, ah, al, xb_hi, xb_lo, id); break;
+                    case 2: mtc::issue_3xtf32<0, 2, GeoT::kLboB>(d, ah, al, xb_hi, xb_lo, id); break;
+                    case 3: mtc::issue_3xtf32<0, 3, GeoT::kLboB>(d, ah, al, xb_hi, xb_lo, id); break;
+                    default: mtc::issue_3xtf32<0, 4, GeoT::kLboB>(d, ah, al, xb_hi, xb_lo, id); break;
+                    }
+                    mtc::commit(&tcbar[0]);
+                }
+                if (has_next)
+                {
+                    prefetch_issue(); // lands while this tile computes (and during phase 2 when it belongs to the next minibatch)
+                    staged = nstep != step;
+                }
+                mbar_wait(&tcbar[0], tc_parity);
+                mtc::fence_after();
+                CPPRL_MARK(2);
+                // h1 = tanh(. + b1) as the two operands it feeds: row-major [row][unit] (layer 2) and unit-major
+                // [unit][row] (dW2), hi / lo planes each
+                {
+                    const float bias = img[(tF ? a.il.b1[1] : a.il.b1[0]) + jF];
+                    const uint32_t ob = (jF >> 2) * GeoT::kLboB + (jF & 3) * 4u;
+#pragma unroll
+                    for (int c = 0; c < CH; c += 4)
+                    {
+                        float v[4], hi[4], lo[4];
+                        mtc::ld4(lane_base + mtc::kColA + ch * CH + c, v);
+                        const int r0 = ch * CH + c;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                        {
+                            const float h = tanhf(v[i] + bias);
+                            hi[i] = mtc::tf32_hi(h), lo[i] = h - hi[i];
+                            *reinterpret_cast<float *>(hb_hi + 16u * (r0 + i) + ob) = hi[i];
+                            *reinterpret_cast<float *>(hb_lo + 16u * (r0 + i) + ob) = lo[i];
+                        }
+                        const uint32_t of = 16u * jF + (r0 >> 2) * GeoT::kLboF;
+                        *reinterpret_cast<float4 *>(hf_hi + of) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+                        *reinterpret_cast<float4 *>(hf_lo + of) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+                    }
+                }
+                mtc::fence_async_smem();
+                mtc::fence_before();
+                __syncthreads();
+                CPPRL_MARK(21);
+                // ---- T2: layer 2, one instruction chain per tower (lanes 0..63 of the first, 64..127 of the second) ----
+                if ((tid & 127) == 0) // one issuing thread per tower (warps 0 and 4): the chains are independent
+                {
+                    const int t = tid >> 7;
+                    mtc::fence_after();
+                    const uint32_t b_hi = smem_u32(smem + sp.hb[t]);
+                    mtc::issue_3xtf32<0, kHid / 8, GeoT::kLboB>(tm + mtc::kColA + 64 * t, tm + mtc::kColW, tm + mtc::kColW + 64, b_hi,
+                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(64));
+                    mtc::commit(&tcbar[1]);
+                }
+                // W2^T (this lane's row of the transposed image) for the data gradient: in flight during the chain and E2
+                tc_fetch32(a.image + (tF ? a.il.w2n[1] : a.il.w2n[0]) + jF * kHid + 32 * ch, wreg);
+                mbar_wait(&tcbar[1], tc_parity);
+                mtc::fence_after();
+                CPPRL_MARK(22);
+                {
+                    const float bias = img[(tF ? a.il.b2[1] : a.il.b2[0]) + jF];
+                    float *h2row = smem + sp.h2[0] + F * LD + ch * CH; // (the two towers' h2 tiles are contiguous)
+#pragma unroll
+                    for (int c = 0; c < CH; c += 4)
+                    {
+                        float v[4];
+                        mtc::ld4(lane_base + mtc::kColA + 64 * tF + ch * CH + c, v);
+                        *reinterpret_cast<float4 *>(h2row + c) =
+                            make_float4(tanhf(v[0] + bias), tanhf(v[1] + bias), tanhf(v[2] + bias), tanhf(v[3] + bias));
+                    }
+                }
+                CPPRL_MARK(23);
+                // layer 2 has consumed W2: its columns take W2^T
+                tc_store32(lane_base + mtc::kColW + 32 * ch, wreg);
+                mtc::wait_st();
+                mtc::fence_before();
+                __syncthreads();
+            }
+            else
+            {
             // ---- P1: layer 1, both towers ------------------------------------------------------------
             {
-                float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(w1t_img, X, Dp, jb, rb, acc);
-                store_tanh<R>(h1t, b1_img, jb, rb, acc);
+                float acc[4][Tile<TC ? 32 : R>::NG * 4];
+                gemm_cf<TC ? 32 : R>(w1t_img, X, Dp, jb, rb, acc);
+                store_tanh<TC ? 32 : R>(h1t, b1_img, jb, rb, acc);
             }
             if (tid < R)
                 ROWIDN[tid] = next_row; // read by prefetch_issue after the next barrier
@@ -524,12 +766,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             CPPRL_MARK(2);
             // ---- P2: layer 2 ---------------------------------------------------------------------------
             {
-                float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(w2t_img, h1t, kHid, jb, rb, acc);
-                store_tanh<R>(h2t, b2_img, jb, rb, acc);
+                float acc[4][Tile<TC ? 32 : R>::NG * 4];
+                gemm_cf<TC ? 32 : R>(w2t_img, h1t, kHid, jb, rb, acc);
+                store_tanh<TC ? 32 : R>(h2t, b2_img, jb, rb, acc);
             }
             __syncthreads();
-            if (has_next)
+            }
+            if (!TC && has_next)
             {
                 prefetch_issue(); // lands during P3..P8 (and phase 2 when it belongs to the next minibatch)
                 staged = nstep != step;
@@ -704,8 +947,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         src = STAT + (5 + item - (6 + A)) * LD, dst = a.po.slog + (item - (6 + A));
                     float sum = 0.f;
 #pragma unroll
-                    for (int r = 0; r < R; r += 32)
-                        sum += src[r + lane];
+                    for (int r = lane; r < R; r += 32)
+                        sum += src[r];
                     sum = warp_sum(sum);
                     if (lane == 0)
                         gsm[dst] += sum; // each destination has exactly one owner in this phase
@@ -714,14 +957,16 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             // ---- P5b: head weight gradients and dz2 = (head^T dout) * (1 - h2^2), in place over H2.
             // Thread = (feature k, half of the rows); dh for its rows stays in registers while the loop over the
             // runtime number of head outputs streams dout rows (broadcast LDS) against the cached h2 row.
+            // Tensor-core variant: (tower, k) is the thread's tensor-memory lane, and dz2 leaves as the two operands it
+            // feeds -- the A operand of dW2 in tensor memory and row-major [row][unit] planes for the data gradient.
             {
                 constexpr int NQ = R / 8; // float4 groups in this thread's half of the rows
-                const int k = u & 63, half = u >> 6;
-                const int nout = tower == 0 ? A : 1;
-                const float *dout = (tower == 0 ? DLOGIT : DVAL) + half * (R / 2);
-                const float *wh = img + (tower == 0 ? a.il.wo : a.il.wv) + k;
-                float *h2 = h2t + k * LD + half * (R / 2);
-                const int wbase = (tower == 0 ? a.po.wo : a.po.wv) + k;
+                const int tw = TC ? tF : tower, k = TC ? jF : (u & 63), half = TC ? ch : (u >> 6);
+                const int nout = tw == 0 ? A : 1;
+                const float *dout = (tw == 0 ? DLOGIT : DVAL) + half * (R / 2);
+                const float *wh = img + (tw == 0 ? a.il.wo : a.il.wv) + k;
+                float *h2 = smem + sp.h2[0] + (tw * kHid + k) * LD + half * (R / 2);
+                const int wbase = (tw == 0 ? a.po.wo : a.po.wv) + k;
                 float4 h[NQ], dh[NQ];
 #pragma unroll
                 for (int qd = 0; qd < NQ; ++qd)
@@ -750,7 +995,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     if (half == 0)
                         gsm[wbase + o * kHid] += g0 + g1;
                     else
-                        (tower == 0 ? G2_WO : G2_WV)[o * kHid + k] += g0 + g1;
+                        (tw == 0 ? G2_WO : G2_WV)[o * kHid + k] += g0 + g1;
                 }
                 float bsum = 0.f;
 #pragma unroll
@@ -762,29 +1007,177 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     dz.z = dh[qd].z * (1.f - h[qd].z * h[qd].z);
                     dz.w = dh[qd].w * (1.f - h[qd].w * h[qd].w);
                     bsum += (dz.x + dz.y) + (dz.z + dz.w);
-                    *reinterpret_cast<float4 *>(h2 + 4 * qd) = dz;
+                    if (TC)
+                    {
+                        using GeoT = mtc::Geo<TC ? R : 8>;
+                        unsigned char *db_hi = reinterpret_cast<unsigned char *>(smem + sp.hb[tw]), *db_lo = db_hi + GeoT::kPlaneB;
+                        const float z[4] = {dz.x, dz.y, dz.z, dz.w};
+                        float hi[4], lo[4];
+                        const int r0 = half * (R / 2) + 4 * qd;
+                        const uint32_t ob = (k >> 2) * GeoT::kLboB + (k & 3) * 4u;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                        {
+                            hi[i] = mtc::tf32_hi(z[i]), lo[i] = z[i] - hi[i];
+                            *reinterpret_cast<float *>(db_hi + 16u * (r0 + i) + ob) = hi[i]; // (layer 2 has consumed h1's planes)
+                            *reinterpret_cast<float *>(db_lo + 16u * (r0 + i) + ob) = lo[i];
+                        }
+                        mtc::st4(lane_base + mtc::kColA + r0, hi[0], hi[1], hi[2], hi[3]);
+                        mtc::st4(lane_base + mtc::kColA + 64 + r0, lo[0], lo[1], lo[2], lo[3]);
+                    }
+                    else
+                        *reinterpret_cast<float4 *>(h2 + 4 * qd) = dz;
                 }
-                if (half == 0)
+                if (TC)
+                    acc_b2 += bsum; // (a register per lane; the two halves meet when the partial is published)
+                else if (half == 0)
                     gsm[po_b2 + k] += bsum;
                 else
                     G2_B2[tower * kHid + k] += bsum;
             }
+            if (TC)
+            {
+                mtc::wait_st();
+                mtc::fence_async_smem();
+                mtc::fence_before();
+            }
             __syncthreads();
             CPPRL_MARK(6);
+            if (TC)
+            {
+                using GeoT = mtc::Geo<TC ? R : 8>;
+                constexpr int CH = GeoT::CH;
+                unsigned char *hf_hi = reinterpret_cast<unsigned char *>(smem + sp.hf[tF]), *hf_lo = hf_hi + GeoT::kPlaneF;
+                // ---- T3: data gradient dh1[F][r] = sum_j W2^T[F][j] dz2[r][j], one chain per tower -------------------
+                if ((tid & 127) == 0)
+                {
+                    const int t = tid >> 7;
+                    mtc::fence_after();
+                    const uint32_t b_hi = smem_u32(smem + sp.hb[t]);
+                    mtc::issue_3xtf32<0, kHid / 8, GeoT::kLboB>(tm + mtc::kColG + 64 * t, tm + mtc::kColW, tm + mtc::kColW + 64, b_hi,
+                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(64));
+                    mtc::commit(&tcbar[2]);
+                }
+                mbar_wait(&tcbar[2], tc_parity);
+                mtc::fence_after();
+                CPPRL_MARK(7);
+                // dz1 = dh1 * (1 - h1^2) -> tensor memory (the A operand of dW1, over W2^T which the chain has consumed); db1
+                {
+                    float bsum = 0.f;
+#pragma unroll
+                    for (int c = 0; c < CH; c += 4)
+                    {
+                        float v[4];
+                        mtc::ld4(lane_base + mtc::kColG + 64 * tF + ch * CH + c, v);
+                        const int r0 = ch * CH + c;
+                        const uint32_t of = 16u * jF + (r0 >> 2) * GeoT::kLboF;
+                        const float4 hh = *reinterpret_cast<const float4 *>(hf_hi + of), hl = *reinterpret_cast<const float4 *>(hf_lo + of);
+                        const float h1v[4] = {hh.x + hl.x, hh.y + hl.y, hh.z + hl.z, hh.w + hl.w}; // hi + lo == h1 exactly
+                        float hi[4], lo[4];
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                        {
+                            const float dz = v[i] * (1.f - h1v[i] * h1v[i]);
+                            bsum += dz;
+                            hi[i] = mtc::tf32_hi(dz), lo[i] = dz - hi[i];
+                        }
+                        mtc::st4(lane_base + mtc::kColW + r0, hi[0], hi[1], hi[2], hi[3]);
+                        mtc::st4(lane_base + mtc::kColW + 64 + r0, lo[0], lo[1], lo[2], lo[3]);
+                    }
+                    acc_b1 += bsum;
+                }
+                mtc::wait_st();
+                mtc::fence_before();
+                __syncthreads();
+                CPPRL_MARK(8);
+                // ---- T4: weight gradients of the tile: dW2[F][k] = sum_r dz2[F][r] h1[k][r] (one chain per tower's h1),
+                //          dW1[F][k] = sum_r dz1[F][r] x[k][r].  These sums are the parameters' gradients, where
+                //          cancellation makes the tensor core's truncating accumulation visible (a2c cfg2: 2e-4 of a
+                //          parameter through RMSprop's normalisation), so the rows run as TWO chains of at most four
+                //          full-size instructions each, drained into fp32 registers with round-to-nearest adds --------
+#pragma unroll
+                for (int pass = 0; pass < 2; ++pass)
+                {
+                    constexpr int KS = (TC ? R : 8) / 8, K0 = (KS + 1) / 2;
+                    const int k_begin = pass ? K0 : 0, k_end = pass ? KS : K0;
+                    if ((tid & 127) == 0 && k_begin < k_end)
+                    {
+                        const int t = tid >> 7;
+                        mtc::fence_after();
+                        const uint32_t b_hi = smem_u32(smem + sp.hf[t]), xf_hi = smem_u32(smem + sp.xf);
+                        const uint32_t d2 = tm + mtc::kColG + 64 * t, a2 = tm + mtc::kColA, d1 = tm + mtc::kColD1, a1 = tm + mtc::kColW;
+                        if (pass == 0)
+                        {
+                            mtc::issue_3xtf32<0, K0, GeoT::kLboF>(d2, a2, a2 + 64, b_hi, b_hi + GeoT::kPlaneF, mtc::idesc_n(64));
+                            if (t == 0)
+                                mtc::issue_3xtf32<0, K0, GeoT::kLboXF>(d1, a1, a1 + 64, xf_hi, xf_hi + GeoT::kPlaneXF, mtc::idesc_n(32));
+                        }
+                        else
+                        {
+                            mtc::issue_3xtf32<K0, KS, GeoT::kLboF>(d2, a2, a2 + 64, b_hi, b_hi + GeoT::kPlaneF, mtc::idesc_n(64));
+                            if (t == 0)
+                                mtc::issue_3xtf32<K0, KS, GeoT::kLboXF>(d1, a1, a1 + 64, xf_hi, xf_hi + GeoT::kPlaneXF, mtc::idesc_n(32));
+                        }
+                        mtc::commit(&tcbar[3 + pass]);
+                    }
+                    if (k_begin < k_end)
+                    {
+                        mbar_wait(&tcbar[3 + pass], tc_parity);
+                        mtc::fence_after();
+#pragma unroll
+                        for (int c = 0; c < 32; c += 4)
+                        {
+                            float v[4];
+                            mtc::ld4(lane_base + mtc::kColG + 64 * tF + 32 * ch + c, v);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                acc_w2[c + i] += v[i];
+                        }
+#pragma unroll
+                        for (int c = 0; c < 16; c += 4)
+                        {
+                            float v[4];
+                            mtc::ld4(lane_base + mtc::kColD1 + 16 * ch + c, v);
+#pragma unroll
+                            for (int i = 0; i < 4; ++i)
+                                acc_w1[c + i] += v[i];
+                        }
+                        if (pass == 0)
+                        {
+                            mtc::fence_before();
+                            __syncthreads(); // every lane has read the first chain's sums before the second overwrites them
+                            CPPRL_MARK(24);
+                        }
+                    }
+                }
+                tc_parity ^= 1u;
+                CPPRL_MARK(25);
+                if (tile + G < n_tiles)
+                {
+                    // another tile of this minibatch follows: its layer 2 needs W2 back in the columns dz1 now occupies
+                    tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]) + jF * kHid + 32 * ch, wreg);
+                    tc_store32(lane_base + mtc::kColW + 32 * ch, wreg);
+                    mtc::wait_st();
+                }
+                mtc::fence_before();
+                __syncthreads(); // the next tile's contractions reuse every accumulator and operand plane
+            }
+            else
+            {
             // ---- P6: dW2 += dz2 h1^T ------------------------------------------------------------------------
-            grad_w2<R>(h2t, h1t, u, gsm + po_w2);
+            grad_w2<TC ? 32 : R>(h2t, h1t, u, gsm + po_w2);
             __syncthreads();
             CPPRL_MARK(7);
             // ---- P7: dz1 = (W2^T dz2) * (1 - h1^2), in place over H1; db1 -----------------------------------
             {
-                float acc[4][Tile<R>::NG * 4];
-                gemm_cf<R>(w2n_img, h2t, kHid, jb, rb, acc);
+                float acc[4][Tile<TC ? 32 : R>::NG * 4];
+                gemm_cf<TC ? 32 : R>(w2n_img, h2t, kHid, jb, rb, acc);
 #pragma unroll
                 for (int q = 0; q < 4; ++q)
                 {
                     float bsum = 0.f;
 #pragma unroll
-                    for (int g = 0; g < Tile<R>::NG; ++g)
+                    for (int g = 0; g < Tile<TC ? 32 : R>::NG; ++g)
                     {
                         float *hp = h1t + (jb + 16 * q) * LD + 32 * g + 4 * rb;
                         const float4 h = *reinterpret_cast<const float4 *>(hp);
@@ -811,8 +1204,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             __syncthreads();
             CPPRL_MARK(8);
             // ---- P8: dW1 += dz1 x^T ---------------------------------------------------------------------------
-            grad_w1<R>(h1t, X, u, D, Dp, gsm + po_w1);
+            grad_w1<TC ? 32 : R>(h1t, X, u, D, Dp, gsm + po_w1);
             __syncthreads();
+            }
         } // tiles
 
         if (!training)
@@ -830,6 +1224,36 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 else
                     gsm[a.po.wv + k] += G2_WV[k];
             }
+            float *part = a.gpart + static_cast<size_t>(blockIdx.x) * Pstride;
+            if (TC)
+            {
+                // the tower gradients leave from registers: this lane's 32 columns of dW2, 16 of dW1; the bias sums of the
+                // two column halves meet in a fixed order (half 1 hands its sum over through shared memory)
+                if (ch == 1)
+                    G2_B2[F] = acc_b2, G2_B2[2 * kHid + F] = acc_b1;
+                __syncthreads();
+                if (ch == 0)
+                {
+                    __stcg(part + (tF ? a.po.b2[1] : a.po.b2[0]) + jF, acc_b2 + G2_B2[F]);
+                    __stcg(part + (tF ? a.po.b1[1] : a.po.b1[0]) + jF, acc_b1 + G2_B2[2 * kHid + F]);
+                }
+                float4 *w2dst = reinterpret_cast<float4 *>(part + (tF ? a.po.w2[1] : a.po.w2[0]) + jF * kHid + 32 * ch);
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+                    __stcg(w2dst + i, make_float4(acc_w2[TC ? 4 * i : 0], acc_w2[TC ? 4 * i + 1 : 0], acc_w2[TC ? 4 * i + 2 : 0], acc_w2[TC ? 4 * i + 3 : 0]));
+                float *w1dst = part + (tF ? a.po.w1[1] : a.po.w1[0]) + jF * D;
+#pragma unroll
+                for (int i = 0; i < 16; ++i)
+                    if (16 * ch + i < D)
+                        __stcg(w1dst + 16 * ch + i, acc_w1[TC ? i : 0]);
+                // value head, scale_log, action head, statistics: the shared-memory accumulators (po.wv is a multiple of 128)
+                float4 *dst = reinterpret_cast<float4 *>(part + sp.g_base);
+                const float4 *src = reinterpret_cast<const float4 *>(gsm + sp.g_base);
+                for (int i = tid; i < (Pstride - sp.g_base) / 4; i += kUpdThreads)
+                    __stcg(dst + i, src[i]);
+            }
+            else
+            {
             for (int i = tid; i < 2 * kHid; i += kUpdThreads)
             {
                 const int t = i >> 6, k = i & 63;
@@ -837,10 +1261,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 gsm[(t ? a.po.b1[1] : a.po.b1[0]) + k] += (G2_B1[(t * 3 + 0) * kHid + k] + G2_B1[(t * 3 + 1) * kHid + k]) + G2_B1[(t * 3 + 2) * kHid + k];
             }
             __syncthreads();
-            float4 *dst = reinterpret_cast<float4 *>(a.gpart + static_cast<size_t>(blockIdx.x) * Pstride);
+            float4 *dst = reinterpret_cast<float4 *>(part);
             const float4 *src = reinterpret_cast<const float4 *>(gsm);
             for (int i = tid; i < Pstride / 4; i += kUpdThreads)
                 __stcg(dst + i, src[i]);
+            }
         }
         CPPRL_MARK(10);
         grid_arrive(a.barrier);
@@ -973,6 +1398,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             {
                 asm volatile("cp.async.wait_all;" ::: "memory");
                 write_back_state();
+                leave();
                 return; // identical decision in every CTA (same data, same summation order)
             }
         }
@@ -1027,21 +1453,22 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     } // steps
     if (training)
         write_back_state();
+    leave();
 }
 
-template <int R>
+template <int R, bool TC>
 int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaStream_t s)
 {
     static std::atomic<uint64_t> configured{0};
     if (!configured_on_device(configured))
     {
-        CPPRL_CUDA_TRY(cudaFuncSetAttribute(mlp_update_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CPPRL_CUDA_TRY(cudaFuncSetAttribute(mlp_update_kernel<R, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         mark_configured_on_device(configured);
     }
     // the grid barrier counts arrivals from zero in every launch
     CPPRL_CUDA_TRY(cudaMemsetAsync(args.barrier, 0, sizeof(unsigned int), s));
     void *kargs[] = {const_cast<MlpUpdateArgs *>(&args)};
-    CPPRL_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(mlp_update_kernel<R>), dim3(grid),
+    CPPRL_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(mlp_update_kernel<R, TC>), dim3(grid),
                                                dim3(kUpdThreads), kargs, smem_bytes, s));
     count_launch();
     return 0;
@@ -1049,20 +1476,29 @@ int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaSt
 } // namespace
 
 // ---- host-side helpers used by cabi_update.cu ------------------------------------------------------------
-size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta)
+size_t mlp_update_smem_bytes(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta, bool tc, int img_tail, int g_tail)
 {
-    return sizeof(float) * static_cast<size_t>(make_plan(R, img_floats, Pstride, Dp, Ap, per_cta).total);
+    return sizeof(float) * static_cast<size_t>(make_plan(R, img_floats, Pstride, Dp, Ap, per_cta, tc, img_tail, g_tail).total);
 }
 
 int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s)
 {
-    const size_t smem = mlp_update_smem_bytes(R, args.il.floats, args.po.Pstride, args.Dp, args.Ap, args.per_cta);
+    const bool tc = args.tc != 0;
+    const size_t smem = mlp_update_smem_bytes(R, args.il.floats, args.po.Pstride, args.Dp, args.Ap, args.per_cta, tc, args.il.tail, args.po.wv);
     if (smem > 227 * 1024)
         return fail(CPPRL_B200_EUNSUPPORTED, "mlp_update: shared-memory plan exceeds 227 KB for this obs/action size");
+    if (tc != (args.il.tc != 0))
+        return fail(CPPRL_B200_EINVAL, "mlp_update: image layout does not match the kernel variant");
+    if (tc)
+    {
+        if (R != kTcRows || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
+            return fail(CPPRL_B200_EINVAL, "mlp_update: unsupported tensor-core plan");
+        return launch_update<kTcRows, true>(args, grid, smem, s);
+    }
     if (R == 64)
-        return launch_update<64>(args, grid, smem, s);
+        return launch_update<64, false>(args, grid, smem, s);
     if (R == 32)
-        return launch_update<32>(args, grid, smem, s);
+        return launch_update<32, false>(args, grid, smem, s);
     return fail(CPPRL_B200_EINVAL, "mlp_update: unsupported tile size");
 }
 } // namespace cpprl_b200

@@ -10,6 +10,7 @@ constexpr int kHid = 64;           // MlpBase hidden size this kernel is special
 constexpr int kUpdThreads = 256;   // 8 warps: warps 0-3 run the actor tower, 4-7 the critic tower
 constexpr int kNumStats = 8;       // slots appended to the gradient vector (5 used)
 constexpr int kMaxActions = 16;
+constexpr int kTcRows = 56;        // tile rows of the tensor-core variant: 148 CTAs x 56 rows cover an 8192-row minibatch in one wave
 
 enum { kAlgoPPO = 0, kAlgoA2C = 1, kAlgoForward = 2 };
 enum { kOptAdam = 0, kOptRmsprop = 1 };
@@ -39,6 +40,11 @@ struct ImageLayout
     int bv;     // [4]
     int slog;   // [Ap]
     int floats; // total, multiple of 4
+    // Tensor-core variant (tc != 0): the matrices are kept in their NATURAL orientation, one row per tensor-memory
+    // lane -- w1t[t] = W1 [64][Dp], w2t[t] = W2 [j][k], w2n[t] = W2^T [k][j] -- the biases unpermuted, and everything
+    // from b1[0] on (biases, heads: `tail`) is what the kernel keeps in shared memory.
+    int tc;
+    int tail;
 };
 
 // Device-resident running state of one update (reset by begin, read back by end).
@@ -82,6 +88,7 @@ struct MlpUpdateArgs
     unsigned int adv_seq; // advantage-moment exchange sequence number of this update
     int n_active;         // CTAs that own tiles and publish a gradient partial (= min(#tiles, grid))
     int per_cta;          // parameters owned by each CTA in phase 2 (multiple of 4; grid * per_cta >= P rounded to 4)
+    int tc;               // tensor-core variant of the kernel (large minibatches, obs <= 32 columns): see mlp_tc.cuh
     const double *adv_sums; // {sum, sumsq} of raw advantages over all rows (PPO), nullable
     // loss
     int algo;

@@ -43,6 +43,16 @@ print(f"{cfg}: {used.sum()} CTAs, step {step}; cycles per phase (min / median / 
 d = np.diff(c[:, :16], axis=1)
 for i, n in enumerate(NAMES):
     print(f"  {n:12s} {d[:, i].min():8d} {int(np.median(d[:, i])):8d} {d[:, i].max():8d}")
+if c[:, 20].any():
+    # tensor-core variant: finer marks (slots 20..26) between the standard ones
+    seq = [("step top -> image landed", 0, 26), ("weights -> tensor memory", 26, 1), ("finalize_stage", 1, 20), ("T1 issue+wait", 20, 2),
+           ("E1 (tanh, operand planes)", 2, 21), ("T2 issue+wait", 21, 22), ("E2 (tanh, h2)", 22, 23), ("W2^T -> tensor memory", 23, 3),
+           ("P3 heads", 3, 4), ("P4 loss", 4, 5), ("P5 head-bwd + dz2 planes", 5, 6), ("T3 issue+wait", 6, 7), ("E3 dz1", 7, 8),
+           ("T4 chain 1 + drain", 8, 24), ("T4 chain 2 + drain", 24, 25), ("tile end", 25, 9)]
+    print("  tensor-core variant, finer marks:")
+    for name, i0, i1 in seq:
+        dd = c[:, i1] - c[:, i0]
+        print(f"    {name:28s} {dd.min():8d} {int(np.median(dd)):8d} {dd.max():8d}")
 tot = c[:, 15] - c[:, 0]
 if world > 1:
     x = np.diff(c[:, 16:20], axis=1)
