@@ -135,7 +135,7 @@ __device__ __forceinline__ void image_scatter(const MlpUpdateArgs &a, float *__r
         {
             const int e = i - po.w1[t], j = e / D, k = e - j * D;
             if (il.tc)
-                image[il.w1t[t] + j * a.Dp + k] = v;
+                image[il.w1t[t] + ((k >> 2) * kHid + j) * 4 + (k & 3)] = v; // [k / 4][unit][k % 4]: see ImageLayout
             else
                 image[il.w1t[t] + k * kHid + perm16(j)] = v;
             return;
@@ -150,8 +150,8 @@ __device__ __forceinline__ void image_scatter(const MlpUpdateArgs &a, float *__r
             const int e = i - po.w2[t], j = e >> 6, k = e & 63;
             if (il.tc)
             {
-                image[il.w2t[t] + j * kHid + k] = v;
-                image[il.w2n[t] + k * kHid + j] = v;
+                image[il.w2t[t] + ((k >> 2) * kHid + j) * 4 + (k & 3)] = v; // row j of W2, 16-byte chunk k / 4
+                image[il.w2n[t] + ((j >> 2) * kHid + k) * 4 + (j & 3)] = v; // row k of W2^T, chunk j / 4
             }
             else
             {
@@ -373,10 +373,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     // Matrix rows -> tensor memory in two steps, so that the global (L2) loads are in flight while something else runs:
     // tc_fetch32 issues the eight 16-byte loads of this thread's 32 floats, tc_store32 splits them into hi / lo planes
     // and writes columns [col, col + 32) / [col + 64, ..) of the thread's lane (warp-collective tcgen05.st).
-    auto tc_fetch32 = [&](const float *src, float4 (&w)[8]) {
+    // `mat` is a [16 chunks][64 units][4] matrix of the image: chunk c of unit jF is the 16-byte word c * 64 + jF, so
+    // the 32 lanes of a warp read 512 contiguous bytes per load
+    auto tc_fetch32 = [&](const float *mat, float4 (&w)[8]) {
+        const float4 *src = reinterpret_cast<const float4 *>(mat) + (8 * ch) * kHid + jF;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            w[i] = __ldcg(reinterpret_cast<const float4 *>(src) + i);
+            w[i] = __ldcg(src + i * kHid);
     };
     auto tc_store32 = [&](uint32_t col, const float4 (&w)[8]) {
         const float4 lo4[4] = {w[0], w[1], w[2], w[3]}, hi4[4] = {w[4], w[5], w[6], w[7]};
@@ -550,6 +553,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     const float inv_b = 1.f / static_cast<float>(a.B_norm);
     uint32_t img_phase = 0;
     bool staged = false; // the first work item of the next step was prefetched during this one
+    bool fin_ahead = false; // ... and already finalised (finalize_stage) while waiting at a grid barrier
     // the optimiser state of this CTA's slice lives in shared memory for the whole launch; it goes back to
     // global memory on every exit path
     auto write_back_state = [&]() {
@@ -592,11 +596,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             {
                 // this lane's row of W2 (the 32 columns of this thread's half) and of W1 (16 columns): the global image is
                 // complete (grid barrier); the loads fly while the shared-memory image arrives
-                tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]) + jF * kHid + 32 * ch, wreg);
-                const float *w1src = a.image + (tF ? a.il.w1t[1] : a.il.w1t[0]) + jF * Dp + 16 * ch;
+                tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]), wreg);
+                const float4 *w1src = reinterpret_cast<const float4 *>(a.image + (tF ? a.il.w1t[1] : a.il.w1t[0])) + (4 * ch) * kHid + jF;
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    w1reg[i] = 16 * ch + 4 * i < Dp ? __ldcg(reinterpret_cast<const float4 *>(w1src) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    w1reg[i] = 16 * ch + 4 * i < Dp ? __ldcg(w1src + i * kHid) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
             for (int i = sp.g_base + tid; i < Pstride; i += kUpdThreads)
                 gsm[i] = 0.f;
@@ -653,7 +657,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             if (ntile >= n_tiles)
                 nstep = step + 1, ntile = blockIdx.x;
             const bool has_next = nstep < a.n_steps && (nstep == step || ntile * R < rows_of(nstep));
-            finalize_stage(nrows); // the rows of THIS item are in place (waits for their cp.async group)
+            if (fin_ahead)
+                fin_ahead = false; // (done while the previous minibatch waited at its grid barrier)
+            else
+                finalize_stage(nrows); // the rows of THIS item are in place (waits for their cp.async group)
             const long long next_row = has_next ? item_rowid(nstep, ntile) : -1;
             if (TC)
             {
@@ -695,7 +702,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 {
                     const float bias = img[(tF ? a.il.b1[1] : a.il.b1[0]) + jF];
                     const uint32_t ob = (jF >> 2) * GeoT::kLboB + (jF & 3) * 4u;
-#pragma unroll
+                    // (rolled: the kernel's code is far larger than the instruction caches and every phase runs once per
+                    // tile, so an unrolled epilogue is paid for in instruction fetches -- ncu: 11 % of the stalls are no_inst)
+#pragma unroll 1
                     for (int c = 0; c < CH; c += 4)
                     {
                         float v[4], hi[4], lo[4];
@@ -729,14 +738,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     mtc::commit(&tcbar[1]);
                 }
                 // W2^T (this lane's row of the transposed image) for the data gradient: in flight during the chain and E2
-                tc_fetch32(a.image + (tF ? a.il.w2n[1] : a.il.w2n[0]) + jF * kHid + 32 * ch, wreg);
+                tc_fetch32(a.image + (tF ? a.il.w2n[1] : a.il.w2n[0]), wreg);
                 mbar_wait(&tcbar[1], tc_parity);
                 mtc::fence_after();
                 CPPRL_MARK(22);
                 {
                     const float bias = img[(tF ? a.il.b2[1] : a.il.b2[0]) + jF];
                     float *h2row = smem + sp.h2[0] + F * LD + ch * CH; // (the two towers' h2 tiles are contiguous)
-#pragma unroll
+#pragma unroll 1
                     for (int c = 0; c < CH; c += 4)
                     {
                         float v[4];
@@ -1064,7 +1073,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 // dz1 = dh1 * (1 - h1^2) -> tensor memory (the A operand of dW1, over W2^T which the chain has consumed); db1
                 {
                     float bsum = 0.f;
-#pragma unroll
+#pragma unroll 1
                     for (int c = 0; c < CH; c += 4)
                     {
                         float v[4];
@@ -1155,7 +1164,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 if (tile + G < n_tiles)
                 {
                     // another tile of this minibatch follows: its layer 2 needs W2 back in the columns dz1 now occupies
-                    tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]) + jF * kHid + 32 * ch, wreg);
+                    tc_fetch32(a.image + (tF ? a.il.w2t[1] : a.il.w2t[0]), wreg);
                     tc_store32(lane_base + mtc::kColW + 32 * ch, wreg);
                     mtc::wait_st();
                 }
@@ -1241,11 +1250,20 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 #pragma unroll
                 for (int i = 0; i < 8; ++i)
                     __stcg(w2dst + i, make_float4(acc_w2[TC ? 4 * i : 0], acc_w2[TC ? 4 * i + 1 : 0], acc_w2[TC ? 4 * i + 2 : 0], acc_w2[TC ? 4 * i + 3 : 0]));
-                float *w1dst = part + (tF ? a.po.w1[1] : a.po.w1[0]) + jF * D;
+                // dW1 rows are D floats long (not a multiple of 4): staged in the flat parameter order [tower][unit * D + k] in
+                // shared memory (the layer-2 operand planes are idle; row stride D: 17 is odd, the 4-byte stores of a warp
+                // spread over the banks), then copied out as 16-byte words (64 * D floats per tower, po.w1[t] % 4 == 0)
+                float *w1s = smem + sp.hb[0];
 #pragma unroll
                 for (int i = 0; i < 16; ++i)
                     if (16 * ch + i < D)
-                        __stcg(w1dst + 16 * ch + i, acc_w1[TC ? i : 0]);
+                        w1s[F * D + 16 * ch + i] = acc_w1[TC ? i : 0];
+                __syncthreads();
+                for (int e = tid; e < 2 * kHid * D / 4; e += kUpdThreads)
+                {
+                    const int t = e >= kHid * D / 4, rem = e - t * (kHid * D / 4);
+                    __stcg(reinterpret_cast<float4 *>(part + (t ? a.po.w1[1] : a.po.w1[0])) + rem, *reinterpret_cast<const float4 *>(w1s + 4 * e));
+                }
                 // value head, scale_log, action head, statistics: the shared-memory accumulators (po.wv is a multiple of 128)
                 float4 *dst = reinterpret_cast<float4 *>(part + sp.g_base);
                 const float4 *src = reinterpret_cast<const float4 *>(gsm + sp.g_base);
@@ -1278,6 +1296,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), t);
             MISC[16] = static_cast<float>(a.lr / bc1);
             MISC[17] = static_cast<float>(sqrt(bc2));
+        }
+        // The rollout does not depend on the parameters: while the slowest CTA is still on its way to the barrier, the
+        // rows of this CTA's first tile of the NEXT minibatch (prefetched during this one) are normalised and laid out
+        // as operands -- work that would otherwise sit on the critical path right after the optimiser step.
+        if (staged && step + 1 < a.n_steps && static_cast<long long>(blockIdx.x) * R < rows_of(step + 1))
+        {
+            finalize_stage(min(R, rows_of(step + 1) - static_cast<int>(blockIdx.x) * R));
+            fin_ahead = true;
         }
         bar_target += G;
         grid_wait(a.barrier, bar_target);

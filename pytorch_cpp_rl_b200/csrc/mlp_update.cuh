@@ -40,9 +40,11 @@ struct ImageLayout
     int bv;     // [4]
     int slog;   // [Ap]
     int floats; // total, multiple of 4
-    // Tensor-core variant (tc != 0): the matrices are kept in their NATURAL orientation, one row per tensor-memory
-    // lane -- w1t[t] = W1 [64][Dp], w2t[t] = W2 [j][k], w2n[t] = W2^T [k][j] -- the biases unpermuted, and everything
-    // from b1[0] on (biases, heads: `tail`) is what the kernel keeps in shared memory.
+    // Tensor-core variant (tc != 0): every matrix row goes to ONE tensor-memory lane, read by one thread with 16-byte
+    // loads; the image therefore interleaves the rows chunk-wise, [k / 4][unit][k % 4], so that the 32 lanes of a warp
+    // load 512 contiguous bytes -- w1t[t] = W1 (Dp / 4 chunks), w2t[t] = W2 (row = unit j), w2n[t] = W2^T (row = input
+    // k) -- the biases are unpermuted, and everything from b1[0] on (biases, heads: `tail`) is what the kernel keeps
+    // in shared memory.
     int tc;
     int tail;
 };
