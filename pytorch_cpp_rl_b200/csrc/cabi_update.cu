@@ -834,6 +834,27 @@ extern "C" void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step)
     g_dbg_step = step;
 }
 
+// Which variant of the fused MlpBase update a minibatch of `minibatch_rows` rows with `obs_dim` observation columns trains
+// on: 1 = tensor-core (tcgen05 3xTF32, mlp_tc.cuh), 0 = fp32 CUDA-core.  What bench.py reports its roofline against.
+extern "C" int cpprl_b200_mlp_update_variant(int64_t minibatch_rows, int64_t obs_dim, int64_t num_actions)
+{
+    if (require_device() != 0 || minibatch_rows <= 0 || obs_dim < 1 || obs_dim > 256 || num_actions < 1 || num_actions > kMaxActions)
+        return 0;
+    cpprl_b200_policy p{};
+    p.base_kind = CPPRL_B200_BASE_MLP;
+    p.head_kind = CPPRL_B200_HEAD_NORMAL;
+    p.hidden = kHid;
+    p.obs_dim = obs_dim;
+    p.num_actions = num_actions;
+    ParamOffsets po;
+    if (!mlp_param_offsets(p, po))
+        return 0;
+    Plan plan;
+    if (choose_plan(minibatch_rows, po, round_up(static_cast<int>(obs_dim), 8), round_up(static_cast<int>(num_actions), 4), true, plan))
+        return 0;
+    return plan.tc ? 1 : 0;
+}
+
 static int ppo_shard_permutation(cpprl_b200_ppo *h, const int64_t *d_perm)
 {
     const size_t need = static_cast<size_t>(h->mbs * h->n_mb);

@@ -217,14 +217,16 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
 // `bar` is one unsigned counter zeroed by the host before every launch; barrier number k (0-based) of the
 // launch is complete when the counter reaches G*(k+1).  Work placed between arrive and wait overlaps the
 // round trip of the slowest CTA.
+// Ordering: the CTA barrier orders every thread's writes before thread 0's release-increment (release is cumulative
+// over what the releasing thread has observed), and thread 0's acquire-load before every thread's later reads through
+// the second CTA barrier -- the scheme of CUTLASS's GenericBarrier, without the two full fences (MEMBAR.SC.GPU,
+// ~0.5 k cycles each on the critical path of every optimiser step) an earlier version wrapped around it.  Everything a
+// CTA reads from another CTA after a barrier bypasses L1 (ld.global.cg, TMA bulk copies).
 __device__ __forceinline__ void grid_arrive(unsigned int *bar)
 {
     __syncthreads();
     if (threadIdx.x == 0)
-    {
-        __threadfence();
         asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
-    }
 }
 __device__ __forceinline__ void grid_wait(unsigned int *bar, unsigned int target)
 {
@@ -235,7 +237,6 @@ __device__ __forceinline__ void grid_wait(unsigned int *bar, unsigned int target
         {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
         } while (v < target);
-        __threadfence();
     }
     __syncthreads();
 }

@@ -1,0 +1,116 @@
+"""The tensor-core variant of the fused MlpBase update (csrc/mlp_tc.cuh: tcgen05 kind::tf32 as 3xTF32, minibatches of
+more than 32 rows per SM) against the compiled reference and against the fp32 CUDA-core variant of the same kernel
+(CPPRL_B200_MLP_TC=0), over the shapes the variant has to get right: observation widths around the 8-column k-step,
+both heads, minibatches that end in a ragged tile, several tiles per CTA, PPO with several optimiser steps and A2C."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from pytorch_cpp_rl_b200 import api, cabi
+from pytorch_cpp_rl_b200.workloads import CONFIGS
+from pytorch_cpp_rl_b200.workloads import synth_rollout
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+def _variant(rows, obs, act):
+    return cabi.load().cpprl_b200_mlp_update_variant(rows, obs, act)
+
+
+def test_variant_selection():
+    assert _variant(8192, 17, 6) == 1          # cfg3's minibatch
+    assert _variant(20480, 8, 4) == 1          # cfg2
+    assert _variant(256, 8, 4) == 0            # cfg1: a minibatch that does not fill the chip
+    assert _variant(8192, 33, 6) == 0          # more than 32 observation columns: CUDA-core variant
+    os.environ["CPPRL_B200_MLP_TC"] = "0"
+    try:
+        assert _variant(8192, 17, 6) == 0
+    finally:
+        del os.environ["CPPRL_B200_MLP_TC"]
+
+
+def _update_once(w, r, params, normalizer, perms, n_updates=1):
+    policy, st = H.make_gpu_side(w, r, params, normalizer)
+    if w.algo == "ppo":
+        algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef, w.entropy_coef,
+                       w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    else:
+        algo = api.A2C(policy, 1.0, w.value_loss_coef, w.entropy_coef, w.learning_rate, w.epsilon, w.alpha)
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    stats = []
+    for u in range(n_updates):
+        st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        got = algo.update(st, 1.0, perms=perms[u]) if w.algo == "ppo" else algo.update(st, 1.0)
+        stats.append(np.array([d.value for d in got], np.float32))
+    return policy.params.cpu().numpy(), stats
+
+
+CASES = {
+    # name: (base config, overrides): minibatch rows > 32 * 148 = 4736 in every case
+    "normal_obs17_ragged": ("cfg3", dict(T=13, N=800, num_epoch=2, num_mini_batch=2)),        # 5200 rows: 92 full tiles + 48 rows
+    "normal_obs3": ("cfg3", dict(T=8, N=640, obs_shape=(3,), num_epoch=1, num_mini_batch=1)),   # one k-step, 5 padded columns
+    "normal_obs32_act1": ("cfg3", dict(T=8, N=640, obs_shape=(32,), num_actions=1, num_epoch=1, num_mini_batch=1)),
+    "categorical_obs9_act16": ("cfg1", dict(T=8, N=700, obs_shape=(9,), num_actions=16, num_epoch=2, num_mini_batch=1,
+                                            storage_hidden=1)),
+    "multi_tile": ("cfg3", dict(T=20, N=1024, num_epoch=1, num_mini_batch=1)),                 # 20480 rows: three tiles per CTA
+    "a2c_obs8": ("cfg2", dict(T=3, N=2048)),
+    "no_normaliser": ("cfg3", dict(T=8, N=640, normalize_obs=False, num_epoch=1, num_mini_batch=1)),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_tc_variant_matches_reference_and_cuda_core_variant(ref, case):
+    base, kw = CASES[case]
+    w = CONFIGS[base].scaled(**kw)
+    assert _variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) == 1, "case does not reach the tensor-core variant"
+    seed = 3
+    r = synth_rollout(w, seed)
+    sess = H.make_ref_session(ref, w, init_seed=seed)
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    params0 = sess.get_params()
+    norm0 = sess.get_normalizer() if w.normalize_obs else None
+    n_updates = 2
+    perms = [H.draw_perms(900 + u, w.rows, w.num_epoch) for u in range(n_updates)] if w.algo == "ppo" else [None] * n_updates
+    want_stats = []
+    for u in range(n_updates):
+        sess.compute_returns(r["next_value"], w.use_gae, w.gamma, w.tau)
+        s, _ = sess.update(1.0, perm_seed=900 + u) if w.algo == "ppo" else sess.update(1.0)
+        want_stats.append(np.asarray(s, np.float32))
+    want = sess.get_params()
+
+    tc_params, tc_stats = _update_once(w, r, params0, norm0, perms, n_updates)
+    os.environ["CPPRL_B200_MLP_TC"] = "0"
+    try:
+        cc_params, cc_stats = _update_once(w, r, params0, norm0, perms, n_updates)
+    finally:
+        del os.environ["CPPRL_B200_MLP_TC"]
+
+    floor = w.learning_rate
+    err_tc = np.abs(tc_params - want) / np.maximum(np.abs(want), floor)
+    err_cc = np.abs(cc_params - want) / np.maximum(np.abs(want), floor)
+    ab = np.abs(tc_params - cc_params) / np.maximum(np.abs(cc_params), floor)
+    steps = n_updates * max(1, w.optimizer_steps)
+    budget = 1e-4 * steps ** 0.5 + 1e-4
+    print(f"[tc] {case}: vs reference tc {err_tc.max():.2e} / cuda-core {err_cc.max():.2e} (budget {budget:.1e}); tc vs cuda-core {ab.max():.2e}")
+    assert err_tc.max() <= budget, (err_tc.max(), int(np.argmax(err_tc)))
+    assert ab.max() <= budget
+    for u in range(n_updates):
+        k = 4 if w.algo == "ppo" else 3
+        np.testing.assert_allclose(tc_stats[u][:k], want_stats[u][:k], rtol=1e-4, atol=2e-6)
+        np.testing.assert_allclose(tc_stats[u][:k], cc_stats[u][:k], rtol=2e-5, atol=1e-6)
+
+
+def test_tc_variant_is_deterministic(ref):
+    w = CONFIGS["cfg3"].scaled(T=13, N=800, num_epoch=2, num_mini_batch=2)
+    r = synth_rollout(w, 1)
+    sess = H.make_ref_session(ref, w, init_seed=1)
+    H.fill_policy_outputs(sess, w, r)
+    params0, norm0 = sess.get_params(), sess.get_normalizer()
+    perms = [H.draw_perms(5, w.rows, w.num_epoch)]
+    a, sa = _update_once(w, r, params0, norm0, perms)
+    b, sb = _update_once(w, r, params0, norm0, perms)
+    assert np.array_equal(a, b) and np.array_equal(sa[0], sb[0])
