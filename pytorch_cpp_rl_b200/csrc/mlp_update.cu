@@ -56,6 +56,7 @@ struct SmemPlan
 //   scratch RED, which is idle while tiles are being processed (cfg3's 64-row plan has 3 KB of shared memory to spare)
 __host__ __device__ inline int g2_floats(int Ap) { return Ap * kHid + kHid; }
 constexpr int kG2BiasFloats = 2 * kHid + 2 * 3 * kHid;
+constexpr int kTcW1Stage = 2 * kHid * mtc::kMaxDp; // floats reserved for the staged dW1 in front of the staged dW2 (tensor-core publish)
 
 __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta, bool tc = false,
                                               int img_tail = 0, int g_tail = 0)
@@ -1162,6 +1163,38 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
                 tc_parity ^= 1u;
                 CPPRL_MARK(25);
+                if (tile + G >= n_tiles)
+                {
+                    // last tile of this CTA in this minibatch: everything of the gradient partial that needs no barrier of
+                    // its own leaves NOW, under the tile's closing barrier -- this lane's 32 columns of dW2 straight from
+                    // registers, dW1 staged in the flat parameter order [tower][unit * D + k] (rows are D floats, not a
+                    // multiple of 4; the data-gradient operand planes are idle), the bias sums of column half 1 handed to
+                    // half 0 through shared memory, the head gradients of row half 1 folded into the accumulator
+                    float *part = a.gpart + static_cast<size_t>(blockIdx.x) * Pstride;
+                    (void)part;
+                    // dW2 [lane][64] staged with a row stride of 68 floats (conflict-free 16-byte stores; a lane's 128 bytes
+                    // written straight to global memory would touch 32 different lines per warp instruction)
+                    float *w2s = smem + sp.hb[0] + kTcW1Stage + F * 68 + 32 * ch;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        *reinterpret_cast<float4 *>(w2s + 4 * i) =
+                            make_float4(acc_w2[TC ? 4 * i : 0], acc_w2[TC ? 4 * i + 1 : 0], acc_w2[TC ? 4 * i + 2 : 0], acc_w2[TC ? 4 * i + 3 : 0]);
+                    float *w1s = smem + sp.hb[0];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (16 * ch + i < D)
+                            w1s[F * D + 16 * ch + i] = acc_w1[TC ? i : 0];
+                    if (ch == 1)
+                        G2_B2[F] = acc_b2, G2_B2[2 * kHid + F] = acc_b1;
+                    for (int i = tid; i < (A + 1) * kHid; i += kUpdThreads)
+                    {
+                        const int o = i >> 6, k = i & 63;
+                        if (o < A)
+                            gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
+                        else
+                            gsm[a.po.wv + k] += G2_WV[k];
+                    }
+                }
                 if (tile + G < n_tiles)
                 {
                     // another tile of this minibatch follows: its layer 2 needs W2 back in the columns dz1 now occupies
@@ -1226,40 +1259,23 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         // ---- fold the second accumulators into the gradient in a fixed order, then publish this CTA's partial ----
         if (active)
         {
-            for (int i = tid; i < (A + 1) * kHid; i += kUpdThreads)
-            {
-                const int o = i >> 6, k = i & 63;
-                if (o < A)
-                    gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
-                else
-                    gsm[a.po.wv + k] += G2_WV[k];
-            }
             float *part = a.gpart + static_cast<size_t>(blockIdx.x) * Pstride;
             if (TC)
             {
-                // the tower gradients leave from registers: this lane's 32 columns of dW2, 16 of dW1; the bias sums of the
-                // two column halves meet in a fixed order (half 1 hands its sum over through shared memory)
-                if (ch == 1)
-                    G2_B2[F] = acc_b2, G2_B2[2 * kHid + F] = acc_b1;
-                __syncthreads();
+                // (the register-held gradients, the bias hand-over and the fold were done at the end of the last tile,
+                // ahead of its closing barrier: see tc_publish_early)
                 if (ch == 0)
                 {
                     __stcg(part + (tF ? a.po.b2[1] : a.po.b2[0]) + jF, acc_b2 + G2_B2[F]);
                     __stcg(part + (tF ? a.po.b1[1] : a.po.b1[0]) + jF, acc_b1 + G2_B2[2 * kHid + F]);
                 }
-                float4 *w2dst = reinterpret_cast<float4 *>(part + (tF ? a.po.w2[1] : a.po.w2[0]) + jF * kHid + 32 * ch);
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    __stcg(w2dst + i, make_float4(acc_w2[TC ? 4 * i : 0], acc_w2[TC ? 4 * i + 1 : 0], acc_w2[TC ? 4 * i + 2 : 0], acc_w2[TC ? 4 * i + 3 : 0]));
-                // dW1 rows are D floats long (not a multiple of 4): staged in the flat parameter order [tower][unit * D + k] in
-                // shared memory (the layer-2 operand planes are idle; row stride D: 17 is odd, the 4-byte stores of a warp
-                // spread over the banks), then copied out as 16-byte words (64 * D floats per tower, po.w1[t] % 4 == 0)
-                float *w1s = smem + sp.hb[0];
-#pragma unroll
-                for (int i = 0; i < 16; ++i)
-                    if (16 * ch + i < D)
-                        w1s[F * D + 16 * ch + i] = acc_w1[TC ? i : 0];
-                __syncthreads();
+                const float *w1s = smem + sp.hb[0], *w2s = w1s + kTcW1Stage;
+                for (int e = tid; e < 2 * kHid * kHid / 4; e += kUpdThreads) // consecutive threads, consecutive 16-byte words
+                {
+                    const int t = e >> 10, rem = e & 1023, j = rem >> 4, c4 = rem & 15;
+                    __stcg(reinterpret_cast<float4 *>(part + (t ? a.po.w2[1] : a.po.w2[0])) + rem,
+                           *reinterpret_cast<const float4 *>(w2s + (t * kHid + j) * 68 + 4 * c4));
+                }
                 for (int e = tid; e < 2 * kHid * D / 4; e += kUpdThreads)
                 {
                     const int t = e >= kHid * D / 4, rem = e - t * (kHid * D / 4);
@@ -1273,6 +1289,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
             else
             {
+            for (int i = tid; i < (A + 1) * kHid; i += kUpdThreads)
+            {
+                const int o = i >> 6, k = i & 63;
+                if (o < A)
+                    gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
+                else
+                    gsm[a.po.wv + k] += G2_WV[k];
+            }
             for (int i = tid; i < 2 * kHid; i += kUpdThreads)
             {
                 const int t = i >> 6, k = i & 63;
