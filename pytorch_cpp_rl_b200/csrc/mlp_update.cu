@@ -577,14 +577,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         const int n_act = min(n_tiles, G);
         const bool active = static_cast<int>(blockIdx.x) < n_act; // owns tiles of this minibatch, publishes a partial
         CPPRL_MARK(0);
-        float4 wreg[8], w1reg[4]; // matrix rows on their way to tensor memory (tensor-core variant)
-        (void)wreg, (void)w1reg;
+        float4 wreg[8], w1reg[4], timg[2]; // matrix rows / image tail on their way to tensor / shared memory (tensor-core variant)
+        (void)wreg, (void)w1reg, (void)timg;
         // ---- (re)load the weight image with one TMA bulk copy per 32 KB, clear the gradient accumulator ------
         if (active)
         {
-            if (tid == 0)
+            if (!TC && tid == 0)
             {
-                // (tensor-core variant: only the image's tail -- biases and heads -- comes to shared memory)
                 const uint32_t bytes = static_cast<uint32_t>(a.il.floats - sp.img_base) * 4u;
                 // the image was written by generic-proxy stores of other CTAs (ordered by the grid barrier); make
                 // them visible to the async proxy that performs the bulk copy
@@ -603,6 +602,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
                     w1reg[i] = 16 * ch + 4 * i < Dp ? __ldcg(w1src + i * kHid) : make_float4(0.f, 0.f, 0.f, 0.f);
+                // the image's tail (biases, heads: at most 345 16-byte words) with the same loads -- one L2 round trip
+                // for everything instead of a bulk copy and its mbarrier
+                const float4 *tsrc = reinterpret_cast<const float4 *>(a.image + sp.img_base);
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (tid + i * kUpdThreads < (a.il.floats - sp.img_base) / 4)
+                        timg[i] = __ldcg(tsrc + tid + i * kUpdThreads);
             }
             for (int i = sp.g_base + tid; i < Pstride; i += kUpdThreads)
                 gsm[i] = 0.f;
@@ -620,9 +626,19 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 prefetch_issue();
             }
             staged = false;
-            mbar_wait(mbar, img_phase);
-            img_phase ^= 1u;
-            if (a.head == 1 && tid < A)
+            if (TC)
+            {
+#pragma unroll
+                for (int i = 0; i < 2; ++i)
+                    if (tid + i * kUpdThreads < (a.il.floats - sp.img_base) / 4)
+                        reinterpret_cast<float4 *>(smem + sp.img)[tid + i * kUpdThreads] = timg[i];
+            }
+            else
+            {
+                mbar_wait(mbar, img_phase);
+                img_phase ^= 1u;
+            }
+            if (!TC && a.head == 1 && tid < A)
             {
                 const float sigma = expf(img[a.il.slog + tid]); // Normal(loc, exp(scale_log))  (output_layers.cpp:54-59)
                 SIG[2 * tid] = sigma * sigma;
@@ -647,6 +663,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             acc_w1[i] = 0.f;
         (void)acc_w2, (void)acc_w1, (void)acc_b1, (void)acc_b2;
         __syncthreads();
+        if (TC && active && a.head == 1 && tid < A)
+        {
+            // (the tail was stored by all threads just above; P4, the reader, is several barriers away)
+            const float sigma = expf(img[a.il.slog + tid]);
+            SIG[2 * tid] = sigma * sigma;
+            SIG[2 * tid + 1] = logf(sigma);
+        }
         const float ce_b = a.c_entropy * inv_b;
         CPPRL_MARK(1);
 
