@@ -80,6 +80,17 @@ int cpprl_b200_compute_returns(const float *d_rewards, float *d_value_preds, con
 int cpprl_b200_advantages(const float *d_returns, const float *d_value_preds, int64_t T, int64_t N,
                           int normalize, float *d_advantages, double *d_moments, void *stream);
 
+/* The same computation WITHOUT any allocation (cpprl_b200_advantages takes a stream-ordered temporary for its per-CTA
+ * partial sums).  No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses that forbid it.  The scratch is a
+ * file-scope device array of the library (32 KB, held by every GPU that loads the library until the process exits).
+ * Limits and rules: T * N <= CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS, else CPPRL_B200_EUNSUPPORTED; all calls share the
+ * one array, so calls that overlap on a GPU (different streams) race -- serialise them; results are bit-identical to
+ * cpprl_b200_advantages (same kernels, same launch shape). */
+#define CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS (1ll << 22)
+int cpprl_b200_advantages_noalloc(const float *d_returns, const float *d_value_preds, int64_t T, int64_t N,
+                                  int normalize, float *d_advantages, double *d_moments, void *stream);
+
 /* ---- (b) minibatch gather ----------------------------------------------------------------
  * replaces the eight `.index(indices[k])` gathers of FeedForwardGenerator::next,
  * src/generators/feed_forward_generator.cpp:42-80, for ONE field:

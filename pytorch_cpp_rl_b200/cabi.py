@@ -83,6 +83,7 @@ SIGNATURES = {
     "cpprl_b200_device_info": (C.c_int, [C.POINTER(C.c_int)] * 3 + [C.c_char_p, C.c_int]),
     "cpprl_b200_compute_returns": (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_int, C.c_float, C.c_float, C.c_void_p]),
     "cpprl_b200_advantages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "cpprl_b200_advantages_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cpprl_b200_gather_rows": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
     "cpprl_b200_rms_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int64]),
     "cpprl_b200_rms_update": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64] + [C.c_void_p] * 5),

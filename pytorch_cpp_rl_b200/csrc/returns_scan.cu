@@ -9,6 +9,9 @@
 // of UNROLL steps are issued before the dependent chain consumes them, which keeps 3*UNROLL lines per warp
 // in flight.  Arithmetic uses __fmul_rn/__fadd_rn in the reference's operator order so results are
 // bit-identical to the CPU libtorch path (no FMA contraction).
+#include <mutex>
+#include <string>
+
 #include "common.cuh"
 
 namespace cpprl_b200
@@ -302,6 +305,81 @@ extern "C" int cpprl_b200_advantages(const float *d_returns, const float *d_valu
     int rc = launch_advantage_moments(d_returns, d_value_preds, n, d_moments, ws, s);
     CPPRL_CUDA_TRY(cudaFreeAsync(ws, s));
     if (rc)
+        return rc;
+    advantage_write_kernel<<<static_cast<unsigned>(blocks), kAdvThreads, 0, s>>>(d_returns, d_value_preds, n, normalize,
+                                                                                 d_advantages, d_moments);
+    CPPRL_LAUNCH_CHECK("advantage_write_kernel");
+    return 0;
+}
+
+// ---- cpprl_b200_advantages_noalloc -------------------------------------------------------------------------------
+// The same two kernels as cpprl_b200_advantages for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc): the per-CTA partial sums and the arrival counter of advantage_moments_kernel live
+// in a file-scope device array instead of a stream-ordered temporary; it
+// has no counterpart in the reference.
+//   * Limit: T * N <= CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS (4 Mi rows) -- and the launch shape the existing entry
+//     point would use must fit the array's kNoAllocMaxBlocks partial pairs (it does on every part with <= 256 SMs).
+//   * Every GPU that loads the library holds the array (32 KB + 8 B) until the process exits.
+//   * Every call shares it: the arrival counter is cleared on the stream at the start of each call (the partials are
+//     overwritten before they are read), and calls that OVERLAP on one GPU (different streams) race on it.
+//   * No cudaMalloc / cudaFree / cudaMallocAsync, no event creation, no library that allocates.
+namespace
+{
+constexpr int kNoAllocMaxBlocks = 2048; // partial {sum, sum of squares} pairs the array holds
+static_assert(CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS == (1ll << 22), "header and kernel file disagree on the row limit");
+// AdvWorkspace layout: {counter, pad} then kNoAllocMaxBlocks pairs of doubles
+static __device__ __align__(256) unsigned char g_adv_noalloc_scratch[sizeof(AdvWorkspace) - 2 * sizeof(double) + kNoAllocMaxBlocks * 2 * sizeof(double)];
+
+// In host code `g_adv_noalloc_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[64] = {};
+
+int noalloc_scratch(void **out)
+{
+    int dev = 0;
+    CPPRL_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64)
+        return fail(CPPRL_B200_EUNSUPPORTED, "advantages_noalloc: device ordinal above 63");
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev])
+    {
+        void *p = nullptr;
+        CPPRL_CUDA_TRY(cudaGetSymbolAddress(&p, g_adv_noalloc_scratch));
+        if (!p)
+            return fail(CPPRL_B200_ECUDA, "advantages_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+} // namespace
+
+extern "C" int cpprl_b200_advantages_noalloc(const float *d_returns, const float *d_value_preds, int64_t T, int64_t N,
+                                             int normalize, float *d_advantages, double *d_moments, void *stream)
+{
+    if (!d_returns || !d_value_preds || !d_advantages || !d_moments)
+        return fail(CPPRL_B200_EINVAL, "advantages_noalloc: null pointer");
+    if (T <= 0 || N <= 0)
+        return fail(CPPRL_B200_EINVAL, "advantages_noalloc: non-positive size");
+    if (T > CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS || N > CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS ||
+        T * N > CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS)
+        return fail(CPPRL_B200_EUNSUPPORTED, "advantages_noalloc: T * N exceeds the static scratch's limit of " +
+                                                 std::to_string(CPPRL_B200_ADVANTAGES_NOALLOC_MAX_ROWS) +
+                                                 " rows; use cpprl_b200_advantages");
+    if (int rc = require_device())
+        return rc;
+    const int64_t n = T * N;
+    const int64_t blocks = advantage_blocks(n); // the launch shape of cpprl_b200_advantages: bit-identical results
+    if (blocks > kNoAllocMaxBlocks)
+        return fail(CPPRL_B200_EUNSUPPORTED, "advantages_noalloc: this device's launch shape needs more partial sums than the static scratch holds");
+    void *ws = nullptr;
+    if (int rc = noalloc_scratch(&ws))
+        return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CPPRL_CUDA_TRY(cudaMemsetAsync(d_moments, 0, 4 * sizeof(double), s));
+    CPPRL_CUDA_TRY(cudaMemsetAsync(ws, 0, sizeof(unsigned int) * 2, s)); // the arrival counter must start at zero
+    if (int rc = launch_advantage_moments(d_returns, d_value_preds, n, d_moments, ws, s))
         return rc;
     advantage_write_kernel<<<static_cast<unsigned>(blocks), kAdvThreads, 0, s>>>(d_returns, d_value_preds, n, normalize,
                                                                                  d_advantages, d_moments);
