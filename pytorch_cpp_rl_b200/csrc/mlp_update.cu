@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     const int G = gridDim.x;
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
     const int D = a.D, Dp = a.Dp, A = a.A;
-    const bool training = a.algo != kAlgoForward;
+    const bool training = TC || a.algo != kAlgoForward; // (the tensor-core variant only trains)
     // rows / tiles / publishing CTAs of minibatch `step` (ragged when the rollout is sharded by environment)
     auto rows_of = [&](int step) { return a.step_rows ? __ldg(a.step_rows + step) : a.B; };
     const int world = a.comm.world, my_rank = a.comm.rank;
@@ -444,10 +444,16 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     auto cp_async4 = [](float *dst, const float *src) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
     };
+    // Tensor-core variant: warps 0 and 4 hold the threads that issue the MMA chains and block on the tensor core's queue
+    // while a chain is in flight, so work that is meant to run UNDER a chain goes to the other six warps only:
+    // wt = this thread's index among them (0..191), -1 for the issuing warps.
+    const int wt = !TC ? tid : (q4 == 0 ? -1 : tid - 32 * (1 + ch));
+    constexpr int kWorkThreads = TC ? kUpdThreads - 64 : kUpdThreads;
     auto prefetch_issue = [&]() { // ROWIDN must be visible to every thread
+        if (wt >= 0)
         {
-            constexpr int LPR = kUpdThreads / R; // lanes per row: consecutive lanes fetch consecutive elements of a row
-            const int r = tid / LPR, q = tid % LPR;
+            constexpr int LPR = kWorkThreads / R; // lanes per row: consecutive lanes fetch consecutive elements of a row
+            const int r = wt / LPR, q = wt % LPR;
             const long long row = r < R ? ROWIDN[r] : -1; // (R need not divide the thread count)
             if (row >= 0)
             {
@@ -462,20 +468,20 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
             }
         }
-        if (tid < R)
+        if (wt >= 0 && wt < R)
         {
-            const long long row = ROWIDN[tid];
+            const long long row = ROWIDN[wt];
             if (row >= 0)
             {
                 if (training)
                 {
-                    cp_async4(SCN + tid, a.returns + row);
-                    cp_async4(SCN + LD + tid, a.old_logp + row);
+                    cp_async4(SCN + wt, a.returns + row);
+                    cp_async4(SCN + LD + wt, a.old_logp + row);
                     if (a.adv_sums)
-                        cp_async4(SCN + 2 * LD + tid, a.value_preds + row);
+                        cp_async4(SCN + 2 * LD + wt, a.value_preds + row);
                 }
                 if (a.head == 0)
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(ACTIN + tid)),
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(ACTIN + wt)),
                                  "l"(static_cast<const long long *>(a.actions) + row)
                                  : "memory");
             }
@@ -714,11 +720,6 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     }
                     mtc::commit(&tcbar[0]);
                 }
-                if (has_next)
-                {
-                    prefetch_issue(); // lands while this tile computes (and during phase 2 when it belongs to the next minibatch)
-                    staged = nstep != step;
-                }
                 mbar_wait(&tcbar[0], tc_parity);
                 mtc::fence_after();
                 CPPRL_MARK(2);
@@ -764,6 +765,13 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
                 // W2^T (this lane's row of the transposed image) for the data gradient: in flight during the chain and E2
                 tc_fetch32(a.image + (tF ? a.il.w2n[1] : a.il.w2n[0]), wreg);
+                if (has_next)
+                {
+                    // the next work item's rows: issued under the layer-2 chain (48 instructions, ~1.5 k cycles of tensor
+                    // pipe), they land while this tile computes (and during phase 2 when they belong to the next minibatch)
+                    prefetch_issue();
+                    staged = nstep != step;
+                }
                 mbar_wait(&tcbar[1], tc_parity);
                 mtc::fence_after();
                 CPPRL_MARK(22);
@@ -813,6 +821,52 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
             CPPRL_MARK(3);
             // ---- P3: heads: logits / loc [A][R] from the actor tower, value [R] from the critic tower ----
+            if (TC)
+            {
+                // Thread = (row r, quarter kq of the 64 hidden units): its 16 activations of each tower stay in registers
+                // while the head rows stream past as broadcast 16-byte loads (60 shared-memory loads per thread for 7
+                // outputs instead of 80 per output); the four quarters meet through shared memory -- the layer-2 operand
+                // planes, idle between the layer-2 chain and P5b.
+                float *PART = smem + sp.hb[0]; // [kq][A + 1][64]
+                const int r = (warp & 1) * 32 + lane, kq = warp >> 1;
+                if (r < R)
+                {
+                    const float *h2a = smem + sp.h2[0] + (16 * kq) * LD + r, *h2c = smem + sp.h2[1] + (16 * kq) * LD + r;
+                    float ha[16], hc[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        ha[j] = h2a[j * LD], hc[j] = h2c[j * LD];
+                    auto dot16 = [](const float *w, const float (&h)[16]) {
+                        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4)
+                        {
+                            const float4 wq = *reinterpret_cast<const float4 *>(w + j);
+                            s0 = fmaf(wq.x, h[j], s0);
+                            s1 = fmaf(wq.y, h[j + 1], s1);
+                            s2 = fmaf(wq.z, h[j + 2], s2);
+                            s3 = fmaf(wq.w, h[j + 3], s3);
+                        }
+                        return (s0 + s1) + (s2 + s3);
+                    };
+                    for (int o = 0; o < A; ++o)
+                        PART[(kq * (A + 1) + o) * 64 + r] = dot16(img + a.il.wo + o * kHid + 16 * kq, ha);
+                    PART[(kq * (A + 1) + A) * 64 + r] = dot16(img + a.il.wv + 16 * kq, hc);
+                }
+                __syncthreads();
+                for (int e = tid; e < (A + 1) * R; e += kUpdThreads)
+                {
+                    const int o = e / R, r2 = e - o * R;
+                    const float *pp = PART + o * 64 + r2;
+                    const int q1 = (A + 1) * 64;
+                    const float sum = ((pp[0] + pp[q1]) + (pp[2 * q1] + pp[3 * q1])) + img[o == A ? a.il.bv : a.il.bo + o];
+                    if (o == A)
+                        VAL[r2] = sum;
+                    else
+                        LOGIT[o * LD + r2] = sum;
+                }
+            }
+            else
             for (int e = tid; e < (A + 1) * R; e += kUpdThreads)
             {
                 const int o = e / R, r = e - o * R;
@@ -884,10 +938,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         const float diff = ACT[i * LD + r] - LOGIT[i * LD + r];
                         if (!training && a.out_dist && valid)
                             a.out_dist[static_cast<size_t>(row0 + r) * A + i] = LOGIT[i * LD + r];
-                        newlp += -(diff * diff) / (2.f * var) - log_sigma - 0.91893853320467274178f;
+                        // (one division per action: the three quotients by var share it)
+                        const float dq = diff / var;
+                        newlp += -0.5f * (diff * dq) - log_sigma - 0.91893853320467274178f;
                         ent += 0.5f + 0.5f * 1.8378770664093454836f + log_sigma;
-                        LOGIT[i * LD + r] = diff / var;                   // d logp / d loc
-                        STAT[(5 + i) * LD + r] = diff * diff / var - 1.f; // d logp / d scale_log
+                        LOGIT[i * LD + r] = dq;                    // d logp / d loc
+                        STAT[(5 + i) * LD + r] = diff * dq - 1.f;  // d logp / d scale_log
                     }
                 }
                 newlp += __shfl_xor_sync(0xffffffffu, newlp, 1);
@@ -965,9 +1021,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 continue;
             CPPRL_MARK(5);
             // ---- P5a: per-row terms -> gradient vector: loss sums, head biases, scale_log (one item per warp) ----
-            {
+            // (tensor-core variant: runs under the data-gradient chain below; nothing before the next tile's P4 touches
+            // its sources, and its destinations in the accumulator have no other writer)
+            auto p5a = [&]() {
                 const int n_items = 5 + A + 1 + (a.head == 1 ? A : 0);
-                for (int item = warp; item < n_items; item += kUpdThreads / 32)
+                for (int item = wt >> 5; wt >= 0 && item < n_items; item += kWorkThreads / 32)
                 {
                     const float *src;
                     int dst;
@@ -987,7 +1045,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     if (lane == 0)
                         gsm[dst] += sum; // each destination has exactly one owner in this phase
                 }
-            }
+            };
+            if (!TC)
+                p5a();
             // ---- P5b: head weight gradients and dz2 = (head^T dout) * (1 - h2^2), in place over H2.
             // Thread = (feature k, half of the rows); dh for its rows stays in registers while the loop over the
             // runtime number of head outputs streams dout rows (broadcast LDS) against the cached h2 row.
@@ -1092,6 +1152,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                                                                 b_hi + GeoT::kPlaneB, mtc::idesc_n(64));
                     mtc::commit(&tcbar[2]);
                 }
+                p5a();
                 mbar_wait(&tcbar[2], tc_parity);
                 mtc::fence_after();
                 CPPRL_MARK(7);
@@ -1154,6 +1215,22 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         }
                         mtc::commit(&tcbar[3 + pass]);
                     }
+                    if (pass == 0 && tile + G >= n_tiles)
+                    {
+                        // last tile of this CTA in this minibatch, first chain in flight: the parts of the gradient partial that
+                        // are already final -- the bias sums of column half 1 are handed to half 0 through shared memory, the
+                        // head gradients of row half 1 are folded into the accumulator
+                        if (ch == 1)
+                            G2_B2[F] = acc_b2, G2_B2[2 * kHid + F] = acc_b1;
+                        for (int i = wt; wt >= 0 && i < (A + 1) * kHid; i += kWorkThreads)
+                        {
+                            const int o = i >> 6, k = i & 63;
+                            if (o < A)
+                                gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
+                            else
+                                gsm[a.po.wv + k] += G2_WV[k];
+                        }
+                    }
                     if (k_begin < k_end)
                     {
                         mbar_wait(&tcbar[3 + pass], tc_parity);
@@ -1191,8 +1268,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     // last tile of this CTA in this minibatch: everything of the gradient partial that needs no barrier of
                     // its own leaves NOW, under the tile's closing barrier -- this lane's 32 columns of dW2 straight from
                     // registers, dW1 staged in the flat parameter order [tower][unit * D + k] (rows are D floats, not a
-                    // multiple of 4; the data-gradient operand planes are idle), the bias sums of column half 1 handed to
-                    // half 0 through shared memory, the head gradients of row half 1 folded into the accumulator
+                    // multiple of 4; the data-gradient operand planes are idle)
                     float *part = a.gpart + static_cast<size_t>(blockIdx.x) * Pstride;
                     (void)part;
                     // dW2 [lane][64] staged with a row stride of 68 floats (conflict-free 16-byte stores; a lane's 128 bytes
@@ -1207,16 +1283,6 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     for (int i = 0; i < 16; ++i)
                         if (16 * ch + i < D)
                             w1s[F * D + 16 * ch + i] = acc_w1[TC ? i : 0];
-                    if (ch == 1)
-                        G2_B2[F] = acc_b2, G2_B2[2 * kHid + F] = acc_b1;
-                    for (int i = tid; i < (A + 1) * kHid; i += kUpdThreads)
-                    {
-                        const int o = i >> 6, k = i & 63;
-                        if (o < A)
-                            gsm[a.po.wo + o * kHid + k] += G2_WO[o * kHid + k];
-                        else
-                            gsm[a.po.wv + k] += G2_WV[k];
-                    }
                 }
                 if (tile + G < n_tiles)
                 {
