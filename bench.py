@@ -420,7 +420,7 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "peak_source": f"nominal 148 SM x 128 FMA/clk x 2 x {sm_max:.0f} MHz; fp32 CUDA-core bound, neither hbm nor tensor "
                        "(see DESIGN.md); share of step = " + f"{upd_ms / total_ms:.2f}",
     }
-    mlp_tc = (w.base == "mlp" and lib.cpprl_b200_mlp_update_variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) == 1)
+    mlp_tc = (w.base == "mlp" and lib.cpprl_b200_mlp_update_variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) > 0)
     if mlp_tc:
         # large minibatches train on the tensor-core variant (tcgen05 kind::tf32 as 3xTF32, csrc/mlp_tc.cuh): three TF32
         # MMAs per algorithmic product at half the bf16 rate -> this path's own ceiling is the measured bf16 peak / 6.

@@ -393,8 +393,9 @@ int cpprl_b200_debug_tc_gemm(int variant, const float *d_a, const float *d_b, fl
 /* Profiling hook: when d_buffer (device, grid*32 int64) is non-NULL, thread 0 of every CTA of the fused PPO
  * update kernel stores clock64() at its phase boundaries during minibatch `step` of each launch. */
 void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step);
-/* Which variant of the fused MlpBase update a minibatch of this shape trains on: 1 = tensor cores (tcgen05 kind::tf32 as
- * 3xTF32, minibatches of more than 32 rows per SM with at most 32 observation columns), 0 = fp32 CUDA cores.
+/* Which variant of the fused MlpBase update a minibatch of this shape trains on: > 0 = tensor cores (tcgen05 kind::tf32 as
+ * 3xTF32, minibatches of more than 32 rows per SM with at most 32 observation columns; the value is the tile's row
+ * count, 56 or 64), 0 = fp32 CUDA cores.
  * CPPRL_B200_MLP_TC=0 in the environment forces 0 (A/B runs). */
 int cpprl_b200_mlp_update_variant(int64_t minibatch_rows, int64_t obs_dim, int64_t num_actions);
 

@@ -210,7 +210,8 @@ struct Scratch
     size_t image_floats = 0;
     float *gpart = nullptr;
     size_t gpart_floats = 0;
-    unsigned int *barrier = nullptr;
+    unsigned int *barrier = nullptr; // two counters (see MlpUpdateArgs::barrier)
+    unsigned int barrier_launches = 0;
     UpdateState *state = nullptr;
     double *adv_sums = nullptr;
     void *adv_ws = nullptr; // per-CTA partials + arrival counter of the deterministic advantage moments
@@ -300,9 +301,11 @@ bool mlp_tc_enabled()
 // tensor-core variant: 56-row tiles, so that 148 CTAs cover an 8192-row minibatch in one wave.
 // Training launches keep at least 16 CTAs so that the phase-2 slice of the parameter vector each CTA reduces,
 // steps and keeps resident in shared memory stays small; CTAs beyond the tile count only take part in phase 2.
-int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan)
+// B_max >= B: the largest minibatch the launch may meet (env-sharded updates: minibatches are ragged around B).
+int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan, int64_t B_max = 0)
 {
     const int sms = sm_count();
+    B_max = std::max(B, B_max);
     auto shape = [&](int r, bool tc, Plan &pl) {
         const int64_t tiles = (B + r - 1) / r;
         pl.R = r;
@@ -314,8 +317,16 @@ int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training
         pl.per_cta = training ? round_up((p4 + pl.grid - 1) / pl.grid, 4) : 0;
         return mlp_update_smem_bytes(r, pl.il.floats, po.Pstride, Dp, Ap, pl.per_cta, tc, pl.il.tail, po.wv);
     };
-    if (training && B > 32ll * sms && Dp <= 32 && mlp_tc_enabled() && shape(kTcRows, true, plan) <= 227 * 1024)
-        return 0;
+    if (training && B > 32ll * sms && Dp <= 32 && mlp_tc_enabled())
+    {
+        // 56-row tiles unless 64-row tiles take fewer waves over the SMs (a tile costs about the same either way)
+        auto waves = [&](int r) { return ((B_max + r - 1) / r + sms - 1) / sms; };
+        const int r = waves(kTcRowsWide) < waves(kTcRows) ? kTcRowsWide : kTcRows;
+        if (shape(r, true, plan) <= 227 * 1024)
+            return 0;
+        if (r != kTcRows && shape(kTcRows, true, plan) <= 227 * 1024)
+            return 0;
+    }
     int R = (B <= 32ll * sms) ? 32 : 64;
     if (R == 64 && shape(64, false, plan) > 227 * 1024)
         R = 32;
@@ -742,7 +753,9 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     // pairs with CTA b of the peers) covers the whole box-wide slice of parameters, and ragged minibatches that
     // exceed it simply take more than one tile per CTA
     const int64_t plan_rows = sharded ? (mbs + view.world - 1) / view.world : mbs;
-    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, h->plan))
+    // (a rank's share of a minibatch is binomial around plan_rows: four standard deviations of headroom)
+    const int64_t plan_max = sharded ? plan_rows + static_cast<int64_t>(4.0 * std::sqrt(static_cast<double>(plan_rows))) + 1 : plan_rows;
+    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, h->plan, plan_max))
         return rc;
     const ImageLayout il = h->plan.il;
     if (sharded)
@@ -852,7 +865,7 @@ extern "C" int cpprl_b200_mlp_update_variant(int64_t minibatch_rows, int64_t obs
     Plan plan;
     if (choose_plan(minibatch_rows, po, round_up(static_cast<int>(obs_dim), 8), round_up(static_cast<int>(num_actions), 4), true, plan))
         return 0;
-    return plan.tc ? 1 : 0;
+    return plan.tc ? plan.R : 0;
 }
 
 static int ppo_shard_permutation(cpprl_b200_ppo *h, const int64_t *d_perm)
@@ -938,8 +951,12 @@ static int ppo_launch_epoch(cpprl_b200_ppo *h, const int64_t *d_perm)
     h->args.perm = reinterpret_cast<const long long *>(d_perm);
     h->args.dbg_clocks = g_dbg_clocks;
     h->args.dbg_step = g_dbg_step;
+    h->args.dbg_launch = static_cast<int>(h->scratch.barrier_launches);
     KernelTimer timer("update", h->stream);
+    h->args.barrier_sel = static_cast<int>(h->scratch.barrier_launches & 1u);
     int rc = mlp_update_launch(h->plan.R, h->args, h->plan.grid, h->stream);
+    if (rc == 0)
+        ++h->scratch.barrier_launches; // (only a launch that ran has zeroed the other counter)
     if (rc == 0)
         ++h->epoch;
     return rc;
@@ -1366,7 +1383,7 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     // not from this rank's own row count (shards may differ by one environment, api.shard_range); a rank that holds
     // more rows than the plan simply walks more than one tile per CTA
     const int64_t plan_rows = sharded ? (rows_global + view.world - 1) / view.world : rows;
-    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, plan))
+    if (int rc = choose_plan(plan_rows, po, Dp, Ap, true, plan, sharded ? plan_rows + ro->T : plan_rows)) // (shards differ by one environment)
         return rc;
     const ImageLayout il = plan.il;
     if (sharded)
@@ -1432,8 +1449,10 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.barrier = h->scratch.barrier;
     a.state = h->scratch.state;
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
+    a.barrier_sel = static_cast<int>(h->scratch.barrier_launches & 1u);
     if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
         return rc;
+    ++h->scratch.barrier_launches;
     CPPRL_CUDA_TRY(cudaMemcpyAsync(h->h_state, h->scratch.state, sizeof(UpdateState), cudaMemcpyDeviceToHost, s));
     return 0;
 }
@@ -1612,8 +1631,10 @@ static int evaluate_impl(EvalScratch &es, const cpprl_b200_policy *policy, const
     a.out_dist = d_dist;
     CPPRL_CUDA_TRY(cudaMemsetAsync(g_eval_scratch.image, 0, il.floats * sizeof(float), s));
     CPPRL_CUDA_TRY(cudaMemsetAsync(d_entropy, 0, sizeof(float), s));
+    a.barrier_sel = static_cast<int>(g_eval_scratch.barrier_launches & 1u);
     if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
         return rc;
+    ++g_eval_scratch.barrier_launches;
     finish_entropy_kernel<<<1, 1, 0, s>>>(d_entropy, 1.f / static_cast<float>(B)); // entropy().mean() (policy.cpp:109)
     CPPRL_LAUNCH_CHECK("finish_entropy_kernel");
     return 0;

@@ -36,7 +36,7 @@ constexpr int kMaxDp = 32;       // observation columns (padded to 8) this path 
 template <int R>
 struct Geo
 {
-    static_assert(R % 8 == 0 && R >= 8 && R <= 56, "tile rows");
+    static_assert(R % 8 == 0 && R >= 8 && R <= 64, "tile rows");
     static constexpr int CH = R / 2;                       // columns (tile rows) per thread in the epilogues
     static constexpr int LD = R + 4;                       // row stride of the fp32 feature-major h2 tile (heads)
     static constexpr uint32_t kLboB = (R / 8) * 128 + 16;  // row-major operands [n = row][k = feature]: 16 B off a multiple of

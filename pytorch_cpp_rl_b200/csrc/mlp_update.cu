@@ -23,6 +23,7 @@
 // fp32 CUDA-core FMAs throughout: the 64-wide contractions stay inside the 1e-4 parity budget only in
 // full fp32; tensor cores are reserved for the CNN base.
 #include <math.h>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "mlp_update.cuh"
@@ -77,8 +78,6 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
         // operand planes, hi then lo each (bytes / 4); the row-major planes read one non-existent 8-row group past
         // their end (N = 64 instructions over R <= 56 rows): something must follow them, which the order guarantees
         const int lbo_b = (R / 8) * 128 + 16, plane_b = 16 * lbo_b, plane_f = (R / 4) * 1024, plane_xf = (R / 4) * 528;
-        const int plane_xb = (Dp / 4) * lbo_b;
-        p.xb = o, o += 2 * plane_xb / 4;
         for (int t = 0; t < 2; ++t)
             p.hb[t] = o, o += 2 * plane_b / 4;
         p.xf = o, o += 2 * plane_xf / 4;
@@ -94,6 +93,11 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     }
     for (int t = 0; t < 2; ++t)
         p.h2[t] = o, o += kHid * LD;
+    // tensor-core variant: the row-major observation planes (layer 1's B operand: at most 2 x 8 x (8 x 128 + 16) bytes) are
+    // live from finalize_stage to the end of the layer-1 chain, the fp32 h2 tile (2 x 64 x LD floats) from the layer-2
+    // epilogue to P5b -- disjoint, so the planes overlay the tile (what lets the 64-row tile fit in 227 KB)
+    if (tc)
+        p.xb = p.h2[0];
     p.logit = o, o += Ap * LD;
     p.dlogit = o, o += Ap * LD;
     p.val = o, o += LD;
@@ -288,6 +292,16 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
     (void)X, (void)h1t, (void)w1t_img, (void)b1_img, (void)w2t_img, (void)w2n_img, (void)b2_img, (void)po_w1, (void)po_b1, (void)po_w2,
         (void)po_b2, (void)G2_B1, (void)tcbar, (void)tmem_slot;
 
+    if (a.dbg_clocks && threadIdx.x == 0)
+    {
+        a.dbg_clocks[blockIdx.x * 32 + 27] = clock64(); // kernel entry
+        if (blockIdx.x == 0)
+        {
+            unsigned long long ns;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+            a.dbg_clocks[148 * 32 + 2 * (a.dbg_launch & 63)] = static_cast<long long>(ns);
+        }
+    }
     const int G = gridDim.x;
     const int P = a.po.P, Pstride = a.po.Pstride, Pstat = Pstride - kNumStats;
     const int D = a.D, Dp = a.Dp, A = a.A;
@@ -550,9 +564,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         if (a.dbg_clocks && tid == 0 && step == a.dbg_step)                           \
             a.dbg_clocks[blockIdx.x * 32 + (slot)] = clock64();                       \
     } while (0)
-    grid_arrive(a.barrier); // the image is complete once every CTA has scattered its share of the parameters
+    unsigned int *const gbar = a.barrier + 8 * a.barrier_sel;
+    if (blockIdx.x == 0 && tid == 0)
+        a.barrier[8 * (a.barrier_sel ^ 1)] = 0u; // the NEXT launch's counter (stream order: the previous launch is complete)
+    grid_arrive(gbar); // the image is complete once every CTA has scattered its share of the parameters
     bar_target += G;
-    grid_wait(a.barrier, bar_target);
+    grid_wait(gbar, bar_target);
+    if (a.dbg_clocks && tid == 0)
+        a.dbg_clocks[blockIdx.x * 32 + 28] = clock64(); // prologue done (image built, first grid barrier passed)
     if (stopped)
     {
         leave();
@@ -1400,7 +1419,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             }
         }
         CPPRL_MARK(10);
-        grid_arrive(a.barrier);
+        grid_arrive(gbar);
         if (tid == 0)
         {
             // bias corrections as host-style doubles (libtorch Adam), t = steps applied so far + 1; computed while
@@ -1420,7 +1439,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             fin_ahead = true;
         }
         bar_target += G;
-        grid_wait(a.barrier, bar_target);
+        grid_wait(gbar, bar_target);
         CPPRL_MARK(11);
 
         // ---- phase 2: fixed-order reduction of the partials for this CTA's slice + the statistics slots ---------
@@ -1584,16 +1603,26 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         CPPRL_MARK(13);
         if (step + 1 < a.n_steps)
         {
-            grid_arrive(a.barrier);
+            grid_arrive(gbar);
             CPPRL_MARK(14);
             bar_target += G;
-            grid_wait(a.barrier, bar_target);
+            grid_wait(gbar, bar_target);
             CPPRL_MARK(15);
         }
     } // steps
     if (training)
         write_back_state();
     leave();
+    if (a.dbg_clocks && tid == 0)
+    {
+        a.dbg_clocks[blockIdx.x * 32 + 29] = clock64(); // kernel exit
+        if (blockIdx.x == 0)
+        {
+            unsigned long long ns;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+            a.dbg_clocks[148 * 32 + 2 * (a.dbg_launch & 63) + 1] = static_cast<long long>(ns);
+        }
+    }
 }
 
 template <int R, bool TC>
@@ -1605,8 +1634,7 @@ int launch_update(const MlpUpdateArgs &args, int grid, size_t smem_bytes, cudaSt
         CPPRL_CUDA_TRY(cudaFuncSetAttribute(mlp_update_kernel<R, TC>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         mark_configured_on_device(configured);
     }
-    // the grid barrier counts arrivals from zero in every launch
-    CPPRL_CUDA_TRY(cudaMemsetAsync(args.barrier, 0, sizeof(unsigned int), s));
+    // (the grid barrier counts arrivals from zero in every launch: the previous launch zeroed this launch's counter)
     void *kargs[] = {const_cast<MlpUpdateArgs *>(&args)};
     CPPRL_CUDA_TRY(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(mlp_update_kernel<R, TC>), dim3(grid),
                                                dim3(kUpdThreads), kargs, smem_bytes, s));
@@ -1631,9 +1659,9 @@ int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s
         return fail(CPPRL_B200_EINVAL, "mlp_update: image layout does not match the kernel variant");
     if (tc)
     {
-        if (R != kTcRows || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
+        if ((R != kTcRows && R != kTcRowsWide) || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
             return fail(CPPRL_B200_EINVAL, "mlp_update: unsupported tensor-core plan");
-        return launch_update<kTcRows, true>(args, grid, smem, s);
+        return R == kTcRows ? launch_update<kTcRows, true>(args, grid, smem, s) : launch_update<kTcRowsWide, true>(args, grid, smem, s);
     }
     if (R == 64)
         return launch_update<64, false>(args, grid, smem, s);

@@ -11,6 +11,7 @@ constexpr int kUpdThreads = 256;   // 8 warps: warps 0-3 run the actor tower, 4-
 constexpr int kNumStats = 8;       // slots appended to the gradient vector (5 used)
 constexpr int kMaxActions = 16;
 constexpr int kTcRows = 56;        // tile rows of the tensor-core variant: 148 CTAs x 56 rows cover an 8192-row minibatch in one wave
+constexpr int kTcRowsWide = 64;    // ... and the tile for minibatches that need fewer waves with it (ragged env-sharded minibatches: 8192 +- 4 sigma rows)
 
 enum { kAlgoPPO = 0, kAlgoA2C = 1, kAlgoForward = 2 };
 enum { kOptAdam = 0, kOptRmsprop = 1 };
@@ -104,10 +105,12 @@ struct MlpUpdateArgs
     float beta1, beta2, eps, alpha;
     // scratch / state
     float *gpart;         // [grid][Pstride] per-CTA gradient partials
-    unsigned int *barrier;
+    unsigned int *barrier; // two grid-barrier counters, 8 words apart: a launch counts on [8 * barrier_sel] and zeroes the other one
+    int barrier_sel;       // for the NEXT launch (no memset between the cooperative launches of an update)
     UpdateState *state;
     long long *dbg_clocks; // nullable: [grid][32] clock64() phase markers of step dbg_step (profiling hook)
     int dbg_step;
+    int dbg_launch;        // launch counter: with dbg_clocks, CTA 0 stores %globaltimer at entry / exit in [148 * 32 + 2 * (dbg_launch % 64)]
     // forward-only outputs (kAlgoForward)
     float *out_value, *out_logp, *out_entropy_sum;
     float *out_dist; // nullable [B][A]: normalised log-probabilities (Categorical) / means (Normal): what act() samples from

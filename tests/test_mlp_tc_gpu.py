@@ -21,8 +21,9 @@ def _variant(rows, obs, act):
 
 
 def test_variant_selection():
-    assert _variant(8192, 17, 6) == 1          # cfg3's minibatch
-    assert _variant(20480, 8, 4) == 1          # cfg2
+    assert _variant(8192, 17, 6) == 56         # cfg3's minibatch
+    assert _variant(20480, 8, 4) == 56         # cfg2
+    assert _variant(9000, 17, 6) == 64         # fewer waves with 64-row tiles
     assert _variant(256, 8, 4) == 0            # cfg1: a minibatch that does not fill the chip
     assert _variant(8192, 33, 6) == 0          # more than 32 observation columns: CUDA-core variant
     os.environ["CPPRL_B200_MLP_TC"] = "0"
@@ -57,6 +58,10 @@ CASES = {
                                             storage_hidden=1)),
     "multi_tile": ("cfg3", dict(T=20, N=1024, num_epoch=1, num_mini_batch=1)),                 # 20480 rows: three tiles per CTA
     "a2c_obs8": ("cfg2", dict(T=3, N=2048)),
+    # 9000-row minibatches: 161 tiles of 56 rows (two waves over 148 SMs) but 141 of 64 -> the 64-row tile
+    "wide_tile_normal": ("cfg3", dict(T=9, N=1000, num_epoch=2, num_mini_batch=1)),
+    "wide_tile_categorical_ragged": ("cfg1", dict(T=7, N=1300, obs_shape=(8,), num_actions=4, num_epoch=1, num_mini_batch=1,
+                                                  storage_hidden=1)),                            # 9100 rows = 142 tiles + 12 rows
     "no_normaliser": ("cfg3", dict(T=8, N=640, normalize_obs=False, num_epoch=1, num_mini_batch=1)),
 }
 
@@ -65,7 +70,7 @@ CASES = {
 def test_tc_variant_matches_reference_and_cuda_core_variant(ref, case):
     base, kw = CASES[case]
     w = CONFIGS[base].scaled(**kw)
-    assert _variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) == 1, "case does not reach the tensor-core variant"
+    assert _variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) > 0, "case does not reach the tensor-core variant"
     seed = 3
     r = synth_rollout(w, seed)
     sess = H.make_ref_session(ref, w, init_seed=seed)
