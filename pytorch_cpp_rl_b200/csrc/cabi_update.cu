@@ -301,6 +301,17 @@ bool mlp_tc_enabled()
 // tensor-core variant: 56-row tiles, so that 148 CTAs cover an 8192-row minibatch in one wave.
 // Training launches keep at least 16 CTAs so that the phase-2 slice of the parameter vector each CTA reduces,
 // steps and keeps resident in shared memory stays small; CTAs beyond the tile count only take part in phase 2.
+// Training launches keep at least this many CTAs: CTAs beyond the tile count only take part in phase 2, where each
+// reduces, steps and keeps resident in shared memory 1 / grid of the parameter vector (CPPRL_B200_MIN_GRID for A/B runs).
+static int min_training_grid(int sms)
+{
+    static const int forced = [] {
+        const char *e = std::getenv("CPPRL_B200_MIN_GRID");
+        return e ? std::atoi(e) : 0;
+    }();
+    return std::min(forced > 0 ? forced : sms, sms); // every SM: measured on cfg1 (8 tiles per minibatch) 16 -> 148 CTAs: 0.467 -> 0.416 ms per update
+}
+
 // B_max >= B: the largest minibatch the launch may meet (env-sharded updates: minibatches are ragged around B).
 int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training, Plan &plan, int64_t B_max = 0)
 {
@@ -312,7 +323,7 @@ int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training
         pl.tc = tc;
         pl.il = make_image_layout(Dp, Ap, tc);
         pl.n_active = static_cast<int>(tiles < sms ? tiles : sms);
-        pl.grid = training ? std::max(pl.n_active, std::min(16, sms)) : pl.n_active;
+        pl.grid = training ? std::max(pl.n_active, min_training_grid(sms)) : pl.n_active;
         const int p4 = po.Pstride - kNumStats; // parameter count rounded up to 4
         pl.per_cta = training ? round_up((p4 + pl.grid - 1) / pl.grid, 4) : 0;
         return mlp_update_smem_bytes(r, pl.il.floats, po.Pstride, Dp, Ap, pl.per_cta, tc, pl.il.tail, po.wv);
@@ -762,7 +773,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     {
         const int sms = sm_count();
         h->plan.grid = std::min(sms, std::max(h->plan.grid, static_cast<int>(std::min<int64_t>(sms, (plan_rows * 5 / 4 + h->plan.R - 1) / h->plan.R))));
-        h->plan.grid = std::max(h->plan.grid, std::min(16, sms));
+        h->plan.grid = std::max(h->plan.grid, min_training_grid(sms));
         h->plan.n_active = h->plan.grid;
         h->plan.per_cta = round_up((po.Pstride - kNumStats + h->plan.grid - 1) / h->plan.grid, 4);
         if (mlp_update_smem_bytes(h->plan.R, il.floats, po.Pstride, Dp, Ap, h->plan.per_cta, h->plan.tc, il.tail, po.wv) > 227 * 1024)

@@ -167,6 +167,16 @@ __device__ __forceinline__ void store_split16(uint32_t col, uint32_t lo_off, con
     st16(col + lo_off, lo);
 }
 
+// tanh for the tensor-core epilogues, 1 - 2 / (exp(2x) + 1) on the special-function unit (ex2.approx + rcp.approx: six
+// instructions against ~25 of tanhf; the epilogues are instruction-issue bound: 28 activations per thread per layer).
+// Absolute error below 2e-7 -- the rounding level of an fp32 activation near 1 -- as in the recurrent kernel's gates
+// (gru_update.cu); CPPRL_B200_MLP_TC=0 keeps the correctly rounded tanhf of the CUDA-core variant for A/B runs.
+__device__ __forceinline__ float tanh_sfu(float x)
+{
+    const float e = __expf(2.f * fminf(fmaxf(x, -15.f), 15.f)); // tanh(+-15) = +-1 in fp32
+    return 1.f - __fdividef(2.f, e + 1.f);
+}
+
 // x = hi + lo with hi on the TF32 grid (round to nearest, ties away) and lo = x - hi exact in fp32 (cnn_gemm_tc.cuh)
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
 } // namespace mtc

@@ -758,7 +758,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
                         {
-                            const float h = tanhf(v[i] + bias);
+                            const float h = mtc::tanh_sfu(v[i] + bias);
                             hi[i] = mtc::tf32_hi(h), lo[i] = h - hi[i];
                             *reinterpret_cast<float *>(hb_hi + 16u * (r0 + i) + ob) = hi[i];
                             *reinterpret_cast<float *>(hb_lo + 16u * (r0 + i) + ob) = lo[i];
@@ -803,7 +803,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         float v[4];
                         mtc::ld4(lane_base + mtc::kColA + 64 * tF + ch * CH + c, v);
                         *reinterpret_cast<float4 *>(h2row + c) =
-                            make_float4(tanhf(v[0] + bias), tanhf(v[1] + bias), tanhf(v[2] + bias), tanhf(v[3] + bias));
+                            make_float4(mtc::tanh_sfu(v[0] + bias), mtc::tanh_sfu(v[1] + bias), mtc::tanh_sfu(v[2] + bias), mtc::tanh_sfu(v[3] + bias));
                     }
                 }
                 CPPRL_MARK(23);
