@@ -130,6 +130,56 @@ __device__ __forceinline__ void ld4(uint32_t addr, float (&v)[4])
                  : "memory");
     v[0] = __uint_as_float(r0), v[1] = __uint_as_float(r1), v[2] = __uint_as_float(r2), v[3] = __uint_as_float(r3);
 }
+// N consecutive columns of this thread's lane WITHOUT the wait: the caller issues all the loads of an epilogue, then one
+// wait_ld(), then reads the registers (the pattern of CUTLASS's fence_view_async_tmem_load)
+__device__ __forceinline__ void ld4_nowait(uint32_t addr, float *v)
+{
+    uint32_t r[4];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void ld8_nowait(uint32_t addr, float *v)
+{
+    uint32_t r[8];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+                 : "r"(addr));
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void ld16_nowait(uint32_t addr, float *v)
+{
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(addr));
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+        v[i] = __uint_as_float(r[i]);
+}
+// CH (a multiple of 4, at most 32: 28 and 32 in the kernel) columns starting at addr, one wait
+template <int CH>
+__device__ __forceinline__ void ld_cols(uint32_t addr, float (&v)[CH])
+{
+    static_assert(CH % 4 == 0 && CH <= 32, "columns per thread");
+    int c = 0;
+#pragma unroll
+    for (; c + 16 <= CH; c += 16)
+        ld16_nowait(addr + c, v + c);
+    if (c + 8 <= CH)
+    {
+        ld8_nowait(addr + c, v + c);
+        c += 8;
+    }
+    if (c + 4 <= CH)
+        ld4_nowait(addr + c, v + c);
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
 __device__ __forceinline__ void st4(uint32_t addr, float a, float b, float c, float d)
 {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(__float_as_uint(a)), "r"(__float_as_uint(b)),

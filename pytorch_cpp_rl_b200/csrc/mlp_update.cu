@@ -747,8 +747,9 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 {
                     const float bias = img[(tF ? a.il.b1[1] : a.il.b1[0]) + jF];
                     const uint32_t ob = (jF >> 2) * GeoT::kLboB + (jF & 3) * 4u;
-                    // (rolled: the kernel's code is far larger than the instruction caches and every phase runs once per
-                    // tile, so an unrolled epilogue is paid for in instruction fetches -- ncu: 11 % of the stalls are no_inst)
+                    // (rolled, four columns per tensor-memory load: the phase is bound by its 70 shared-memory stores and the
+                    // issue slots of 28 activations per thread; one wide load + straight-line code measured 15 % slower here,
+                    // while the store-free dz1 epilogue below gained 25 % from it)
 #pragma unroll 1
                     for (int c = 0; c < CH; c += 4)
                     {
@@ -1178,11 +1179,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 // dz1 = dh1 * (1 - h1^2) -> tensor memory (the A operand of dW1, over W2^T which the chain has consumed); db1
                 {
                     float bsum = 0.f;
-#pragma unroll 1
+                    float va[CH];
+                    mtc::ld_cols<CH>(lane_base + mtc::kColG + 64 * tF + ch * CH, va);
+#pragma unroll
                     for (int c = 0; c < CH; c += 4)
                     {
-                        float v[4];
-                        mtc::ld4(lane_base + mtc::kColG + 64 * tF + ch * CH + c, v);
+                        const float v[4] = {va[c], va[c + 1], va[c + 2], va[c + 3]};
                         const int r0 = ch * CH + c;
                         const uint32_t of = 16u * jF + (r0 >> 2) * GeoT::kLboF;
                         const float4 hh = *reinterpret_cast<const float4 *>(hf_hi + of), hl = *reinterpret_cast<const float4 *>(hf_lo + of);
