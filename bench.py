@@ -424,13 +424,13 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     if mlp_tc:
         # large minibatches train on the tensor-core variant (tcgen05 kind::tf32 as 3xTF32, csrc/mlp_tc.cuh): three TF32
         # MMAs per algorithmic product at half the bf16 rate -> this path's own ceiling is the measured bf16 peak / 6.
-        # What bounds the kernel is NOT the tensor pipe (ncu: 10 % active) but the chain of dependent stages of each of
+        # What bounds the kernel is NOT the tensor pipe (ncu: 13 % active) but the chain of dependent stages of each of
         # the update's sequential optimiser steps (two grid barriers per step): DESIGN.md section 4.
         pk = ROOT / "MEASURED_PEAKS.json"
         peaks = json.loads(pk.read_text()) if pk.exists() else {}
         tc_peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 2250.0
         roofline.update({
-            "kernel": "mlp_update_kernel<56, tensor cores> (tcgen05 3xTF32 towers + CUDA-core heads, loss, reduction, Adam)",
+            "kernel": "mlp_update_kernel<56 or 64 rows, tensor cores> (tcgen05 3xTF32 towers + CUDA-core heads, loss, reduction, Adam)",
             "bound": "tensor", "peak": tc_peak, "frac": achieved / tc_peak,
             "ceiling_3xtf32": tc_peak / 6.0, "frac_of_3xtf32_ceiling": achieved / (tc_peak / 6.0),
             "frac_of_nominal_fp32_cuda_core_peak": achieved / fp32_peak,
@@ -440,7 +440,7 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     if w.name == "cfg3" and world == 1:
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch (= one epoch) from the committed ncu --set full capture;
         # the algorithmic bytes of an epoch are the gathered rollout rows, 262144 x 112 B = 29.4 MB: no wasted re-reads
-        roofline["traffic"] = (29655296 + 1394944) if mlp_tc else (29616128 + 353792)
+        roofline["traffic"] = (29674240 + 630016) if mlp_tc else (29616128 + 353792)
         roofline["traffic_source"] = "profiles/r2_mlp_update_tc_cfg3_raw.csv" if mlp_tc else "profiles/r1b_mlp_update_cfg3_raw.csv"
     if w.base == "cnn" and os.environ.get("CPPRL_B200_CNN_FP32") != "1":
         # the ten CnnBase contractions run on tcgen05 as 3xTF32 (hi*hi + hi*lo + lo*hi): three TF32 MMAs per

@@ -1511,15 +1511,45 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             const bool comm_ok = *reinterpret_cast<volatile int *>(&a.state->comm_error) == 0;
             for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
             {
-                float g = 0.f;
-                for (int r = 0; r < world; ++r) // rank order: bit-identical sums on every rank
+                // the words of ALL peers are polled together (independent loads in flight: one L2 round trip per sweep
+                // instead of one per peer -- 7 dependent round trips per step at 8 GPUs), then added in rank order
+                const LLWord *base = exchange_xbuf(a.comm.area[my_rank]) + par_off + cta_off + i;
+                float v[kMaxRanks];
+                unsigned int pending = 0;
+#pragma unroll
+                for (int r = 0; r < kMaxRanks; ++r)
                 {
-                    float v = RED[i];
-                    if (r != my_rank && comm_ok &&
-                        !ll_load(exchange_xbuf(a.comm.area[my_rank]) + par_off + static_cast<size_t>(r) * a.comm.x_stride + cta_off + i, seq, v))
-                        a.state->comm_error = 1;
-                    g += v;
+                    v[r] = 0.f;
+                    if (r < world && r != my_rank && comm_ok)
+                        pending |= 1u << r;
                 }
+                for (long long spins = 0; pending && spins < (1ll << 22); ++spins)
+                {
+                    unsigned int w[kMaxRanks], sq[kMaxRanks];
+#pragma unroll
+                    for (int r = 0; r < kMaxRanks; ++r)
+                        if (pending >> r & 1u)
+                            asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];"
+                                         : "=r"(w[r]), "=r"(sq[r])
+                                         : "l"(base + static_cast<size_t>(r) * a.comm.x_stride)
+                                         : "memory");
+#pragma unroll
+                    for (int r = 0; r < kMaxRanks; ++r)
+                        if ((pending >> r & 1u) && sq[r] == seq)
+                        {
+                            v[r] = __uint_as_float(w[r]);
+                            pending &= ~(1u << r);
+                        }
+                    if (pending && spins > 8192)
+                        __nanosleep(200);
+                }
+                if (pending)
+                    a.state->comm_error = 1; // a peer never published its record (bounded wait expired)
+                float g = 0.f;
+#pragma unroll
+                for (int r = 0; r < kMaxRanks; ++r) // rank order: bit-identical sums on every rank
+                    if (r < world)
+                        g += r == my_rank ? RED[i] : v[r];
                 RED[i] = g;
             }
             CPPRL_MARK(18);

@@ -39,7 +39,11 @@ c = c[used]
 if rank != 0:
     torch.cuda.synchronize()
     sys.exit(0)
-print(f"{cfg}: {used.sum()} CTAs, step {step}; cycles per phase (min / median / max over CTAs); multi-tile CTAs show the LAST tile")
+# CTAs beyond the tile count only take part in phase 2 (their tile marks stay zero): statistics over the CTAs with tiles
+has_tile = c[:, 3] != 0
+print(f"{cfg}: {used.sum()} CTAs ({has_tile.sum()} with tiles), step {step}; cycles per phase (min / median / max over the CTAs with tiles); "
+      "multi-tile CTAs show the LAST tile")
+c = c[has_tile]
 d = np.diff(c[:, :16], axis=1)
 for i, n in enumerate(NAMES):
     print(f"  {n:12s} {d[:, i].min():8d} {int(np.median(d[:, i])):8d} {d[:, i].max():8d}")
