@@ -119,3 +119,36 @@ def test_tc_variant_is_deterministic(ref):
     a, sa = _update_once(w, r, params0, norm0, perms)
     b, sb = _update_once(w, r, params0, norm0, perms)
     assert np.array_equal(a, b) and np.array_equal(sa[0], sb[0])
+
+
+def test_tc_variant_kl_early_stop(ref):
+    """The KL early stop (ppo.cpp:100-104) INSIDE the tensor-core kernel: every CTA must take the same decision, hand its
+    tensor memory back and write its optimiser state before leaving; later epochs' launches must return at once; the next
+    update must start from a clean state.  Large learning rate + the default kl_target trip the stop mid-update."""
+    w = CONFIGS["cfg3"].scaled(T=13, N=800, num_epoch=4, num_mini_batch=2, kl_target=0.01, learning_rate=2e-2)
+    assert _variant(w.rows // w.num_mini_batch, w.obs_dim, w.num_actions) > 0
+    seed = 11
+    r = synth_rollout(w, seed)
+    sess = H.make_ref_session(ref, w, init_seed=seed)
+    H.fill_policy_outputs(sess, w, r)
+    H.ref_load_rollout(sess, r)
+    policy, st = H.make_gpu_side(w, r, sess.get_params(), sess.get_normalizer())
+    algo = api.PPO(policy, w.clip_param, w.num_epoch, w.num_mini_batch, w.actor_loss_coef, w.value_loss_coef, w.entropy_coef,
+                   w.learning_rate, w.epsilon, 0.5, w.kl_target)
+    nv = torch.from_numpy(r["next_value"]).cuda()
+    stops = 0
+    for upd in range(3):
+        sess.compute_returns(r["next_value"], w.use_gae, w.gamma, w.tau)
+        want, _ = sess.update(1.0, perm_seed=70 + upd)
+        st.compute_returns(nv, w.use_gae, w.gamma, w.tau)
+        got = np.array([d.value for d in algo.update(st, 1.0, perms=H.draw_perms(70 + upd, w.rows, w.num_epoch))], np.float32)
+        assert len(got) == len(want), (got, want)
+        if len(want) > 5:
+            stops += 1
+            assert got[5] == want[5], "early-stop index differs from the reference's"
+        np.testing.assert_allclose(got[:5], want[:5], rtol=5e-4, atol=5e-6, equal_nan=True)
+        want_p, got_p = sess.get_params(), policy.params.cpu().numpy()
+        err = np.abs(got_p - want_p) / np.maximum(np.abs(want_p), w.learning_rate)
+        print(f"[tc] kl stop update {upd}: stats {got} max param err {err.max():.2e}")
+        assert err.max() <= 1e-3
+    assert stops >= 1, "the case was meant to trip the KL stop"
