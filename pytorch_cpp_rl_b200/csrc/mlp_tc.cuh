@@ -38,6 +38,7 @@ struct Geo
 {
     static_assert(R % 8 == 0 && R >= 8 && R <= 64, "tile rows");
     static constexpr int CH = R / 2;                       // columns (tile rows) per thread in the epilogues
+    static constexpr int kN = (R + 15) / 16 * 16;          // N of the instructions whose columns are the tile's rows (M = 128: N % 16 == 0)
     static constexpr int LD = R + 4;                       // row stride of the fp32 feature-major h2 tile (heads)
     static constexpr uint32_t kLboB = (R / 8) * 128 + 16;  // row-major operands [n = row][k = feature]: 16 B off a multiple of
                                                            // 128 -> the per-feature 4-byte stores of a warp are conflict-free

@@ -44,6 +44,7 @@ struct SmemPlan
         misc, total;
     // tensor-core variant: hi / lo operand planes (see mlp_tc.cuh); offsets in floats like the others
     int xb, xf, hb[2], hf[2];
+    int stage; // tensor-core variant: scratch for the heads' partial sums (P3) and the staged dW1 / dW2 of the publish
     int img_base; // first float of the GLOBAL image that the shared-memory image holds (tensor-core variant: its tail)
     int g_base;   // first gradient index the shared-memory accumulator `gsm` holds (tensor-core variant: po.wv)
 };
@@ -72,7 +73,7 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.img = o, o += img_floats - p.img_base;
     p.gsm = o, o += ((Pstride + 3) & ~3) - p.g_base;
     p.g2 = o, o += g2_floats(Ap); // second accumulators of the gradients that several threads share (see G2 below)
-    p.xb = p.xf = p.hb[0] = p.hb[1] = p.hf[0] = p.hf[1] = 0;
+    p.xb = p.xf = p.hb[0] = p.hb[1] = p.hf[0] = p.hf[1] = p.stage = 0;
     if (tc)
     {
         // operand planes, hi then lo each (bytes / 4); the row-major planes read one non-existent 8-row group past
@@ -83,6 +84,13 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
         p.xf = o, o += 2 * plane_xf / 4;
         for (int t = 0; t < 2; ++t)
             p.hf[t] = o, o += 2 * plane_f / 4;
+        // the row-major operand planes are idle when the scratch is in use (between the layer-2 chain and P5b; after
+        // the last tile's data-gradient chain) and host it when they are large enough (56- and 64-row tiles)
+        const int stage_need = kTcW1Stage + 2 * kHid * 68;
+        if (4 * plane_b / 4 >= stage_need)
+            p.stage = p.hb[0];
+        else
+            p.stage = o, o += stage_need;
         p.x = p.h1[0] = p.h1[1] = 0; // (fp32 x / h1 tiles are not kept)
     }
     else
@@ -558,12 +566,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         __syncthreads();
     };
 
-#define CPPRL_MARK(slot)                                                              \
-    do                                                                                \
-    {                                                                                 \
-        if (a.dbg_clocks && tid == 0 && step == a.dbg_step)                           \
-            a.dbg_clocks[blockIdx.x * 32 + (slot)] = clock64();                       \
-    } while (0)
+// Phase marks: one opaque predicated store of %clock64 (thread 0 of a CTA, the step being looked at).  A C++ "if (tid == 0
+// && ...)" here lets the compiler thread the known tid into the branches that follow, and thread 0 then runs the next phase
+// diverged from the rest of its warp -- which showed up as a phase twice as long as it is in an unmarked run.
+#define CPPRL_MARK(slot)                                                                                       \
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 t;\n\tsetp.ne.u32 p, %0, 0;\n\tmov.u64 t, %%clock64;\n\t"   \
+                 "@p st.global.u64 [%1], t;\n\t}" ::"r"(static_cast<unsigned>(a.dbg_clocks && tid == 0 && step == a.dbg_step)), \
+                 "l"(a.dbg_clocks + blockIdx.x * 32 + (slot))                                                  \
+                 : "memory")
     unsigned int *const gbar = a.barrier + 8 * a.barrier_sel;
     if (blockIdx.x == 0 && tid == 0)
         a.barrier[8 * (a.barrier_sel ^ 1)] = 0u; // the NEXT launch's counter (stream order: the previous launch is complete)
@@ -729,7 +739,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 if (tid == 0)
                 {
                     mtc::fence_after();
-                    const uint32_t d = tm + mtc::kColA, ah = tm + mtc::kColX, al = ah + 32, id = mtc::idesc_n(64);
+                    const uint32_t d = tm + mtc::kColA, ah = tm + mtc::kColX, al = ah + 32, id = mtc::idesc_n(GeoT::kN);
                     switch (Dp / 8) // (k-steps are compile-time constants: every descriptor is base + immediate)
                     {
                     case 1: mtc::issue_3xtf32<0, 1, GeoT::kLboB>(d, ah, al, xb_hi, xb_lo, id); break;
@@ -780,7 +790,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     mtc::fence_after();
                     const uint32_t b_hi = smem_u32(smem + sp.hb[t]);
                     mtc::issue_3xtf32<0, kHid / 8, GeoT::kLboB>(tm + mtc::kColA + 64 * t, tm + mtc::kColW, tm + mtc::kColW + 64, b_hi,
-                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(64));
+                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(GeoT::kN));
                     mtc::commit(&tcbar[1]);
                 }
                 // W2^T (this lane's row of the transposed image) for the data gradient: in flight during the chain and E2
@@ -847,7 +857,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 // while the head rows stream past as broadcast 16-byte loads (60 shared-memory loads per thread for 7
                 // outputs instead of 80 per output); the four quarters meet through shared memory -- the layer-2 operand
                 // planes, idle between the layer-2 chain and P5b.
-                float *PART = smem + sp.hb[0]; // [kq][A + 1][64]
+                float *PART = smem + sp.stage; // [kq][A + 1][64]: at most 4 x 17 x 64 floats
                 const int r = (warp & 1) * 32 + lane, kq = warp >> 1;
                 if (r < R)
                 {
@@ -1169,7 +1179,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     mtc::fence_after();
                     const uint32_t b_hi = smem_u32(smem + sp.hb[t]);
                     mtc::issue_3xtf32<0, kHid / 8, GeoT::kLboB>(tm + mtc::kColG + 64 * t, tm + mtc::kColW, tm + mtc::kColW + 64, b_hi,
-                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(64));
+                                                                b_hi + GeoT::kPlaneB, mtc::idesc_n(GeoT::kN));
                     mtc::commit(&tcbar[2]);
                 }
                 p5a();
@@ -1294,12 +1304,12 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     (void)part;
                     // dW2 [lane][64] staged with a row stride of 68 floats (conflict-free 16-byte stores; a lane's 128 bytes
                     // written straight to global memory would touch 32 different lines per warp instruction)
-                    float *w2s = smem + sp.hb[0] + kTcW1Stage + F * 68 + 32 * ch;
+                    float *w2s = smem + sp.stage + kTcW1Stage + F * 68 + 32 * ch;
 #pragma unroll
                     for (int i = 0; i < 8; ++i)
                         *reinterpret_cast<float4 *>(w2s + 4 * i) =
                             make_float4(acc_w2[TC ? 4 * i : 0], acc_w2[TC ? 4 * i + 1 : 0], acc_w2[TC ? 4 * i + 2 : 0], acc_w2[TC ? 4 * i + 3 : 0]);
-                    float *w1s = smem + sp.hb[0];
+                    float *w1s = smem + sp.stage;
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
                         if (16 * ch + i < D)
@@ -1379,7 +1389,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                     __stcg(part + (tF ? a.po.b2[1] : a.po.b2[0]) + jF, acc_b2 + G2_B2[F]);
                     __stcg(part + (tF ? a.po.b1[1] : a.po.b1[0]) + jF, acc_b1 + G2_B2[2 * kHid + F]);
                 }
-                const float *w1s = smem + sp.hb[0], *w2s = w1s + kTcW1Stage;
+                const float *w1s = smem + sp.stage, *w2s = w1s + kTcW1Stage;
                 for (int e = tid; e < 2 * kHid * kHid / 4; e += kUpdThreads) // consecutive threads, consecutive 16-byte words
                 {
                     const int t = e >> 10, rem = e & 1023, j = rem >> 4, c4 = rem & 15;
@@ -1691,8 +1701,10 @@ int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s
         return fail(CPPRL_B200_EINVAL, "mlp_update: image layout does not match the kernel variant");
     if (tc)
     {
-        if ((R != kTcRows && R != kTcRowsWide) || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
+        if ((R != kTcRows && R != kTcRowsWide && R != kTcRowsSmall) || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
             return fail(CPPRL_B200_EINVAL, "mlp_update: unsupported tensor-core plan");
+        if (R == kTcRowsSmall)
+            return launch_update<kTcRowsSmall, true>(args, grid, smem, s);
         return R == kTcRows ? launch_update<kTcRows, true>(args, grid, smem, s) : launch_update<kTcRowsWide, true>(args, grid, smem, s);
     }
     if (R == 64)

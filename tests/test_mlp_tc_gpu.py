@@ -1,5 +1,5 @@
-"""The tensor-core variant of the fused MlpBase update (csrc/mlp_tc.cuh: tcgen05 kind::tf32 as 3xTF32, minibatches of
-more than 32 rows per SM) against the compiled reference and against the fp32 CUDA-core variant of the same kernel
+"""The tensor-core variant of the fused MlpBase update (csrc/mlp_tc.cuh: tcgen05 kind::tf32 as 3xTF32; 56- or 64-row tiles
+for minibatches of more than 32 rows per SM, 16-row tiles for minibatches of at most 16 rows per SM) against the compiled reference and against the fp32 CUDA-core variant of the same kernel
 (CPPRL_B200_MLP_TC=0), over the shapes the variant has to get right: observation widths around the 8-column k-step,
 both heads, minibatches that end in a ragged tile, several tiles per CTA, PPO with several optimiser steps and A2C."""
 import os
@@ -24,11 +24,15 @@ def test_variant_selection():
     assert _variant(8192, 17, 6) == 56         # cfg3's minibatch
     assert _variant(20480, 8, 4) == 56         # cfg2
     assert _variant(9000, 17, 6) == 64         # fewer waves with 64-row tiles
-    assert _variant(256, 8, 4) == 0            # cfg1: a minibatch that does not fill the chip
+    assert _variant(256, 8, 4) == 16           # cfg1: a minibatch that does not fill the chip -> 16 tiles of 16 rows
+    assert _variant(16 * 148, 8, 4) == 16      # one 16-row tile on every SM
+    assert _variant(16 * 148 + 1, 8, 4) == 0   # 32-row CUDA-core tiles up to 32 rows per SM
+    assert _variant(256, 33, 4) == 0
     assert _variant(8192, 33, 6) == 0          # more than 32 observation columns: CUDA-core variant
     os.environ["CPPRL_B200_MLP_TC"] = "0"
     try:
         assert _variant(8192, 17, 6) == 0
+        assert _variant(256, 8, 4) == 0
     finally:
         del os.environ["CPPRL_B200_MLP_TC"]
 
@@ -50,7 +54,7 @@ def _update_once(w, r, params, normalizer, perms, n_updates=1):
 
 
 CASES = {
-    # name: (base config, overrides): minibatch rows > 32 * 148 = 4736 in every case
+    # name: (base config, overrides): minibatch rows > 32 * 148 = 4736 (56- / 64-row tiles) or <= 16 * 148 = 2368 (16-row tiles)
     "normal_obs17_ragged": ("cfg3", dict(T=13, N=800, num_epoch=2, num_mini_batch=2)),        # 5200 rows: 92 full tiles + 48 rows
     "normal_obs3": ("cfg3", dict(T=8, N=640, obs_shape=(3,), num_epoch=1, num_mini_batch=1)),   # one k-step, 5 padded columns
     "normal_obs32_act1": ("cfg3", dict(T=8, N=640, obs_shape=(32,), num_actions=1, num_epoch=1, num_mini_batch=1)),
@@ -62,6 +66,12 @@ CASES = {
     "wide_tile_normal": ("cfg3", dict(T=9, N=1000, num_epoch=2, num_mini_batch=1)),
     "wide_tile_categorical_ragged": ("cfg1", dict(T=7, N=1300, obs_shape=(8,), num_actions=4, num_epoch=1, num_mini_batch=1,
                                                   storage_hidden=1)),                            # 9100 rows = 142 tiles + 12 rows
+    "small_tile_cfg1": ("cfg1", dict()),                                                         # 256-row minibatches: 16 tiles
+    "small_tile_normal_ragged": ("cfg3", dict(T=7, N=30, num_epoch=2, num_mini_batch=2)),        # 105 rows: 6 tiles + 9 rows
+    "small_tile_act16_every_sm": ("cfg1", dict(T=16, N=148, obs_shape=(9,), num_actions=16, num_epoch=1, num_mini_batch=1,
+                                               storage_hidden=1)),                               # 2368 rows = 148 full tiles
+    "small_tile_obs32_act1": ("cfg3", dict(T=5, N=9, obs_shape=(32,), num_actions=1, num_epoch=2, num_mini_batch=1)),  # 45 rows
+    "small_tile_a2c": ("cfg2", dict(T=5, N=64)),
     "no_normaliser": ("cfg3", dict(T=8, N=640, normalize_obs=False, num_epoch=1, num_mini_batch=1)),
 }
 
