@@ -390,12 +390,19 @@ void cpprl_b200_kernel_time_enable(int on);
  * row-major device operands A [M][K] (variant bit 0: given transposed, [K][M]) and B [K][N]; variant bits 4..: tile
  * columns (32, 64, 128).  M, N, K multiples of 4. */
 int cpprl_b200_debug_tc_gemm(int variant, const float *d_a, const float *d_b, float *d_c, int M, int N, int K, void *stream);
+/* Test hook for the permutation stream behind cpprl_b200_ppo_update_rng (csrc/host_rng.cu): `updates` consecutive updates
+ * on ONE stream with a ring of 2 * count permutations; update u takes used[u] <= count permutations (fewer = an early
+ * stop) and hands the state after its last one to the next; reseed_before[u] != 0 (may be NULL) first replaces the state
+ * with reseed_state.  out receives the sum(used) permutations in order, *restarts how many updates had to restart the
+ * stream instead of continuing with the permutations drawn ahead.  Host code only. */
+int cpprl_b200_debug_perm_stream(void *rng_state, const void *reseed_state, int64_t n, int count, int updates, const int *used,
+                                 const int *reseed_before, int64_t *out, long long *restarts);
 /* Profiling hook: when d_buffer (device, grid*32 int64) is non-NULL, thread 0 of every CTA of the fused PPO
  * update kernel stores clock64() at its phase boundaries during minibatch `step` of each launch. */
 void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step);
 /* Which variant of the fused MlpBase update a minibatch of this shape trains on: > 0 = tensor cores (tcgen05 kind::tf32 as
- * 3xTF32, minibatches of more than 32 rows per SM with at most 32 observation columns; the value is the tile's row
- * count, 56 or 64), 0 = fp32 CUDA cores.
+ * 3xTF32, at most 32 observation columns: minibatches of more than 32 rows per SM on 56- or 64-row tiles, minibatches of
+ * at most 16 rows per SM on 16-row tiles; the value is the tile's row count), 0 = fp32 CUDA cores.
  * CPPRL_B200_MLP_TC=0 in the environment forces 0 (A/B runs). */
 int cpprl_b200_mlp_update_variant(int64_t minibatch_rows, int64_t obs_dim, int64_t num_actions);
 

@@ -135,6 +135,8 @@ SIGNATURES = {
     "cpprl_b200_kernel_time_enable": (None, [C.c_int]),
     "cpprl_b200_debug_phase_clocks": (None, [C.c_void_p, C.c_int]),
     "cpprl_b200_mlp_update_variant": (C.c_int, [C.c_int64, C.c_int64, C.c_int64]),
+    "cpprl_b200_debug_perm_stream": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]),
     "cpprl_b200_debug_tc_gemm": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
 }
 

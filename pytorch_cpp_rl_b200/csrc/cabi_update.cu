@@ -1127,8 +1127,9 @@ extern "C" int cpprl_b200_ppo_update(cpprl_b200_ppo *h, const cpprl_b200_policy 
 // PPO::update with the permutations the reference itself would draw (ppo.cpp:63-84 builds one generator per epoch,
 // each drawing torch::randperm from the default CPU generator): `rng_state` is that generator's state
 // (at::CPUGeneratorImpl::get_state, cpprl_b200_rng_state_bytes() bytes) on entry and what it must be set to on return.
-// The epochs' permutations are drawn by background threads while the device runs (host_rng.cu); after a KL early stop
-// the state is the one after the last epoch the reference would have started.
+// The epochs' permutations are drawn by background threads while the device runs (host_rng.cu), and the next update's
+// are drawn ahead: they are used when that update arrives with the state this one returned.  After a KL early stop the
+// state is the one after the last epoch the reference would have started.
 extern "C" int cpprl_b200_ppo_update_rng(cpprl_b200_ppo *h, const cpprl_b200_policy *policy, const cpprl_b200_rollout *rollout,
                                          const cpprl_b200_ppo_options *opt, void *rng_state, cpprl_b200_ppo_stats *stats,
                                          void *stream)
@@ -1145,27 +1146,27 @@ extern "C" int cpprl_b200_ppo_update_rng(cpprl_b200_ppo *h, const cpprl_b200_pol
     };
     if (!PermStream::supported(n))
         return bail(fail(CPPRL_B200_EUNSUPPORTED, "ppo_update_rng: rollout too large for randperm's 32-bit branch"));
-    if (static_cast<size_t>(n) * epochs > h->rng_perms_cap)
+    // a ring of 2 * epochs permutations: this update's and, drawn ahead by the stream's threads, the next one's
+    const size_t ring_elems = 2 * static_cast<size_t>(n) * epochs;
+    if (ring_elems != h->rng_perms_cap)
     {
-        delete h->perm_stream;
+        delete h->perm_stream; // (stops its threads before the block they write goes away)
         h->perm_stream = nullptr;
         if (h->h_rng_perms)
             cudaFreeHost(h->h_rng_perms);
         h->h_rng_perms = nullptr, h->rng_perms_cap = 0;
-        if (int rc = check_cuda(cudaMallocHost(&h->h_rng_perms, static_cast<size_t>(n) * epochs * sizeof(int64_t)), "cudaMallocHost(perms)"))
+        if (int rc = check_cuda(cudaMallocHost(&h->h_rng_perms, ring_elems * sizeof(int64_t)), "cudaMallocHost(perms)"))
             return bail(rc);
-        h->rng_perms_cap = static_cast<size_t>(n) * epochs;
+        h->rng_perms_cap = ring_elems;
     }
     if (!h->perm_stream)
         h->perm_stream = new PermStream();
-    std::vector<int64_t *> outs(static_cast<size_t>(epochs));
-    for (int e = 0; e < epochs; ++e)
-        outs[e] = h->h_rng_perms + static_cast<int64_t>(e) * n;
-    // the device buffers of the previous update may still be read by its last kernels: the H2D below waits on the
-    // `consumed` events; the PINNED block is rewritten by the threads right away, so its last copies must be done
+    // Ring slots are rewritten only with permutations two updates ahead of the one that last read them, and that update's
+    // H2D copies were complete when its ppo_end returned; the device buffers of the previous update may still be read by
+    // its last kernels: the H2D below waits on the `consumed` events.
     if (int rc = check_cuda(cudaStreamSynchronize(h->copy_stream), "cudaStreamSynchronize(copy)"))
         return bail(rc);
-    if (int rc = h->perm_stream->start(rng_state, n, epochs, outs.data(), 0))
+    if (int rc = h->perm_stream->start(rng_state, n, epochs, h->h_rng_perms, 2 * epochs, 0))
         return bail(rc);
     const bool can_stop = static_cast<double>(opt->kl_target) * 1.5 < 1e3; // a mean log-prob difference cannot reach that
     int drawn = 0, rc = 0;
@@ -1178,15 +1179,16 @@ extern "C" int cpprl_b200_ppo_update_rng(cpprl_b200_ppo *h, const cpprl_b200_pol
             if (rc || stopped)
                 break; // the reference leaves its epoch loop here: no further randperm is drawn (ppo.cpp:100-104)
         }
-        h->perm_stream->wait(e);
+        const int64_t *perm = h->perm_stream->wait(e);
         drawn = e + 1;
-        rc = ppo_epoch_host(h, outs[e], n, true);
+        rc = ppo_epoch_host(h, perm, n, true);
     }
     if (drawn > 0)
         h->perm_stream->state_after(drawn - 1, rng_state);
     if (rc == 0)
         rc = cpprl_b200_ppo_end(h, stats); // synchronises: every H2D of the pinned block has finished
-    h->perm_stream->join();
+    else
+        cudaStreamSynchronize(h->copy_stream);
     if (rc)
         return bail(rc);
     return 0;

@@ -11,7 +11,10 @@
 // epochs' swap walks in parallel (the walk of epoch e needs only its own draws), and the caller picks the
 // permutations up in order while the GPU runs the previous epoch.  The generator state goes in and out as the
 // 5056-byte blob of at::CPUGeneratorImpl::get_state / set_state, so torch's generator ends where torch::randperm
-// would have left it.  Bit-exactness against torch.randperm is pinned by tests/test_host_rng_cpu.py.
+// would have left it.  The threads also draw AHEAD of the update, into the second half of a ring: when the next update
+// arrives with the state this one returned (nobody drew from the generator in between), its first permutation is
+// already there instead of 1.3 ms away (host_rng.h).  Bit-exactness against torch.randperm is pinned by
+// tests/test_host_rng_cpu.py.
 //
 // Host code only (no kernel here); it lives in the C-ABI library because the reference's host language is C++.
 #include <atomic>
@@ -142,33 +145,60 @@ void walk(const uint32_t *raw, int64_t n, int64_t *out, std::vector<uint32_t> &i
 }
 } // namespace
 
-// ---- PermStream: `count` permutations of n ids, produced in order by background threads ------------------------------
+// ---- PermStream: a rolling stream of permutations of n ids, produced in order by background threads --------------------
+// Permutations carry a global index g = 0, 1, ... from the state the stream was (re)started with; g lives in ring slot
+// g % slots.  The producer may run up to `slots` permutations past `base`, the first permutation of the current update.
 struct PermStream::Impl
 {
     int64_t n = 0;
-    int count = 0;
-    std::vector<int64_t *> out;
-    std::vector<std::vector<uint32_t>> raw;              // raw draws per permutation
-    std::vector<std::vector<unsigned char>> state_after; // generator state after permutation e
-    std::vector<int> raw_ready, perm_ready;
+    int count = 0, slots = 0, max_threads = 0;
+    int64_t *ring = nullptr;
+    long long base = 0;     // global index of the current update's first permutation
+    long long produced = 0; // raw draws exist for [.., produced)
+    long long next_job = 0; // next global index a worker walks
+    std::vector<std::vector<uint32_t>> raw;              // per slot: raw draws of its permutation
+    std::vector<std::vector<unsigned char>> state_after; // per slot: generator state after its permutation
+    std::vector<long long> raw_g, perm_g;                // per slot: which g its draws / its finished permutation belong to
+                                                         // (-1: none yet, -2: being written)
+    bool quit = false;
+    long long restarts = 0;
     std::mutex mu;
     std::condition_variable cv;
     std::vector<std::thread> threads;
     Mt19937 mt;
     std::vector<unsigned char> blob;
-    std::atomic<int> next_job{0};
 
     void producer()
     {
-        for (int e = 0; e < count; ++e)
+        for (;;)
         {
-            raw[e].resize(static_cast<size_t>(n > 0 ? n - 1 : 0));
-            mt.fill(raw[e].data(), n > 0 ? n - 1 : 0);
-            state_after[e] = blob;
-            store_state(state_after[e].data(), mt);
+            long long g;
+            int s;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] {
+                    if (quit)
+                        return true;
+                    if (produced >= base + slots)
+                        return false;
+                    // the slot's previous permutation (never asked for after an early stop, perhaps) must have left the walk
+                    const int sl = static_cast<int>(produced % slots);
+                    return produced < slots || perm_g[sl] == produced - slots;
+                });
+                if (quit)
+                    return;
+                g = produced;
+                s = static_cast<int>(g % slots);
+                raw_g[s] = -2;
+            }
+            raw[s].resize(static_cast<size_t>(n > 0 ? n - 1 : 0));
+            mt.fill(raw[s].data(), n > 0 ? n - 1 : 0);
+            state_after[s] = blob;
+            store_state(state_after[s].data(), mt);
             {
                 std::lock_guard<std::mutex> lk(mu);
-                raw_ready[e] = 1;
+                raw_g[s] = g;
+                produced = g + 1;
             }
             cv.notify_all();
         }
@@ -178,28 +208,42 @@ struct PermStream::Impl
         std::vector<uint32_t> ids;
         for (;;)
         {
-            const int e = next_job.fetch_add(1);
-            if (e >= count)
-                return;
+            long long g;
             {
                 std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return raw_ready[e] != 0; });
+                cv.wait(lk, [&] { return quit || next_job < produced; });
+                if (quit)
+                    return;
+                g = next_job++;
             }
-            walk(raw[e].data(), n, out[e], ids);
-            std::vector<uint32_t>().swap(raw[e]);
+            const int s = static_cast<int>(g % slots);
+            walk(raw[s].data(), n, ring + static_cast<int64_t>(s) * n, ids);
             {
                 std::lock_guard<std::mutex> lk(mu);
-                perm_ready[e] = 1;
+                perm_g[s] = g;
             }
             cv.notify_all();
         }
+    }
+    void stop()
+    {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            quit = true;
+        }
+        cv.notify_all();
+        for (auto &t : threads)
+            if (t.joinable())
+                t.join();
+        threads.clear();
+        quit = false;
     }
 };
 
 PermStream::PermStream() : impl_(new Impl) {}
 PermStream::~PermStream()
 {
-    join();
+    impl_->stop();
     delete impl_;
 }
 
@@ -209,23 +253,42 @@ bool PermStream::supported(int64_t n)
     return n >= 0 && n < static_cast<int64_t>(0xffffffffu / 20);
 }
 
-int PermStream::start(const void *rng_state, int64_t n, int count, int64_t *const *out, int max_threads)
+int PermStream::start(const void *rng_state, int64_t n, int count, int64_t *ring, int slots, int max_threads)
 {
-    join();
     Impl &s = *impl_;
-    if (!supported(n) || count < 0)
+    if (count < 0 || slots < count || (count > 0 && n > 0 && !ring))
+        return fail(CPPRL_B200_EINVAL, "host_randperm: bad ring");
+    if (!supported(n))
         return fail(CPPRL_B200_EUNSUPPORTED, "host_randperm: n outside the range of randperm's 32-bit branch");
-    s.blob.assign(static_cast<const unsigned char *>(rng_state), static_cast<const unsigned char *>(rng_state) + kStateBytes);
-    if (!load_state(rng_state, s.mt))
+    if (!s.threads.empty() && n == s.n && count == s.count && slots == s.slots && ring == s.ring && max_threads == s.max_threads)
+    {
+        // does the incoming state continue the stream?  It does when it is the state recorded after one of the permutations
+        // of the window the ring still holds (the full update: base + count - 1; an early stop: an earlier one)
+        std::lock_guard<std::mutex> lk(s.mu);
+        for (int sl = 0; sl < slots; ++sl)
+        {
+            const long long g = s.raw_g[sl];
+            if (g >= s.base && std::memcmp(s.state_after[sl].data(), rng_state, kStateBytes) == 0)
+            {
+                s.base = g + 1;
+                s.cv.notify_all();
+                return 0;
+            }
+        }
+    }
+    s.stop();
+    Mt19937 mt;
+    if (!load_state(rng_state, mt))
         return fail(CPPRL_B200_EINVAL, "host_randperm: not a seeded at::CPUGeneratorImpl state (5056 bytes expected)");
-    s.n = n;
-    s.count = count;
-    s.out.assign(out, out + count);
-    s.raw.assign(count, {});
-    s.state_after.assign(count, {});
-    s.raw_ready.assign(count, 0);
-    s.perm_ready.assign(count, 0);
-    s.next_job = 0;
+    s.mt = mt;
+    s.blob.assign(static_cast<const unsigned char *>(rng_state), static_cast<const unsigned char *>(rng_state) + kStateBytes);
+    s.n = n, s.count = count, s.slots = slots, s.ring = ring, s.max_threads = max_threads;
+    s.base = s.produced = s.next_job = 0;
+    s.raw.assign(static_cast<size_t>(slots), {});
+    s.state_after.assign(static_cast<size_t>(slots), {});
+    s.raw_g.assign(static_cast<size_t>(slots), -1);
+    s.perm_g.assign(static_cast<size_t>(slots), -1);
+    ++s.restarts;
     if (count == 0)
         return 0;
     int hw = static_cast<int>(std::thread::hardware_concurrency());
@@ -241,30 +304,28 @@ int PermStream::start(const void *rng_state, int64_t n, int count, int64_t *cons
     return 0;
 }
 
-void PermStream::wait(int e)
+const int64_t *PermStream::wait(int e)
 {
     Impl &s = *impl_;
+    const long long g = s.base + e;
+    const int sl = static_cast<int>(g % s.slots);
     std::unique_lock<std::mutex> lk(s.mu);
-    s.cv.wait(lk, [&] { return s.perm_ready[e] != 0; });
+    s.cv.wait(lk, [&] { return s.perm_g[sl] == g; });
+    return s.ring + static_cast<int64_t>(sl) * s.n;
 }
 
 void PermStream::state_after(int e, void *rng_state_out)
 {
     Impl &s = *impl_;
-    {
-        std::unique_lock<std::mutex> lk(s.mu);
-        s.cv.wait(lk, [&] { return s.raw_ready[e] != 0; });
-    }
-    std::memcpy(rng_state_out, s.state_after[e].data(), kStateBytes);
+    const long long g = s.base + e;
+    const int sl = static_cast<int>(g % s.slots);
+    std::unique_lock<std::mutex> lk(s.mu);
+    s.cv.wait(lk, [&] { return s.raw_g[sl] == g; });
+    std::memcpy(rng_state_out, s.state_after[sl].data(), kStateBytes);
 }
 
-void PermStream::join()
-{
-    for (auto &t : impl_->threads)
-        if (t.joinable())
-            t.join();
-    impl_->threads.clear();
-}
+void PermStream::stop() { impl_->stop(); }
+long long PermStream::restarts() const { return impl_->restarts; }
 } // namespace cpprl_b200
 
 using namespace cpprl_b200;
@@ -277,15 +338,44 @@ extern "C" int cpprl_b200_host_randperm(void *rng_state, int64_t n, int64_t coun
         return fail(CPPRL_B200_EINVAL, "host_randperm: bad arguments");
     if (count == 0)
         return 0;
-    std::vector<int64_t *> outs(static_cast<size_t>(count));
-    for (int64_t e = 0; e < count; ++e)
-        outs[e] = out + e * n;
-    PermStream ps;
-    if (int rc = ps.start(rng_state, n, static_cast<int>(count), outs.data(), max_threads))
+    PermStream ps; // the caller's buffer is the ring: `count` slots, nothing drawn ahead
+    if (int rc = ps.start(rng_state, n, static_cast<int>(count), out, static_cast<int>(count), max_threads))
         return rc;
     for (int e = 0; e < count; ++e)
         ps.wait(e);
     ps.state_after(static_cast<int>(count) - 1, rng_state);
-    ps.join();
+    return 0;
+}
+
+// Test hook (tests/test_host_rng_cpu.py): `updates` consecutive updates on ONE stream with a ring of 2 * count slots, the
+// way cpprl_b200_ppo_update_rng drives it; update u takes used[u] <= count permutations (an early stop) and hands the state
+// after its last one to the next.  reseed_before[u] != 0 replaces the state with `reseed_state` before update u (someone
+// else drew from the generator).  out receives the sum(used) permutations in order; *restarts the number of stream restarts.
+extern "C" int cpprl_b200_debug_perm_stream(void *rng_state, const void *reseed_state, int64_t n, int count, int updates,
+                                            const int *used, const int *reseed_before, int64_t *out, long long *restarts)
+{
+    if (!rng_state || !used || !out || n < 0 || count <= 0 || updates < 0)
+        return fail(CPPRL_B200_EINVAL, "debug_perm_stream: bad arguments");
+    std::vector<int64_t> ring(static_cast<size_t>(2 * count) * static_cast<size_t>(n));
+    PermStream ps;
+    int64_t written = 0;
+    for (int u = 0; u < updates; ++u)
+    {
+        if (reseed_before && reseed_before[u] && reseed_state)
+            std::memcpy(rng_state, reseed_state, kStateBytes);
+        if (used[u] < 0 || used[u] > count)
+            return fail(CPPRL_B200_EINVAL, "debug_perm_stream: used[u] outside [0, count]");
+        if (int rc = ps.start(rng_state, n, count, ring.data(), 2 * count, 0))
+            return rc;
+        for (int e = 0; e < used[u]; ++e)
+        {
+            std::memcpy(out + written * n, ps.wait(e), static_cast<size_t>(n) * sizeof(int64_t));
+            ++written;
+        }
+        if (used[u] > 0)
+            ps.state_after(used[u] - 1, rng_state);
+    }
+    if (restarts)
+        *restarts = ps.restarts();
     return 0;
 }

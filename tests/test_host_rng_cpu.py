@@ -64,6 +64,61 @@ def test_empty_and_errors():
     assert lib.cpprl_b200_host_randperm(C.c_void_p(bad.data_ptr()), 8, 1, C.c_void_p(dummy.data_ptr()), 0) == cabi.EINVAL
 
 
+def _stream(seed, n, count, used, reseed_before=None, reseed_seed=None):
+    """Consecutive updates on one permutation stream (the way cpprl_b200_ppo_update_rng drives it)."""
+    lib = cabi.load()
+    torch.manual_seed(seed)
+    state = torch.get_rng_state()
+    reseed_state = None
+    if reseed_seed is not None:
+        torch.manual_seed(reseed_seed)
+        reseed_state = torch.get_rng_state()
+    used_a = np.asarray(used, np.int32)
+    flags = np.asarray(reseed_before if reseed_before is not None else [0] * len(used), np.int32)
+    out = torch.empty(int(used_a.sum()), n, dtype=torch.int64)
+    restarts = C.c_longlong(0)
+    rc = lib.cpprl_b200_debug_perm_stream(C.c_void_p(state.data_ptr()), C.c_void_p(reseed_state.data_ptr()) if reseed_state is not None else None,
+                                          n, count, len(used), C.c_void_p(used_a.ctypes.data), C.c_void_p(flags.ctypes.data),
+                                          C.c_void_p(out.data_ptr()), C.byref(restarts))
+    assert rc == 0, cabi.last_error()
+    return out, state, restarts.value
+
+
+def test_stream_continues_across_updates():
+    # five full updates of four permutations each: the stream starts once, every later update finds its permutations
+    # already drawn ahead, and what comes out is torch's stream
+    seed, n, count = 21, 3001, 4
+    got, state, restarts = _stream(seed, n, count, [count] * 5)
+    torch.manual_seed(seed)
+    want = torch.stack([torch.randperm(n, dtype=torch.int64) for _ in range(5 * count)])
+    after_want = torch.rand(4)
+    assert torch.equal(got, want)
+    assert restarts == 1
+    torch.set_rng_state(state)
+    assert torch.equal(torch.rand(4), after_want), "state handed back after the last update differs from torch's"
+
+
+def test_stream_after_early_stops_and_foreign_draws():
+    # updates that stop early use fewer permutations: the next update continues from where the LAST USED one left the
+    # generator (the unused ones drawn ahead are the right ones for it); a state nobody recorded restarts the stream
+    seed, n, count = 5, 777, 5
+    used = [5, 2, 5, 0, 1, 5, 3]
+    got, _, restarts = _stream(seed, n, count, used)
+    torch.manual_seed(seed)
+    want = torch.stack([torch.randperm(n, dtype=torch.int64) for _ in range(sum(used))])
+    assert torch.equal(got, want)
+    assert restarts == 2, "only the first update and the one after the update that drew nothing restart the stream"
+    # someone reseeds the generator before the third update
+    used = [3, 3, 3, 3]
+    got, _, restarts = _stream(seed, n, 3, used, reseed_before=[0, 0, 1, 0], reseed_seed=99)
+    torch.manual_seed(seed)
+    a = [torch.randperm(n, dtype=torch.int64) for _ in range(6)]
+    torch.manual_seed(99)
+    b = [torch.randperm(n, dtype=torch.int64) for _ in range(6)]
+    assert torch.equal(got, torch.stack(a + b))
+    assert restarts == 2
+
+
 def test_faster_than_torch():
     n, count = 262144, 10
     torch.manual_seed(0)
