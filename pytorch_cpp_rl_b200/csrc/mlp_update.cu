@@ -41,7 +41,7 @@ constexpr int kRedMaxPer = (148 + kRedSplit - 1) / kRedSplit; // partials one wa
 struct SmemPlan
 {
     int img, gsm, g2, x, h1[2], h2[2], logit, dlogit, val, dval, ret, oldlp, adv, act, rowid, stat, xn, actn, scn, rowidn, actin, norm, red, own, sig,
-        misc, total;
+        misc, bc, total;
     // tensor-core variant: hi / lo operand planes (see mlp_tc.cuh); offsets in floats like the others
     int xb, xf, hb[2], hf[2];
     int stage; // tensor-core variant: scratch for the heads' partial sums (P3) and the staged dW1 / dW2 of the publish
@@ -59,6 +59,7 @@ struct SmemPlan
 __host__ __device__ inline int g2_floats(int Ap) { return Ap * kHid + kHid; }
 constexpr int kG2BiasFloats = 2 * kHid + 2 * 3 * kHid;
 constexpr int kTcW1Stage = 2 * kHid * mtc::kMaxDp; // floats reserved for the staged dW1 in front of the staged dW2 (tensor-core publish)
+constexpr int kBcSteps = 64;
 
 __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride, int Dp, int Ap, int per_cta, bool tc = false,
                                               int img_tail = 0, int g_tail = 0)
@@ -130,6 +131,7 @@ __host__ __device__ inline SmemPlan make_plan(int R, int img_floats, int Pstride
     p.own = o, o += 3 * per_cta;                       // this CTA's slice of params / Adam exp_avg / exp_avg_sq
     p.sig = o, o += 2 * Ap;                            // Normal head: {sigma^2, log sigma} per action
     p.misc = o, o += 48;
+    p.bc = o, o += 2 * kBcSteps; // Adam bias corrections of the launch's first kBcSteps optimiser steps
     p.total = o;
     return p;
 }
@@ -338,6 +340,20 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             OWN_M[i] = (real && a.opt == kOptAdam) ? a.opt_m[gi] : 0.f;
         }
     }
+    // Adam's bias corrections as host-style doubles (libtorch Adam: 1 - pow(beta, t), t = steps applied so far + 1) for
+    // every optimiser step of this launch, one step per lane of the last warp: a double pow is ~2 k cycles of dependent
+    // software arithmetic, which one thread used to spend between the arrival at the grid barrier and its poll in EVERY
+    // step -- 4 k cycles on the critical path of each (the barrier itself had long been satisfied)
+    float *BC = smem + sp.bc;
+    if (training && a.opt == kOptAdam && tid >= kUpdThreads - 32)
+        for (int i = tid - (kUpdThreads - 32); i < min(a.n_steps, kBcSteps); i += 32)
+        {
+            const double t = static_cast<double>(opt_step0 + i + 1);
+            const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t);
+            const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), t);
+            BC[2 * i] = static_cast<float>(a.lr / bc1);
+            BC[2 * i + 1] = static_cast<float>(sqrt(bc2));
+        }
     for (int i = blockIdx.x * kUpdThreads + tid; i < P; i += G * kUpdThreads)
         image_scatter(a, a.image, i, a.params[i]);
     if (tid == 0)
@@ -510,11 +526,69 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
+    int mark_step = -1; // the optimiser step in progress (the marks below are also used inside lambdas defined before the loop)
+// Phase marks: one opaque predicated store of %clock64 (thread 0 of a CTA, the step being looked at).  A C++ "if (tid == 0
+// && ...)" here lets the compiler thread the known tid into the branches that follow, and thread 0 then runs the next phase
+// diverged from the rest of its warp -- which showed up as a phase twice as long as it is in an unmarked run.
+#define CPPRL_MARK(slot)                                                                                       \
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 t;\n\tsetp.ne.u32 p, %0, 0;\n\tmov.u64 t, %%clock64;\n\t"   \
+                 "@p st.global.u64 [%1], t;\n\t}" ::"r"(static_cast<unsigned>(a.dbg_clocks && tid == 0 && mark_step == a.dbg_step)), \
+                 "l"(a.dbg_clocks + blockIdx.x * 32 + (slot))                                                  \
+                 : "memory")
     auto finalize_stage = [&](int nrows) { // nrows = valid rows of the item (row r is valid iff r < nrows)
         asm volatile("cp.async.wait_all;" ::: "memory");
         __syncthreads();
         const float clip = a.norm_mean ? NCLIP[0] : 0.f;
         const bool norm = a.norm_mean != nullptr;
+        if (TC)
+        {
+            // The observation tile as the two tensor-core operands it feeds, hi / lo planes each: row-major [row][column]
+            // (layer 1) and column-major [column][row] (dW1); rows past the tile are ZERO.  Thread = (row, group of four
+            // columns): four independent normalisations in flight (the exact division is a ~60-cycle dependent chain), one
+            // 16-byte store per row-major plane.
+            using GeoT = mtc::Geo<TC ? R : 8>;
+            unsigned char *xb = reinterpret_cast<unsigned char *>(smem + sp.xb), *xf = reinterpret_cast<unsigned char *>(smem + sp.xf);
+            for (int it = tid; it < (Dp >> 2) * R; it += kUpdThreads)
+            {
+                const int kg = it / R, r = it - kg * R; // R is a compile-time constant
+                float x[4], hi[4], lo[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    x[j] = XN[(4 * kg + j) * LD + r];
+                bool ok[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    ok[j] = 4 * kg + j < D && r < nrows;
+                if (norm)
+                {
+                    // (padding columns and rows divide 1 by the deviation instead of 0: a zero numerator sends the exact
+                    // division -- and with it the whole warp -- down its ~500-cycle slow path)
+                    const float4 mean = *reinterpret_cast<const float4 *>(NMEAN + 4 * kg), sd = *reinterpret_cast<const float4 *>(NSTD + 4 * kg);
+                    x[0] = (ok[0] ? x[0] - mean.x : 1.f) / sd.x, x[1] = (ok[1] ? x[1] - mean.y : 1.f) / sd.y;
+                    x[2] = (ok[2] ? x[2] - mean.z : 1.f) / sd.z, x[3] = (ok[3] ? x[3] - mean.w : 1.f) / sd.w;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        x[j] = fminf(fmaxf(x[j], -clip), clip);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    x[j] = ok[j] ? x[j] : 0.f;
+                    hi[j] = mtc::tf32_hi(x[j]), lo[j] = x[j] - hi[j];
+                }
+                const uint32_t ob = 16u * r + kg * GeoT::kLboB;
+                *reinterpret_cast<float4 *>(xb + ob) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<float4 *>(xb + GeoT::plane_xb(Dp) + ob) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+                const uint32_t of = 64u * kg + (r >> 2) * GeoT::kLboXF + (r & 3) * 4u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                {
+                    *reinterpret_cast<float *>(xf + of + 16u * j) = hi[j];
+                    *reinterpret_cast<float *>(xf + GeoT::kPlaneXF + of + 16u * j) = lo[j];
+                }
+            }
+        }
+        else
 #pragma unroll 4
         for (int e = tid; e < Dp * R; e += kUpdThreads)
         {
@@ -523,26 +597,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             float x = XN[k * LD + r];
             if (norm)
             {
-                x = (x - NMEAN[k]) / NSTD[k];
+                x = (ok ? x - NMEAN[k] : 1.f) / NSTD[k]; // (never 0 / s: see above)
                 x = fminf(fmaxf(x, -clip), clip);
             }
-            x = ok ? x : 0.f;
-            if (TC)
-            {
-                // the observation tile as the two tensor-core operands it feeds, hi / lo planes each:
-                // row-major [row][column] (layer 1) and column-major [column][row] (dW1); rows past the tile are ZERO
-                using GeoT = mtc::Geo<TC ? R : 8>;
-                const float hi = mtc::tf32_hi(x), lo = x - hi;
-                unsigned char *xb = reinterpret_cast<unsigned char *>(smem + sp.xb), *xf = reinterpret_cast<unsigned char *>(smem + sp.xf);
-                const uint32_t ob = 16u * r + (k >> 2) * GeoT::kLboB + (k & 3) * 4u;
-                const uint32_t of = 16u * k + (r >> 2) * GeoT::kLboXF + (r & 3) * 4u;
-                *reinterpret_cast<float *>(xb + ob) = hi;
-                *reinterpret_cast<float *>(xb + GeoT::plane_xb(Dp) + ob) = lo;
-                *reinterpret_cast<float *>(xf + of) = hi;
-                *reinterpret_cast<float *>(xf + GeoT::kPlaneXF + of) = lo;
-            }
-            else
-                X[k * LD + r] = x;
+            X[k * LD + r] = ok ? x : 0.f;
         }
         if (a.head == 1)
 #pragma unroll 2
@@ -566,14 +624,6 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         __syncthreads();
     };
 
-// Phase marks: one opaque predicated store of %clock64 (thread 0 of a CTA, the step being looked at).  A C++ "if (tid == 0
-// && ...)" here lets the compiler thread the known tid into the branches that follow, and thread 0 then runs the next phase
-// diverged from the rest of its warp -- which showed up as a phase twice as long as it is in an unmarked run.
-#define CPPRL_MARK(slot)                                                                                       \
-    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 t;\n\tsetp.ne.u32 p, %0, 0;\n\tmov.u64 t, %%clock64;\n\t"   \
-                 "@p st.global.u64 [%1], t;\n\t}" ::"r"(static_cast<unsigned>(a.dbg_clocks && tid == 0 && step == a.dbg_step)), \
-                 "l"(a.dbg_clocks + blockIdx.x * 32 + (slot))                                                  \
-                 : "memory")
     unsigned int *const gbar = a.barrier + 8 * a.barrier_sel;
     if (blockIdx.x == 0 && tid == 0)
         a.barrier[8 * (a.barrier_sel ^ 1)] = 0u; // the NEXT launch's counter (stream order: the previous launch is complete)
@@ -608,6 +658,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
 
     for (int step = 0; step < a.n_steps; ++step)
     {
+        mark_step = step;
         const int n_tiles = (rows_of(step) + R - 1) / R;
         const int n_act = min(n_tiles, G);
         const bool active = static_cast<int>(blockIdx.x) < n_act; // owns tiles of this minibatch, publishes a partial
@@ -1432,10 +1483,10 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         }
         CPPRL_MARK(10);
         grid_arrive(gbar);
-        if (tid == 0)
+        CPPRL_MARK(30);
+        if (tid == 0 && a.opt == kOptAdam && applied >= kBcSteps)
         {
-            // bias corrections as host-style doubles (libtorch Adam), t = steps applied so far + 1; computed while
-            // the barrier round trip is in flight
+            // (launches of more than kBcSteps optimiser steps: the later steps' corrections are formed here)
             const double t = static_cast<double>(opt_step0 + applied + 1);
             const double bc1 = 1.0 - pow(static_cast<double>(a.beta1), t);
             const double bc2 = 1.0 - pow(static_cast<double>(a.beta2), t);
@@ -1450,6 +1501,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
             finalize_stage(min(R, rows_of(step + 1) - static_cast<int>(blockIdx.x) * R));
             fin_ahead = true;
         }
+        CPPRL_MARK(31);
         bar_target += G;
         grid_wait(gbar, bar_target);
         CPPRL_MARK(11);
@@ -1613,7 +1665,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         }
         CPPRL_MARK(12);
         {
-            const float step_size = MISC[16], bc2_sqrt = MISC[17];
+            const float step_size = applied < kBcSteps ? BC[2 * applied] : MISC[16], bc2_sqrt = applied < kBcSteps ? BC[2 * applied + 1] : MISC[17];
             const float lr = static_cast<float>(a.lr);
             for (int i = tid; i < n_own; i += kUpdThreads)
             {

@@ -72,6 +72,8 @@ CASES = {
                                                storage_hidden=1)),                               # 2368 rows = 148 full tiles
     "small_tile_obs32_act1": ("cfg3", dict(T=5, N=9, obs_shape=(32,), num_actions=1, num_epoch=2, num_mini_batch=1)),  # 45 rows
     "small_tile_a2c": ("cfg2", dict(T=5, N=64)),
+    # 80 optimiser steps in one launch: beyond the table of bias corrections the kernel fills at launch (64 steps)
+    "small_tile_80_minibatches": ("cfg1", dict(T=80, N=8, num_epoch=1, num_mini_batch=80)),
     "no_normaliser": ("cfg3", dict(T=8, N=640, normalize_obs=False, num_epoch=1, num_mini_batch=1)),
 }
 

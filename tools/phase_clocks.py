@@ -57,6 +57,12 @@ if c[:, 20].any():
     for name, i0, i1 in seq:
         dd = c[:, i1] - c[:, i0]
         print(f"    {name:28s} {dd.min():8d} {int(np.median(dd)):8d} {dd.max():8d}")
+if c[:, 30].any():
+    print("  barrier 1 in detail:")
+    for name, i0, i1 in [("publish done -> arrived (CTA barrier + release)", 10, 30), ("next minibatch's first tile laid out", 30, 31),
+                         ("poll + CTA barrier", 31, 11)]:
+        dd = c[:, i1] - c[:, i0]
+        print(f"    {name:48s} {dd.min():8d} {int(np.median(dd)):8d} {dd.max():8d}")
 tot = c[:, 15] - c[:, 0]
 if world > 1:
     x = np.diff(c[:, 16:20], axis=1)
