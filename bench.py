@@ -420,17 +420,18 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
         "peak_source": f"nominal 148 SM x 128 FMA/clk x 2 x {sm_max:.0f} MHz; fp32 CUDA-core bound, neither hbm nor tensor "
                        "(see DESIGN.md); share of step = " + f"{upd_ms / total_ms:.2f}",
     }
-    mlp_tc = (w.base == "mlp" and lib.cpprl_b200_mlp_update_variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) > 0)
+    tc_rows = lib.cpprl_b200_mlp_update_variant(w.rows // max(1, w.num_mini_batch), w.obs_dim, w.num_actions) if w.base == "mlp" else 0
+    mlp_tc = tc_rows > 0
     if mlp_tc:
-        # large minibatches train on the tensor-core variant (tcgen05 kind::tf32 as 3xTF32, csrc/mlp_tc.cuh): three TF32
-        # MMAs per algorithmic product at half the bf16 rate -> this path's own ceiling is the measured bf16 peak / 6.
-        # What bounds the kernel is NOT the tensor pipe (ncu: 13 % active) but the chain of dependent stages of each of
+        # minibatches of more than 32 or at most 16 rows per SM train on the tensor-core variant (tcgen05 kind::tf32 as 3xTF32,
+        # csrc/mlp_tc.cuh): three TF32 MMAs per algorithmic product at half the bf16 rate -> this path's own ceiling is the
+        # measured bf16 peak / 6.  What bounds the kernel is NOT the tensor pipe (ncu: 13 % active) but the chain of dependent stages of each of
         # the update's sequential optimiser steps (two grid barriers per step): DESIGN.md section 4.
         pk = ROOT / "MEASURED_PEAKS.json"
         peaks = json.loads(pk.read_text()) if pk.exists() else {}
         tc_peak = peaks.get("bf16_tflops_sustained") or peaks.get("bf16_tflops") or 2250.0
         roofline.update({
-            "kernel": "mlp_update_kernel<56 or 64 rows, tensor cores> (tcgen05 3xTF32 towers + CUDA-core heads, loss, reduction, Adam)",
+            "kernel": f"mlp_update_kernel<{tc_rows}-row tiles, tensor cores> (tcgen05 3xTF32 towers + CUDA-core heads, loss, reduction, Adam)",
             "bound": "tensor", "peak": tc_peak, "frac": achieved / tc_peak,
             "ceiling_3xtf32": tc_peak / 6.0, "frac_of_3xtf32_ceiling": achieved / (tc_peak / 6.0),
             "frac_of_nominal_fp32_cuda_core_peak": achieved / fp32_peak,
@@ -440,8 +441,8 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     if w.name == "cfg3" and world == 1:
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch (= one epoch) from the committed ncu --set full capture;
         # the algorithmic bytes of an epoch are the gathered rollout rows, 262144 x 112 B = 29.4 MB: no wasted re-reads
-        roofline["traffic"] = (29674240 + 630016) if mlp_tc else (29616128 + 353792)
-        roofline["traffic_source"] = "profiles/r2_mlp_update_tc_cfg3_raw.csv" if mlp_tc else "profiles/r1b_mlp_update_cfg3_raw.csv"
+        roofline["traffic"] = (29649152 + 651776) if mlp_tc else (29616128 + 353792)
+        roofline["traffic_source"] = "profiles/r2b_mlp_update_tc_cfg3_raw.csv" if mlp_tc else "profiles/r1b_mlp_update_cfg3_raw.csv"
     if w.base == "cnn" and os.environ.get("CPPRL_B200_CNN_FP32") != "1":
         # the ten CnnBase contractions run on tcgen05 as 3xTF32 (hi*hi + hi*lo + lo*hi): three TF32 MMAs per
         # algorithmic product at half the bf16 rate, so this path's own ceiling is the measured bf16 peak / 6

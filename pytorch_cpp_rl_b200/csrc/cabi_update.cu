@@ -1468,6 +1468,8 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.state = h->scratch.state;
     CPPRL_CUDA_TRY(cudaMemsetAsync(h->scratch.image, 0, il.floats * sizeof(float), s));
     a.barrier_sel = static_cast<int>(h->scratch.barrier_launches & 1u);
+    a.dbg_clocks = g_dbg_clocks; // (cpprl_b200_debug_phase_clocks)
+    a.dbg_step = g_dbg_step;
     if (int rc = mlp_update_launch(plan.R, a, plan.grid, s))
         return rc;
     ++h->scratch.barrier_launches;

@@ -45,7 +45,8 @@ print(f"{cfg}: {used.sum()} CTAs ({has_tile.sum()} with tiles), step {step}; cyc
       "multi-tile CTAs show the LAST tile")
 c = c[has_tile]
 d = np.diff(c[:, :16], axis=1)
-for i, n in enumerate(NAMES):
+last = 15 if c[:, 15].all() else 13  # the last optimiser step of a launch has no second barrier (marks 14, 15 stay zero)
+for i, n in enumerate(NAMES[:last]):
     print(f"  {n:12s} {d[:, i].min():8d} {int(np.median(d[:, i])):8d} {d[:, i].max():8d}")
 if c[:, 20].any():
     # tensor-core variant: finer marks (slots 20..26) between the standard ones
@@ -63,7 +64,7 @@ if c[:, 30].any():
                          ("poll + CTA barrier", 31, 11)]:
         dd = c[:, i1] - c[:, i0]
         print(f"    {name:48s} {dd.min():8d} {int(np.median(dd)):8d} {dd.max():8d}")
-tot = c[:, 15] - c[:, 0]
+tot = c[:, last] - c[:, 0]
 if world > 1:
     x = np.diff(c[:, 16:20], axis=1)
     for i, n in enumerate(["x: push to peers", "x: poll + add", "x: barrier"]):
