@@ -38,8 +38,11 @@ __global__ void __launch_bounds__(256)
 // ---- running mean / std ------------------------------------------------------------------------
 constexpr int kRmsThreads = 256;
 
-// ws[0..D) += column sums, ws[D..2D) += column sums of squares (double); the last block to finish
-// performs the Chan merge (running_mean_std.cpp:30-43) and re-zeroes nothing (caller memset).
+// Block b leaves its column sums and column sums of squares (double) in ws[b][0..2D); the last block to finish adds the
+// blocks' partials in a FIXED order (slices of blocks by block index, then the slices in order: the same bits every run,
+// where atomics would add in arrival order), leaves the totals in ws[0][..] and performs the Chan merge
+// (running_mean_std.cpp:30-43).  The arrival counter sits behind the kRmsMaxBlocks partial rows (caller memset).
+constexpr int kRmsMaxBlocks = 1024;
 __global__ void __launch_bounds__(kRmsThreads)
     rms_update_kernel(const float *__restrict__ x, int64_t M, int D, double *__restrict__ ws,
                       unsigned int *__restrict__ done_counter, float *__restrict__ count,
@@ -73,8 +76,8 @@ __global__ void __launch_bounds__(kRmsThreads)
             cs += sh[j];
             css += sh[lanes_used + j];
         }
-        atomicAdd(&ws[tid], cs);
-        atomicAdd(&ws[D + tid], css);
+        __stcg(&ws[static_cast<size_t>(blockIdx.x) * 2 * D + tid], cs);
+        __stcg(&ws[static_cast<size_t>(blockIdx.x) * 2 * D + D + tid], css);
     }
     __threadfence();
     __syncthreads();
@@ -85,6 +88,29 @@ __global__ void __launch_bounds__(kRmsThreads)
     if (!is_last)
         return;
     __threadfence();
+    {
+        const int cols = 2 * D, nblocks = static_cast<int>(gridDim.x);
+        const int slices = cols <= kRmsThreads ? kRmsThreads / cols : 1; // (cols > kRmsThreads: one slice, two column passes)
+        for (int c0 = 0; c0 < cols; c0 += kRmsThreads)
+        {
+            const int c = c0 + (slices > 1 ? tid % cols : tid), j = slices > 1 ? tid / cols : 0;
+            double acc = 0.0;
+            if (c < cols && j < slices)
+                for (int b = j; b < nblocks; b += slices)
+                    acc += __ldcg(&ws[static_cast<size_t>(b) * cols + c]);
+            if (c < cols && j < slices)
+                sh[j * cols + c] = acc; // (slices * cols <= 2 * lanes_used doubles of dynamic shared memory)
+        }
+        __syncthreads();
+        for (int c = tid; c < cols; c += kRmsThreads)
+        {
+            double total = 0.0;
+            for (int j = 0; j < slices; ++j)
+                total += sh[j * cols + c];
+            ws[c] = total; // (every partial of block 0's row has been read: the barrier above)
+        }
+        __syncthreads();
+    }
     double rows_total = static_cast<double>(M);
     __shared__ double sh_rows;
     if (comm.world > 1)
@@ -248,7 +274,7 @@ extern "C" int cpprl_b200_gather_rows(const void *d_src, int64_t n_src_rows, int
 
 extern "C" int64_t cpprl_b200_rms_workspace_bytes(int64_t /*M*/, int64_t D)
 {
-    return D <= 0 ? 0 : static_cast<int64_t>(sizeof(double)) * 2 * D + 16;
+    return D <= 0 ? 0 : static_cast<int64_t>(sizeof(double)) * 2 * D * kRmsMaxBlocks + 16;
 }
 
 namespace cpprl_b200
@@ -264,18 +290,17 @@ int launch_rms_update(const float *d_x, int64_t M, int64_t D, float *d_count, fl
         return fail(CPPRL_B200_EUNSUPPORTED, "rms_update: D > 256 is not implemented");
     if (int rc = require_device())
         return rc;
-    const int64_t ws_bytes = cpprl_b200_rms_workspace_bytes(M, D);
     KernelTimer timer("rms", s);
-    CPPRL_CUDA_TRY(cudaMemsetAsync(d_workspace, 0, ws_bytes, s));
+    double *ws = static_cast<double *>(d_workspace);
+    unsigned int *counter = reinterpret_cast<unsigned int *>(ws + static_cast<size_t>(2) * D * kRmsMaxBlocks);
+    CPPRL_CUDA_TRY(cudaMemsetAsync(counter, 0, 16, s)); // (the partial rows are written before they are read)
     const int lanes_used = (kRmsThreads / static_cast<int>(D)) * static_cast<int>(D);
     int64_t blocks = (M * D + lanes_used * 8 - 1) / (static_cast<int64_t>(lanes_used) * 8);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 4;
+    const int64_t cap = std::min<int64_t>(static_cast<int64_t>(sm_count()) * 4, kRmsMaxBlocks);
     if (blocks > cap)
         blocks = cap;
     if (blocks < 1)
         blocks = 1;
-    double *ws = static_cast<double *>(d_workspace);
-    unsigned int *counter = reinterpret_cast<unsigned int *>(ws + 2 * D);
     const CommView view = comm_view(comm);
     const unsigned int seq = view.world > 1 ? ++*comm_rms_seq(comm) : 0u;
     rms_update_kernel<<<static_cast<unsigned>(blocks), kRmsThreads, sizeof(double) * 2 * lanes_used, s>>>(

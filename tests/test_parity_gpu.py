@@ -146,7 +146,7 @@ def test_observation_normalizer_clips_known_answer():
     assert float(out.max()) <= 1.0 and float(out.min()) >= -1.0
 
 
-@pytest.mark.parametrize("M,D", [(1032, 8), (24576, 8), (263168, 17), (10, 3), (1, 5)])
+@pytest.mark.parametrize("M,D", [(1032, 8), (24576, 8), (263168, 17), (10, 3), (1, 5), (40000, 200), (3000, 128), (5000, 129)])
 def test_rms_update_vs_reference(ref, M, D):
     rng = np.random.default_rng(M + D)
     x = (rng.standard_normal((M, D)) * 2.5 + 0.7).astype(np.float32)
@@ -163,6 +163,18 @@ def test_rms_update_vs_reference(ref, M, D):
         np.testing.assert_allclose(n.rms.mean.cpu().numpy(), m, rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(n.rms.variance.cpu().numpy(), v, rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(got_y, want_y, rtol=1e-5, atol=1e-5)
+
+
+def test_rms_update_is_deterministic():
+    """Per-block partial sums merged in a fixed order: the same bits every run, at a size with hundreds of blocks."""
+    x = torch.randn(263168, 17, device="cuda") * 3 + 1
+    outs = []
+    for _ in range(4):
+        n = api.ObservationNormalizer(17)
+        n.update(x)
+        n.update(x * 0.5)
+        outs.append(torch.cat([n.rms.count, n.rms.mean, n.rms.variance]).cpu())
+    assert all(torch.equal(outs[0], o) for o in outs[1:])
 
 
 def test_normalize_clamps(ref):
