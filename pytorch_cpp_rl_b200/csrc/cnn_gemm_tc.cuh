@@ -122,6 +122,20 @@ struct ExactOf<L, decltype(void(L::kTf32Exact))>
     static constexpr bool value = L::kTf32Exact;
 };
 
+// An epilogue type may declare `static constexpr bool kColSum = true`: it then has store(m, n, v) returning what it wrote,
+// a pointer `colsum` (may be null) and `colmod`; the kernel adds the column sums of what its CTA wrote to
+// colsum[n % colmod] (one atomic per column and CTA).
+template <class E, class = void>
+struct ColSumOf
+{
+    static constexpr bool value = false;
+};
+template <class E>
+struct ColSumOf<E, decltype(void(E::kColSum))>
+{
+    static constexpr bool value = E::kColSum;
+};
+
 // A_T: A(m, k) = X[k][m] (the loader's vectors run along m: transposed on the way into shared memory); else
 // A(m, k) = X[m][k] (vectors along k).  B(k, n) = Y[k][n] always (vectors along n, transposed likewise).
 template <int BN, bool A_T, class ALoad, class BLoad, class Epi>
@@ -386,13 +400,47 @@ __global__ void __launch_bounds__(kThreads, BN == 128 ? 1 : 2) gemm_tc_kernel(co
         for (int c = 0; c < BN / 2; c += 4)
             *reinterpret_cast<float4 *>(tile + row * LD + half * (BN / 2) + c) = make_float4(racc[c], racc[c + 1], racc[c + 2], racc[c + 3]);
         __syncthreads();
+        float4 cs = make_float4(0.f, 0.f, 0.f, 0.f);
+        (void)cs;
 #pragma unroll
         for (int j = 0; j < BN / 8; ++j)
         {
             const int v = tid + j * kThreads, r = v / (BN / 4), c4 = v % (BN / 4);
             const int m = m0 + r, n = n0 + 4 * c4;
             if (m < M && n < N)
-                epi(m, n, *reinterpret_cast<const float4 *>(tile + r * LD + 4 * c4));
+            {
+                if constexpr (ColSumOf<Epi>::value)
+                {
+                    const float4 o = epi.store(m, n, *reinterpret_cast<const float4 *>(tile + r * LD + 4 * c4));
+                    cs.x += o.x, cs.y += o.y, cs.z += o.z, cs.w += o.w;
+                }
+                else
+                    epi(m, n, *reinterpret_cast<const float4 *>(tile + r * LD + 4 * c4));
+            }
+        }
+        if constexpr (ColSumOf<Epi>::value)
+        {
+            if (epi.colsum) // (uniform over the grid)
+            {
+                // kThreads is a multiple of BN / 4, so a thread met the same four columns in every iteration above: the
+                // threads of a column group combine through the (idle again) tile memory, one atomic per column
+                constexpr int G = BN / 4;
+                __syncthreads();
+                float4 *red = reinterpret_cast<float4 *>(tc_smem);
+                red[tid] = cs;
+                __syncthreads();
+                if (tid < G && n0 + 4 * tid < N)
+                {
+                    float4 sum = red[tid];
+                    for (int t = tid + G; t < kThreads; t += G)
+                    {
+                        const float4 o = red[t];
+                        sum.x += o.x, sum.y += o.y, sum.z += o.z, sum.w += o.w;
+                    }
+                    float *dst = epi.colsum + (n0 + 4 * tid) % epi.colmod;
+                    atomicAdd(dst, sum.x), atomicAdd(dst + 1, sum.y), atomicAdd(dst + 2, sum.z), atomicAdd(dst + 3, sum.w);
+                }
+            }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

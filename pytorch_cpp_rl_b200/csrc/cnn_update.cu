@@ -349,25 +349,37 @@ struct AtomicAddStore // gradient image, reduction split across the grid (div as
     }
 };
 
+// The two epilogues that write an activation gradient dz can also form its column sums -- the bias gradient of the layer
+// that produced the activation -- on the way out (tensor-core kernel only: tc::ColSumOf): `colsum` (may be null) receives
+// sum_m dz[m][n] at index n % colmod with one atomic per column and CTA, instead of a separate pass that re-reads dz from
+// HBM (dz1 alone is 210 MB per 4096-row pass).
 struct ReluMaskStore // dz[m][n] = acc where the forward activation was positive
 {
+    static constexpr bool kColSum = true;
     float *out;
     const float *act;
     int ld;
-    __device__ __forceinline__ void operator()(int m, int n, float4 v) const
+    float *colsum;
+    int colmod;
+    __device__ __forceinline__ float4 store(int m, int n, float4 v) const
     {
         const size_t o = static_cast<size_t>(m) * ld + n;
         const float4 a = __ldg(reinterpret_cast<const float4 *>(act + o));
         v.x = a.x > 0.f ? v.x : 0.f, v.y = a.y > 0.f ? v.y : 0.f, v.z = a.z > 0.f ? v.z : 0.f, v.w = a.w > 0.f ? v.w : 0.f;
         *reinterpret_cast<float4 *>(out + o) = v;
+        return v;
     }
+    __device__ __forceinline__ void operator()(int m, int n, float4 v) const { store(m, n, v); }
 };
 
 struct Dgrad2Store // rows are (i, py, px) of parity class blockIdx.z: scatter to the NHWC pixel (2 py + cy, 2 px + cx)
 {
+    static constexpr bool kColSum = true;
     float *out;
     const float *act;
-    __device__ __forceinline__ void operator()(int m, int n, float4 v) const
+    float *colsum;
+    int colmod;
+    __device__ __forceinline__ float4 store(int m, int n, float4 v) const
     {
         const int cy = blockIdx.z >> 1, cx = blockIdx.z & 1;
         const int i = m / 100, p = m - i * 100, py = p / 10, px = p - py * 10;
@@ -375,7 +387,9 @@ struct Dgrad2Store // rows are (i, py, px) of parity class blockIdx.z: scatter t
         const float4 a = __ldg(reinterpret_cast<const float4 *>(act + o));
         v.x = a.x > 0.f ? v.x : 0.f, v.y = a.y > 0.f ? v.y : 0.f, v.z = a.z > 0.f ? v.z : 0.f, v.w = a.w > 0.f ? v.w : 0.f;
         *reinterpret_cast<float4 *>(out + o) = v;
+        return v;
     }
+    __device__ __forceinline__ void operator()(int m, int n, float4 v) const { store(m, n, v); }
 };
 
 // ---- parameter index -> image index ------------------------------------------------------------------------------------
@@ -896,6 +910,16 @@ inline bool use_tensor_cores()
     return on;
 }
 
+// CPPRL_B200_CNN_COLSUM_KERNEL=1 keeps the separate column-sum launches on the tensor-core path (A/B runs)
+inline bool cnn_fold_colsum()
+{
+    static const bool on = [] {
+        const char *e = std::getenv("CPPRL_B200_CNN_COLSUM_KERNEL");
+        return !(e && e[0] == '1');
+    }();
+    return on;
+}
+
 template <int BM, int BN, int TM, int TN, bool A_T, class AL, class BL, class EP>
 int launch_gemm(const AL &al, const BL &bl, const EP &ep, int M, int N, int K, int grid_z, bool z_is_k_split, const int *stop,
                 cudaStream_t s)
@@ -982,6 +1006,8 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
 {
     const int K1 = a.C * 64;
     const float *img = ws.img;
+    // the tensor-core kernels form the conv layers' bias gradients in the epilogue that writes dz (ReluMaskStore above)
+    const bool fold = use_tensor_cores() && cnn_fold_colsum();
     // linear 1568 -> 512: weight gradient (reduction over rows), bias, data gradient masked by conv3's ReLU
     if (int rc = launch_gemm<128, 128, 8, 8, true>(MatLoad{ws.act3, rows, kCnnFlat}, MatLoad{ws.dh, rows, kCnnHid},
                                                    AtomicAddStore{ws.gimg + a.il.wfc, kCnnHid, 1.f}, kCnnFlat, kCnnHid, rows,
@@ -990,8 +1016,8 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     if (int rc = launch_colsum(ws.dh, rows, kCnnHid, ws.gflat + a.po.bfc, stop, s))
         return rc;
     if (int rc = launch_gemm<128, 128, 8, 8, false>(MatLoad{ws.dh, rows, kCnnHid}, MatLoad{img + a.il.wfd, kCnnHid, kCnnFlat},
-                                                    ReluMaskStore{ws.dz3, ws.act3, kCnnFlat}, rows, kCnnFlat, kCnnHid, 1, false,
-                                                    stop, s))
+                                                    ReluMaskStore{ws.dz3, ws.act3, kCnnFlat, fold ? ws.gflat + a.po.b3 : nullptr, kCnnC3},
+                                                    rows, kCnnFlat, kCnnHid, 1, false, stop, s))
         return rc;
     // conv3
     if (int rc = launch_gemm<256, 32, 8, 4, true>(ActIm2col<kCnnO2, kCnnO3, 3, 1, kCnnC2>{ws.act2, rows},
@@ -999,11 +1025,12 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
                                                   AtomicAddStore{ws.gimg + a.il.w3, kCnnC3, 1.f}, kCnnK3, kCnnC3, rows * kCnnP3,
                                                   splits_for(use_tensor_cores() ? 5 : 3, static_cast<long long>(rows) * kCnnP3), true, stop, s))
         return rc;
-    if (int rc = launch_colsum(ws.dz3, static_cast<long long>(rows) * kCnnP3, kCnnC3, ws.gflat + a.po.b3, stop, s))
-        return rc;
+    if (!fold)
+        if (int rc = launch_colsum(ws.dz3, static_cast<long long>(rows) * kCnnP3, kCnnC3, ws.gflat + a.po.b3, stop, s))
+            return rc;
     if (int rc = launch_gemm<128, 64, 8, 4, false>(Dgrad3Load{ws.dz3, rows}, MatLoad{img + a.il.w3d, 9 * kCnnC3, kCnnC2},
-                                                   ReluMaskStore{ws.dz2, ws.act2, kCnnC2}, rows * kCnnP2, kCnnC2, 9 * kCnnC3, 1,
-                                                   false, stop, s))
+                                                   ReluMaskStore{ws.dz2, ws.act2, kCnnC2, fold ? ws.gflat + a.po.b2 : nullptr, kCnnC2},
+                                                   rows * kCnnP2, kCnnC2, 9 * kCnnC3, 1, false, stop, s))
         return rc;
     // conv2
     if (int rc = launch_gemm<128, 64, 8, 4, true>(ActIm2col<kCnnO1, kCnnO2, 4, 2, kCnnC1>{ws.act1, rows},
@@ -1011,11 +1038,12 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
                                                   AtomicAddStore{ws.gimg + a.il.w2, kCnnC2, 1.f}, kCnnK2, kCnnC2, rows * kCnnP2,
                                                   splits_for(4, static_cast<long long>(rows) * kCnnP2), true, stop, s))
         return rc;
-    if (int rc = launch_colsum(ws.dz2, static_cast<long long>(rows) * kCnnP2, kCnnC2, ws.gflat + a.po.b2, stop, s))
-        return rc;
+    if (!fold)
+        if (int rc = launch_colsum(ws.dz2, static_cast<long long>(rows) * kCnnP2, kCnnC2, ws.gflat + a.po.b2, stop, s))
+            return rc;
     if (int rc = launch_gemm<256, 32, 8, 4, false>(Dgrad2Load{ws.dz2, rows}, ClassMatLoad{img + a.il.w2d, 4 * kCnnC2, kCnnC1},
-                                                   Dgrad2Store{ws.dz1, ws.act1}, rows * 100, kCnnC1, 4 * kCnnC2, 4, false, stop,
-                                                   s))
+                                                   Dgrad2Store{ws.dz1, ws.act1, fold ? ws.gflat + a.po.b1 : nullptr, kCnnC1}, rows * 100,
+                                                   kCnnC1, 4 * kCnnC2, 4, false, stop, s))
         return rc;
     // conv1 (its input needs no gradient)
     const ObsIm2col obs_rows{a.obs, a.perm, a.row_base + base, rows, a.C};
@@ -1025,7 +1053,7 @@ int cnn_backward_pass(const CnnUpdateArgs &a, const CnnWorkspace &ws, int base, 
     if (int rc = a.obs_exact ? launch_gemm<256, 32, 8, 4, true>(ObsIm2colExact{obs_rows}, dz1, gw1, K1, kCnnC1, rows * kCnnP1, z1, true, stop, s)
                              : launch_gemm<256, 32, 8, 4, true>(obs_rows, dz1, gw1, K1, kCnnC1, rows * kCnnP1, z1, true, stop, s))
         return rc;
-    return launch_colsum(ws.dz1, static_cast<long long>(rows) * kCnnP1, kCnnC1, ws.gflat + a.po.b1, stop, s);
+    return fold ? 0 : launch_colsum(ws.dz1, static_cast<long long>(rows) * kCnnP1, kCnnC1, ws.gflat + a.po.b1, stop, s);
 }
 } // namespace
 
