@@ -288,6 +288,13 @@ struct Plan
     ImageLayout il;
 };
 
+// CPPRL_B200_MLP_STAGE_AHEAD=0: A/B switch of the tensor-core kernel (MlpUpdateArgs::no_stage_ahead)
+static int mlp_no_stage_ahead()
+{
+    const char *e = std::getenv("CPPRL_B200_MLP_STAGE_AHEAD");
+    return (e && e[0] == '0') ? 1 : 0;
+}
+
 // CPPRL_B200_MLP_TC=0 keeps every update on the fp32 CUDA-core kernel (A/B runs)
 bool mlp_tc_enabled()
 {
@@ -810,6 +817,7 @@ extern "C" int cpprl_b200_ppo_begin(cpprl_b200_ppo *h, const cpprl_b200_policy *
     a.n_active = h->plan.n_active;
     a.per_cta = h->plan.per_cta;
     a.tc = h->plan.tc ? 1 : 0;
+    a.no_stage_ahead = mlp_no_stage_ahead();
     a.adv_sums = sharded ? comm_local_adv(h->comm) : h->scratch.adv_sums;
     if (sharded)
         a.adv_seq = ++*comm_update_seq(h->comm);
@@ -1452,6 +1460,7 @@ extern "C" int cpprl_b200_a2c_update_async(cpprl_b200_a2c *h, const cpprl_b200_p
     a.n_active = plan.n_active;
     a.per_cta = plan.per_cta;
     a.tc = plan.tc ? 1 : 0;
+    a.no_stage_ahead = mlp_no_stage_ahead();
     a.adv_sums = nullptr;
     a.algo = kAlgoA2C;
     a.c_actor = 1.f;

@@ -535,91 +535,128 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                  "@p st.global.u64 [%1], t;\n\t}" ::"r"(static_cast<unsigned>(a.dbg_clocks && tid == 0 && mark_step == a.dbg_step)), \
                  "l"(a.dbg_clocks + blockIdx.x * 32 + (slot))                                                  \
                  : "memory")
-    auto finalize_stage = [&](int nrows) { // nrows = valid rows of the item (row r is valid iff r < nrows)
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        __syncthreads();
+    // The rows of a work item, from the staging buffers the cp.async prefetch filled to the operands of the tile phases.
+    // Tensor-core variant, pieces (thread index t of nt threads, so that they can also run on the non-issuing warps under
+    // an MMA chain): stage_obs normalises the observations IN PLACE (XN) and writes the row-major planes (layer 1's B
+    // operand: they overlay the h2 tile, dead after P5b); stage_rows the actions and per-row terms (dead after P4);
+    // stage_xf the column-major planes from the normalised XN (dW1's B operand: in use until the tile's last chain ends).
+    bool pre_staged = false; // stage_obs + stage_rows of the staged item already ran (under the last tile's dW chains)
+    auto stage_obs = [&](int nrows, int t, int nt) {
+        using GeoT = mtc::Geo<TC ? R : 8>;
         const float clip = a.norm_mean ? NCLIP[0] : 0.f;
         const bool norm = a.norm_mean != nullptr;
-        if (TC)
+        unsigned char *xb = reinterpret_cast<unsigned char *>(smem + sp.xb);
+        for (int it = t; it < (Dp >> 2) * R; it += nt)
         {
-            // The observation tile as the two tensor-core operands it feeds, hi / lo planes each: row-major [row][column]
-            // (layer 1) and column-major [column][row] (dW1); rows past the tile are ZERO.  Thread = (row, group of four
-            // columns): four independent normalisations in flight (the exact division is a ~60-cycle dependent chain), one
-            // 16-byte store per row-major plane.
-            using GeoT = mtc::Geo<TC ? R : 8>;
-            unsigned char *xb = reinterpret_cast<unsigned char *>(smem + sp.xb), *xf = reinterpret_cast<unsigned char *>(smem + sp.xf);
-            for (int it = tid; it < (Dp >> 2) * R; it += kUpdThreads)
-            {
-                const int kg = it / R, r = it - kg * R; // R is a compile-time constant
-                float x[4], hi[4], lo[4];
+            const int kg = it / R, r = it - kg * R; // R is a compile-time constant
+            float x[4], hi[4], lo[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    x[j] = XN[(4 * kg + j) * LD + r];
-                bool ok[4];
+            for (int j = 0; j < 4; ++j)
+                x[j] = XN[(4 * kg + j) * LD + r];
+            bool ok[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    ok[j] = 4 * kg + j < D && r < nrows;
-                if (norm)
-                {
-                    // (padding columns and rows divide 1 by the deviation instead of 0: a zero numerator sends the exact
-                    // division -- and with it the whole warp -- down its ~500-cycle slow path)
-                    const float4 mean = *reinterpret_cast<const float4 *>(NMEAN + 4 * kg), sd = *reinterpret_cast<const float4 *>(NSTD + 4 * kg);
-                    x[0] = (ok[0] ? x[0] - mean.x : 1.f) / sd.x, x[1] = (ok[1] ? x[1] - mean.y : 1.f) / sd.y;
-                    x[2] = (ok[2] ? x[2] - mean.z : 1.f) / sd.z, x[3] = (ok[3] ? x[3] - mean.w : 1.f) / sd.w;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        x[j] = fminf(fmaxf(x[j], -clip), clip);
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                {
-                    x[j] = ok[j] ? x[j] : 0.f;
-                    hi[j] = mtc::tf32_hi(x[j]), lo[j] = x[j] - hi[j];
-                }
-                const uint32_t ob = 16u * r + kg * GeoT::kLboB;
-                *reinterpret_cast<float4 *>(xb + ob) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<float4 *>(xb + GeoT::plane_xb(Dp) + ob) = make_float4(lo[0], lo[1], lo[2], lo[3]);
-                const uint32_t of = 64u * kg + (r >> 2) * GeoT::kLboXF + (r & 3) * 4u;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                {
-                    *reinterpret_cast<float *>(xf + of + 16u * j) = hi[j];
-                    *reinterpret_cast<float *>(xf + GeoT::kPlaneXF + of + 16u * j) = lo[j];
-                }
-            }
-        }
-        else
-#pragma unroll 4
-        for (int e = tid; e < Dp * R; e += kUpdThreads)
-        {
-            const int k = e / R, r = e - k * R; // R is a compile-time constant
-            const bool ok = k < D && r < nrows;
-            float x = XN[k * LD + r];
+            for (int j = 0; j < 4; ++j)
+                ok[j] = 4 * kg + j < D && r < nrows;
             if (norm)
             {
-                x = (ok ? x - NMEAN[k] : 1.f) / NSTD[k]; // (never 0 / s: see above)
-                x = fminf(fmaxf(x, -clip), clip);
+                // (padding columns and rows divide 1 by the deviation instead of 0: a zero numerator sends the exact
+                // division -- and with it the whole warp -- down its ~500-cycle slow path)
+                const float4 mean = *reinterpret_cast<const float4 *>(NMEAN + 4 * kg), sd = *reinterpret_cast<const float4 *>(NSTD + 4 * kg);
+                x[0] = (ok[0] ? x[0] - mean.x : 1.f) / sd.x, x[1] = (ok[1] ? x[1] - mean.y : 1.f) / sd.y;
+                x[2] = (ok[2] ? x[2] - mean.z : 1.f) / sd.z, x[3] = (ok[3] ? x[3] - mean.w : 1.f) / sd.w;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    x[j] = fminf(fmaxf(x[j], -clip), clip);
             }
-            X[k * LD + r] = ok ? x : 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                x[j] = ok[j] ? x[j] : 0.f;
+                XN[(4 * kg + j) * LD + r] = x[j];
+                hi[j] = mtc::tf32_hi(x[j]), lo[j] = x[j] - hi[j];
+            }
+            const uint32_t ob = 16u * r + kg * GeoT::kLboB;
+            *reinterpret_cast<float4 *>(xb + ob) = make_float4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<float4 *>(xb + GeoT::plane_xb(Dp) + ob) = make_float4(lo[0], lo[1], lo[2], lo[3]);
         }
+    };
+    auto stage_xf = [&](int t, int nt) {
+        using GeoT = mtc::Geo<TC ? R : 8>;
+        unsigned char *xf = reinterpret_cast<unsigned char *>(smem + sp.xf);
+        for (int it = t; it < (Dp >> 2) * R; it += nt)
+        {
+            const int kg = it / R, r = it - kg * R;
+            const uint32_t of = 64u * kg + (r >> 2) * GeoT::kLboXF + (r & 3) * 4u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+            {
+                const float x = XN[(4 * kg + j) * LD + r];
+                const float hi = mtc::tf32_hi(x);
+                *reinterpret_cast<float *>(xf + of + 16u * j) = hi;
+                *reinterpret_cast<float *>(xf + GeoT::kPlaneXF + of + 16u * j) = x - hi;
+            }
+        }
+    };
+    auto stage_rows = [&](int nrows, int t, int nt) {
         if (a.head == 1)
 #pragma unroll 2
-            for (int e = tid; e < A * R; e += kUpdThreads)
+            for (int e = t; e < A * R; e += nt)
             {
                 const int k = e / R, r = e - k * R;
                 ACT[k * LD + r] = r < nrows ? ACTN[k * LD + r] : 0.f;
             }
-        if (tid < R)
+        if (t < R)
         {
-            const bool ok = tid < nrows;
-            const float ret = ok && training ? SCN[tid] : 0.f;
-            const float olp = ok && training ? SCN[LD + tid] : 0.f;
-            const float vold = ok && training && a.adv_sums ? SCN[2 * LD + tid] : 0.f;
-            RET[tid] = ret;
-            OLDLP[tid] = olp;
-            ADV[tid] = (ret - vold - MISC[0]) / MISC[1]; // (adv - mean) / (std + 1e-5)              (ppo.cpp:57)
+            const bool ok = t < nrows;
+            const float ret = ok && training ? SCN[t] : 0.f;
+            const float olp = ok && training ? SCN[LD + t] : 0.f;
+            const float vold = ok && training && a.adv_sums ? SCN[2 * LD + t] : 0.f;
+            RET[t] = ret;
+            OLDLP[t] = olp;
+            ADV[t] = (ret - vold - MISC[0]) / MISC[1]; // (adv - mean) / (std + 1e-5)              (ppo.cpp:57)
             if (a.head == 0)
-                reinterpret_cast<int *>(ACT)[tid] = ok ? static_cast<int>(ACTIN[tid]) : 0;
+                reinterpret_cast<int *>(ACT)[t] = ok ? static_cast<int>(ACTIN[t]) : 0;
+        }
+    };
+    auto finalize_stage = [&](int nrows) { // nrows = valid rows of the item (row r is valid iff r < nrows)
+        if (!(TC && pre_staged))
+        {
+            // (a pre-staged item's rows were waited for, and published by a barrier, before the chains that staged them:
+            // its remaining piece starts at once -- while thread 0's warp still sits in the release of the grid arrival)
+            asm volatile("cp.async.wait_all;" ::: "memory");
+            __syncthreads();
+        }
+        if (TC)
+        {
+            if (!pre_staged)
+            {
+                stage_obs(nrows, tid, kUpdThreads);
+                stage_rows(nrows, tid, kUpdThreads);
+            }
+            if (!pre_staged)
+                stage_xf(tid, kUpdThreads); // (same item -> thread mapping as stage_obs: a thread reads back its own values)
+            else if (warp > 0)
+                stage_xf(tid - 32, kUpdThreads - 32); // (warp 0's stores would queue behind its release fence)
+            pre_staged = false;
+        }
+        else
+        {
+            const float clip = a.norm_mean ? NCLIP[0] : 0.f;
+            const bool norm = a.norm_mean != nullptr;
+#pragma unroll 4
+            for (int e = tid; e < Dp * R; e += kUpdThreads)
+            {
+                const int k = e / R, r = e - k * R; // R is a compile-time constant
+                const bool ok = k < D && r < nrows;
+                float x = XN[k * LD + r];
+                if (norm)
+                {
+                    x = (ok ? x - NMEAN[k] : 1.f) / NSTD[k]; // (never 0 / s: see stage_obs)
+                    x = fminf(fmaxf(x, -clip), clip);
+                }
+                X[k * LD + r] = ok ? x : 0.f;
+            }
+            stage_rows(nrows, tid, kUpdThreads);
         }
         __syncthreads();
     };
@@ -1265,6 +1302,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 }
                 mtc::wait_st();
                 mtc::fence_before();
+                // last tile of this minibatch with the next minibatch's first tile prefetched: its rows are staged by the
+                // non-issuing warps under the two weight-gradient chains below (the barrier publishes every thread's copies)
+                const bool stage_ahead = staged && tile + G >= n_tiles && !a.no_stage_ahead;
+                if (stage_ahead)
+                    asm volatile("cp.async.wait_all;" ::: "memory");
                 __syncthreads();
                 CPPRL_MARK(8);
                 // ---- T4: weight gradients of the tile: dW2[F][k] = sum_r dz2[F][r] h1[k][r] (one chain per tower's h1),
@@ -1313,6 +1355,14 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                                 gsm[a.po.wv + k] += G2_WV[k];
                         }
                     }
+                    if (stage_ahead && wt >= 0)
+                    {
+                        const int nr = min(R, rows_of(step + 1) - static_cast<int>(blockIdx.x) * R);
+                        if (pass == 0)
+                            stage_obs(nr, wt, kWorkThreads);
+                        else
+                            stage_rows(nr, wt, kWorkThreads);
+                    }
                     if (k_begin < k_end)
                     {
                         mbar_wait(&tcbar[3 + pass], tc_parity);
@@ -1343,6 +1393,8 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                         }
                     }
                 }
+                if (stage_ahead)
+                    pre_staged = true;
                 tc_parity ^= 1u;
                 CPPRL_MARK(25);
                 if (tile + G >= n_tiles)

@@ -111,6 +111,7 @@ struct MlpUpdateArgs
     UpdateState *state;
     long long *dbg_clocks; // nullable: [grid][32] clock64() phase markers of step dbg_step (profiling hook)
     int dbg_step;
+    int no_stage_ahead;    // A/B switch (CPPRL_B200_MLP_STAGE_AHEAD=0): the next minibatch's first tile is staged at the grid barrier only
     int dbg_launch;        // launch counter: with dbg_clocks, CTA 0 stores %globaltimer at entry / exit in [148 * 32 + 2 * (dbg_launch % 64)]
     // forward-only outputs (kAlgoForward)
     float *out_value, *out_logp, *out_entropy_sum;
