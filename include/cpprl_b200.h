@@ -401,8 +401,8 @@ int cpprl_b200_debug_perm_stream(void *rng_state, const void *reseed_state, int6
  * update kernel stores clock64() at its phase boundaries during minibatch `step` of each launch. */
 void cpprl_b200_debug_phase_clocks(long long *d_buffer, int step);
 /* Which variant of the fused MlpBase update a minibatch of this shape trains on: > 0 = tensor cores (tcgen05 kind::tf32 as
- * 3xTF32, at most 32 observation columns: minibatches of more than 32 rows per SM on 56- or 64-row tiles, minibatches of
- * at most 16 rows per SM on 16-row tiles; the value is the tile's row count), 0 = fp32 CUDA cores.
+ * 3xTF32, at most 32 observation columns: minibatches of more than 32 rows per SM on 56- or 64-row tiles, smaller ones on
+ * 32- or 16-row tiles; the value is the tile's row count), 0 = fp32 CUDA cores (more than 32 observation columns).
  * CPPRL_B200_MLP_TC=0 in the environment forces 0 (A/B runs). */
 int cpprl_b200_mlp_update_variant(int64_t minibatch_rows, int64_t obs_dim, int64_t num_actions);
 

@@ -306,7 +306,7 @@ bool mlp_tc_enabled()
 // tile, falling back to the smaller tile when the shared-memory plan of the larger one does not fit.  Minibatches that
 // fill the chip with 64-row tiles (more than 32 rows per SM) and have at most 32 observation columns train on the
 // tensor-core variant: 56-row tiles, so that 148 CTAs cover an 8192-row minibatch in one wave; minibatches of at most 16
-// rows per SM train on its 16-row tile.
+// rows per SM train on its 16-row tile, those up to 32 rows per SM on its 32-row tile.
 // Training launches keep at least 16 CTAs so that the phase-2 slice of the parameter vector each CTA reduces,
 // steps and keeps resident in shared memory stays small; CTAs beyond the tile count only take part in phase 2.
 // Training launches keep at least this many CTAs: CTAs beyond the tile count only take part in phase 2, where each
@@ -349,6 +349,10 @@ int choose_plan(int64_t B, const ParamOffsets &po, int Dp, int Ap, bool training
     // minibatches that do not fill the chip with 32-row CUDA-core tiles: 16-row tensor-core tiles put twice as many SMs to
     // work on a tile that is itself shorter (cfg1: 256 rows, 16 tiles: 0.426 -> 0.369 ms per update, 2.40 -> 2.78 M transitions/s)
     if (training && B_max <= 16ll * sms && Dp <= 32 && mlp_tc_enabled() && shape(kTcRowsSmall, true, plan) <= 227 * 1024)
+        return 0;
+    // ... and the sizes in between (16 to 32 rows per SM) on 32-row tensor-core tiles: one tile per SM either way, the tile
+    // itself a third shorter than the CUDA-core one
+    if (training && B_max <= 32ll * sms && Dp <= 32 && mlp_tc_enabled() && shape(kTcRowsMid, true, plan) <= 227 * 1024)
         return 0;
     int R = (B <= 32ll * sms) ? 32 : 64;
     if (R == 64 && shape(64, false, plan) > 227 * 1024)

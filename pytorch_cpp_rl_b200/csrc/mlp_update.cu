@@ -1805,10 +1805,12 @@ int mlp_update_launch(int R, const MlpUpdateArgs &args, int grid, cudaStream_t s
         return fail(CPPRL_B200_EINVAL, "mlp_update: image layout does not match the kernel variant");
     if (tc)
     {
-        if ((R != kTcRows && R != kTcRowsWide && R != kTcRowsSmall) || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
+        if ((R != kTcRows && R != kTcRowsWide && R != kTcRowsSmall && R != kTcRowsMid) || args.Dp > mtc::kMaxDp || args.algo == kAlgoForward)
             return fail(CPPRL_B200_EINVAL, "mlp_update: unsupported tensor-core plan");
         if (R == kTcRowsSmall)
             return launch_update<kTcRowsSmall, true>(args, grid, smem, s);
+        if (R == kTcRowsMid)
+            return launch_update<kTcRowsMid, true>(args, grid, smem, s);
         return R == kTcRows ? launch_update<kTcRows, true>(args, grid, smem, s) : launch_update<kTcRowsWide, true>(args, grid, smem, s);
     }
     if (R == 64)

@@ -11,6 +11,7 @@ constexpr int kUpdThreads = 256;   // 8 warps: warps 0-3 run the actor tower, 4-
 constexpr int kNumStats = 8;       // slots appended to the gradient vector (5 used)
 constexpr int kMaxActions = 16;
 constexpr int kTcRows = 56;        // tile rows of the tensor-core variant: 148 CTAs x 56 rows cover an 8192-row minibatch in one wave
+constexpr int kTcRowsMid = 32;     // ... for minibatches of 16 to 32 rows per SM
 constexpr int kTcRowsSmall = 16;   // ... and for minibatches that do not fill the chip (cfg1: 256 rows = 16 tiles instead of 8 CUDA-core tiles of 32)
 constexpr int kTcRowsWide = 64;    // ... and the tile for minibatches that need fewer waves with it (ragged env-sharded minibatches: 8192 +- 4 sigma rows)
 

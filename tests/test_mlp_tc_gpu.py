@@ -1,5 +1,5 @@
 """The tensor-core variant of the fused MlpBase update (csrc/mlp_tc.cuh: tcgen05 kind::tf32 as 3xTF32; 56- or 64-row tiles
-for minibatches of more than 32 rows per SM, 16-row tiles for minibatches of at most 16 rows per SM) against the compiled reference and against the fp32 CUDA-core variant of the same kernel
+for minibatches of more than 32 rows per SM, 32- and 16-row tiles for smaller ones) against the compiled reference and against the fp32 CUDA-core variant of the same kernel
 (CPPRL_B200_MLP_TC=0), over the shapes the variant has to get right: observation widths around the 8-column k-step,
 both heads, minibatches that end in a ragged tile, several tiles per CTA, PPO with several optimiser steps and A2C."""
 import os
@@ -26,7 +26,9 @@ def test_variant_selection():
     assert _variant(9000, 17, 6) == 64         # fewer waves with 64-row tiles
     assert _variant(256, 8, 4) == 16           # cfg1: a minibatch that does not fill the chip -> 16 tiles of 16 rows
     assert _variant(16 * 148, 8, 4) == 16      # one 16-row tile on every SM
-    assert _variant(16 * 148 + 1, 8, 4) == 0   # 32-row CUDA-core tiles up to 32 rows per SM
+    assert _variant(16 * 148 + 1, 8, 4) == 32  # 32-row tiles up to 32 rows per SM
+    assert _variant(32 * 148, 17, 6) == 32
+    assert _variant(32 * 148 + 1, 17, 6) == 56
     assert _variant(256, 33, 4) == 0
     assert _variant(8192, 33, 6) == 0          # more than 32 observation columns: CUDA-core variant
     os.environ["CPPRL_B200_MLP_TC"] = "0"
@@ -74,6 +76,8 @@ CASES = {
     "small_tile_a2c": ("cfg2", dict(T=5, N=64)),
     # 80 optimiser steps in one launch: beyond the table of bias corrections the kernel fills at launch (64 steps)
     "small_tile_80_minibatches": ("cfg1", dict(T=80, N=8, num_epoch=1, num_mini_batch=80)),
+    "mid_tile_normal": ("cfg3", dict(T=16, N=200, num_epoch=2, num_mini_batch=1)),               # 3200 rows = 100 tiles of 32
+    "mid_tile_categorical_ragged": ("cfg1", dict(T=13, N=300, num_epoch=1, num_mini_batch=1, storage_hidden=1)),  # 121 tiles + 28 rows
     "no_normaliser": ("cfg3", dict(T=8, N=640, normalize_obs=False, num_epoch=1, num_mini_batch=1)),
 }
 
