@@ -63,6 +63,8 @@ CASES = {
     "categorical_obs9_act16": ("cfg1", dict(T=8, N=700, obs_shape=(9,), num_actions=16, num_epoch=2, num_mini_batch=1,
                                             storage_hidden=1)),
     "multi_tile": ("cfg3", dict(T=20, N=1024, num_epoch=1, num_mini_batch=1)),                 # 20480 rows: three tiles per CTA
+    # 10240-row minibatches = 183 tiles: some CTAs own two tiles, and stage the next minibatch's first tile under the second
+    "multi_tile_two_minibatches": ("cfg3", dict(T=20, N=1024, num_epoch=2, num_mini_batch=2)),
     "a2c_obs8": ("cfg2", dict(T=3, N=2048)),
     # 9000-row minibatches: 161 tiles of 56 rows (two waves over 148 SMs) but 141 of 64 -> the 64-row tile
     "wide_tile_normal": ("cfg3", dict(T=9, N=1000, num_epoch=2, num_mini_batch=1)),
