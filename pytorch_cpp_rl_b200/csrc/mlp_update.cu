@@ -776,6 +776,19 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                 mtc::fence_before();
             }
         }
+        else if (training && !staged && step + 1 < a.n_steps && static_cast<long long>(blockIdx.x) * R < rows_of(step + 1))
+        {
+            // No tile in this minibatch but one in the next (env-sharded updates: a rank's share of a minibatch is ragged,
+            // the CTAs around the tile count drop in and out): fetch that tile now and lay it out while waiting at the grid
+            // barrier below, like the CTAs that prefetched under their last tile -- otherwise this CTA would start the next
+            // step with a cold fetch + the full staging on the critical path, and every other CTA would wait for its partial.
+            const long long row = item_rowid(step + 1, blockIdx.x);
+            if (tid < R)
+                ROWIDN[tid] = row;
+            __syncthreads();
+            prefetch_issue();
+            staged = true;
+        }
         // gradients of the tower matrices of this minibatch: registers of the tensor-core variant
         float acc_w2[TC ? 32 : 1], acc_w1[TC ? 16 : 1], acc_b1 = 0.f, acc_b2 = 0.f;
 #pragma unroll
@@ -1562,6 +1575,11 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
         // Granule = 4 consecutive floats.  Warp w sums the partials of CTAs w, w+8, ...; all of a lane's loads are
         // issued before the first add, so the phase costs one L2 round trip.
         const int red_ld = a.per_cta + kNumStats;
+        // (multi-GPU: the error word the exchange below looks at is fetched here, so that its L2 round trip runs under the
+        // local reduction instead of between the push and the first poll of every step)
+        int comm_error_seen = 0;
+        if (world > 1)
+            comm_error_seen = *reinterpret_cast<volatile int *>(&a.state->comm_error);
         {
             const int own_gran = n_own >> 2;
             const int n_gran = own_gran + (kNumStats >> 2);
@@ -1622,7 +1640,7 @@ __global__ void __launch_bounds__(kUpdThreads, 1) mlp_update_kernel(const MlpUpd
                                  mine, seq);
             }
             CPPRL_MARK(17);
-            const bool comm_ok = *reinterpret_cast<volatile int *>(&a.state->comm_error) == 0;
+            const bool comm_ok = comm_error_seen == 0;
             for (int i = tid; i < n_own + kNumStats; i += kUpdThreads)
             {
                 // the words of ALL peers are polled together (independent loads in flight: one L2 round trip per sweep
