@@ -17,6 +17,7 @@
 // tests/test_host_rng_cpu.py.
 //
 // Host code only (no kernel here); it lives in the C-ABI library because the reference's host language is C++.
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <cstdint>
@@ -127,14 +128,24 @@ void store_state(void *blob, const Mt19937 &mt)
 // array stays in the core's L2, and the result is widened to the int64 ids the generator hands out.  The 32-bit
 // modulo equals torch's `int64_t(random()) % (n - i)` (both operands are below 2^32) and, having no dependence on the
 // swaps, overlaps them in the out-of-order window (0.8 ms per 262 144 ids against 1.4 ms as two passes).
-void walk(const uint32_t *raw, int64_t n, int64_t *out, std::vector<uint32_t> &ids)
+// `avail` counts the raw draws the producer has written so far: the walk follows the Mersenne Twister a block behind
+// instead of waiting for all n - 1 draws (the producer is about twice as fast as the walk, so the wait is one block).
+constexpr int64_t kHandOff = 8192;
+void walk(const uint32_t *raw, int64_t n, int64_t *out, std::vector<uint32_t> &ids, const std::atomic<int64_t> *avail)
 {
     ids.resize(static_cast<size_t>(n));
     for (int64_t i = 0; i < n; ++i)
         ids[i] = static_cast<uint32_t>(i);
     const uint32_t un = static_cast<uint32_t>(n);
+    int64_t ready = 0;
     for (int64_t i = 0; i + 1 < n; ++i)
     {
+        if (i >= ready)
+        {
+            const int64_t want = std::min<int64_t>(i + kHandOff, n - 1);
+            while ((ready = avail->load(std::memory_order_acquire)) < want && ready <= i)
+                std::this_thread::yield();
+        }
         const uint32_t j = static_cast<uint32_t>(i) + raw[i] % (un - static_cast<uint32_t>(i));
         const uint32_t a = ids[i], b = ids[j];
         ids[i] = b;
@@ -154,8 +165,10 @@ struct PermStream::Impl
     int count = 0, slots = 0, max_threads = 0;
     int64_t *ring = nullptr;
     long long base = 0;     // global index of the current update's first permutation
-    long long produced = 0; // raw draws exist for [.., produced)
+    long long produced = 0; // all raw draws (and the state after them) exist for [.., produced)
+    long long started = 0;  // the producer has begun (or finished) the draws of [.., started): their walks may start
     long long next_job = 0; // next global index a worker walks
+    std::unique_ptr<std::atomic<int64_t>[]> filled; // per slot: raw draws written so far (producer -> walker hand-off)
     std::vector<std::vector<uint32_t>> raw;              // per slot: raw draws of its permutation
     std::vector<std::vector<unsigned char>> state_after; // per slot: generator state after its permutation
     std::vector<long long> raw_g, perm_g;                // per slot: which g its draws / its finished permutation belong to
@@ -191,8 +204,20 @@ struct PermStream::Impl
                 s = static_cast<int>(g % slots);
                 raw_g[s] = -2;
             }
-            raw[s].resize(static_cast<size_t>(n > 0 ? n - 1 : 0));
-            mt.fill(raw[s].data(), n > 0 ? n - 1 : 0);
+            const int64_t draws = n > 0 ? n - 1 : 0;
+            raw[s].resize(static_cast<size_t>(draws));
+            filled[s].store(0, std::memory_order_relaxed);
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                started = g + 1;
+            }
+            cv.notify_all();
+            for (int64_t off = 0; off < draws; off += kHandOff)
+            {
+                const int64_t len = std::min<int64_t>(kHandOff, draws - off);
+                mt.fill(raw[s].data() + off, len);
+                filled[s].store(off + len, std::memory_order_release);
+            }
             state_after[s] = blob;
             store_state(state_after[s].data(), mt);
             {
@@ -211,13 +236,13 @@ struct PermStream::Impl
             long long g;
             {
                 std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return quit || next_job < produced; });
+                cv.wait(lk, [&] { return quit || next_job < started; });
                 if (quit)
                     return;
                 g = next_job++;
             }
             const int s = static_cast<int>(g % slots);
-            walk(raw[s].data(), n, ring + static_cast<int64_t>(s) * n, ids);
+            walk(raw[s].data(), n, ring + static_cast<int64_t>(s) * n, ids, &filled[s]);
             {
                 std::lock_guard<std::mutex> lk(mu);
                 perm_g[s] = g;
@@ -283,7 +308,8 @@ int PermStream::start(const void *rng_state, int64_t n, int count, int64_t *ring
     s.mt = mt;
     s.blob.assign(static_cast<const unsigned char *>(rng_state), static_cast<const unsigned char *>(rng_state) + kStateBytes);
     s.n = n, s.count = count, s.slots = slots, s.ring = ring, s.max_threads = max_threads;
-    s.base = s.produced = s.next_job = 0;
+    s.base = s.produced = s.started = s.next_job = 0;
+    s.filled.reset(new std::atomic<int64_t>[static_cast<size_t>(slots > 0 ? slots : 1)]);
     s.raw.assign(static_cast<size_t>(slots), {});
     s.state_after.assign(static_cast<size_t>(slots), {});
     s.raw_g.assign(static_cast<size_t>(slots), -1);
