@@ -441,8 +441,8 @@ def run_ours(args, w: Workload, rank: int, local_rank: int, world: int):
     if w.name == "cfg3" and world == 1:
         # dram__bytes_read.sum + dram__bytes_write.sum of one launch (= one epoch) from the committed ncu --set full capture;
         # the algorithmic bytes of an epoch are the gathered rollout rows, 262144 x 112 B = 29.4 MB: no wasted re-reads
-        roofline["traffic"] = (29649152 + 651776) if mlp_tc else (29616128 + 353792)
-        roofline["traffic_source"] = "profiles/r2b_mlp_update_tc_cfg3_raw.csv" if mlp_tc else "profiles/r1b_mlp_update_cfg3_raw.csv"
+        roofline["traffic"] = (29662464 + 775680) if mlp_tc else (29616128 + 353792)
+        roofline["traffic_source"] = "profiles/r2c_mlp_update_tc_cfg3_raw.csv" if mlp_tc else "profiles/r1b_mlp_update_cfg3_raw.csv"
     if w.base == "cnn" and os.environ.get("CPPRL_B200_CNN_FP32") != "1":
         # the ten CnnBase contractions run on tcgen05 as 3xTF32 (hi*hi + hi*lo + lo*hi): three TF32 MMAs per
         # algorithmic product at half the bf16 rate, so this path's own ceiling is the measured bf16 peak / 6
